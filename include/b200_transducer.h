@@ -1,0 +1,100 @@
+/*
+ * b200_transducer.h — C ABI of libb200_transducer.so
+ *
+ * Drop-in boundary for the transducer hot path of WeNet (reference tree:
+ * Vindicator645/wenet-celoss).  Every entry point takes raw DEVICE pointers
+ * owned by the caller, plain sizes and a CUDA stream handle; the library
+ * allocates nothing, keeps no global state except a thread-local error string,
+ * enqueues its kernels on the given stream and returns immediately.
+ * Return value: 0 = ok, non-zero = error (text via b200_last_error()).
+ * Nothing throws across this boundary.
+ *
+ * The reference has no FFI of its own for this path: the arithmetic lives in
+ * torchaudio / ATen and is reached through Python call sites.  Each function
+ * below names the reference call site (file:line under /root/reference) whose
+ * work it replaces.  The Python wrappers in wenet_celoss_b200/ bind these via
+ * ctypes.
+ */
+#ifndef B200_TRANSDUCER_H_
+#define B200_TRANSDUCER_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* cudaStream_t without pulling in cuda_runtime.h */
+typedef void* b200_stream_t;
+
+/* element types of a logits / gradient buffer */
+enum b200_dtype { B200_F32 = 0, B200_F16 = 1, B200_BF16 = 2 };
+
+enum b200_status {
+  B200_OK = 0,
+  B200_ERR_ARG = 1,      /* bad shape / null pointer / unsupported dtype */
+  B200_ERR_CUDA = 2,     /* a CUDA runtime call or launch failed */
+  B200_ERR_WORKSPACE = 3 /* workspace too small */
+};
+
+/* ---- library ---------------------------------------------------------- */
+int b200_version(void);
+const char* b200_last_error(void);
+/* compute capability the kernels were compiled for (100 => sm_100a) */
+int b200_compiled_arch(void);
+/* number of kernel launches this library has enqueued in this process */
+uint64_t b200_launch_count(void);
+
+/* ---- RNN-T loss over materialised logits ------------------------------
+ * replaces torchaudio.functional.rnnt_loss as called at
+ *   wenet/transducer/transducer.py:142-147 (training, reduction="mean")
+ *   wenet/transducer/transducer.py:296-301 (rescoring, reduction="none")
+ * logits  [B,T,U1,V] contiguous, dtype f32/f16/bf16   (U1 = max target len + 1)
+ * targets [B,U1-1] int32 zero padded; logit_len/target_len [B] int32.
+ * lse, lp_blank, lp_emit, alpha, beta: [B,T,U1] f32; costs [B] f32.
+ */
+
+/* pass 1: per lattice cell, log-sum-exp over V and the two log-probs the
+ * lattice needs (blank, and the target symbol y[b,u] for u < U_b). Cells with
+ * t >= T_b or u > U_b are not read. */
+int b200_rnnt_logprobs(const void* logits, int dtype, const int32_t* targets,
+                       const int32_t* logit_len, const int32_t* target_len,
+                       int B, int T, int U1, int V, int blank,
+                       float* lse, float* lp_blank, float* lp_emit,
+                       b200_stream_t stream);
+
+/* pass 2: alpha / beta lattices by anti-diagonal wavefront; costs[b] = -beta[b,0,0] */
+int b200_rnnt_lattice(const float* lp_blank, const float* lp_emit,
+                      const int32_t* logit_len, const int32_t* target_len,
+                      int B, int T, int U1,
+                      float* alpha, float* beta, float* costs,
+                      b200_stream_t stream);
+
+/* pass 2b: per-cell gradient coefficients {c0, cb, ce, scale} (float4 per cell):
+ *   grad[v] = scale * ( exp(x[v]+c0) - [v==blank] exp(x[v]+cb) - [v==y_u] exp(x[v]+ce) )
+ * with scale = dy[b]; padded cells get c0=cb=ce=-inf (gradient exactly 0). */
+int b200_rnnt_grad_coef(const float* lse, const float* alpha, const float* beta,
+                        const float* costs, const float* dy,
+                        const int32_t* targets,
+                        const int32_t* logit_len, const int32_t* target_len,
+                        int B, int T, int U1, int blank,
+                        float* coef /* [B,T,U1,4] */, b200_stream_t stream);
+
+/* pass 3: gradient w.r.t. logits, same dtype/layout as logits; softmax is
+ * recomputed from logits + coef; clamp <= 0 disables clamping. */
+int b200_rnnt_grad(const void* logits, int dtype, const int32_t* targets,
+                   const float* coef, int B, int T, int U1, int V, int blank,
+                   float clamp, void* grad, b200_stream_t stream);
+
+/* convenience: passes 1+2 back to back */
+int b200_rnnt_loss_fwd(const void* logits, int dtype, const int32_t* targets,
+                       const int32_t* logit_len, const int32_t* target_len,
+                       int B, int T, int U1, int V, int blank,
+                       float* costs, float* lse, float* lp_blank, float* lp_emit,
+                       float* alpha, float* beta, b200_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_TRANSDUCER_H_ */

@@ -1,0 +1,277 @@
+"""oracle/reference.py — TEST INFRASTRUCTURE, NOT THE PRODUCT.
+
+CPU restatement (PyTorch fp32 on CPU + the same third-party kernels the reference
+calls) of the transducer hot path of Vindicator645/wenet-celoss.  Only tests/,
+``__graft_entry__.smoke()`` and bench.py's ``cpu_baseline`` / ``--impl reference``
+legs may import this module; nothing under wenet_celoss_b200/ does.
+
+What is restated, and from where (paths under /root/reference):
+  joint_logits            wenet/transducer/joint.py:45-70
+  OracleJoint             wenet/transducer/joint.py:11-43 (parameter names kept)
+  OraclePredictor         wenet/transducer/predictor.py:58-200 (RNNPredictor, lstm)
+  OracleCTC               wenet/transformer/ctc.py:21-84
+  add_blank               wenet/utils/common.py:56-87
+  log_add                 wenet/utils/common.py:268-276
+  transducer_loss         wenet/transducer/transducer.py:124-147
+  transducer_score        wenet/transducer/transducer.py:277-302
+  greedy_search           wenet/transducer/search/greedy_search copy.py:6-63 and
+                          wenet/transducer/search/greedy_search.py:34-176 with
+                          context_filter_state='off' and an identity context bias
+  prefix_beam_search      wenet/transducer/search/prefix_beam_search.py:22-148
+
+Third-party arithmetic is NOT re-derived here: like the reference, this module
+calls torchaudio.functional.rnnt_loss (reference pin torchaudio==0.10.0,
+README.md:57) and torch's CTC loss / LSTM (pin torch==1.10.0).  The fp64 C
+restatement of those two recurrences lives in oracle/lattice_ref.c.
+
+Pinning: the reference's own tests hold no vectors for this path.
+oracle/gen_golden.py runs the real reference modules from /root/reference on
+seeded inputs, checks every function here against them and writes the fixtures
+in tests/golden/ that the CPU test-suite replays.
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+
+# --------------------------------------------------------------------------- helpers
+def add_blank(ys_pad: torch.Tensor, blank: int, ignore_id: int) -> torch.Tensor:
+    """[B,L] -> [B,L+1]: blank in column 0, padding (ignore_id) replaced by blank."""
+    head = ys_pad.new_full((ys_pad.size(0), 1), blank)
+    ys = torch.cat([head, ys_pad], dim=1)
+    return ys.masked_fill(ys == ignore_id, blank)
+
+
+def log_add(values: Sequence[float]) -> float:
+    """log(sum(exp(v))) in Python double; all -inf stays -inf."""
+    if all(v == -math.inf for v in values):
+        return -math.inf
+    top = max(values)
+    return top + math.log(sum(math.exp(v - top) for v in values))
+
+
+# --------------------------------------------------------------------------- modules
+class OracleJoint(nn.Module):
+    """Add-mode joint with tanh: parameter names match TransducerJoint."""
+
+    def __init__(self, vocab: int, enc_dim: int, pred_dim: int, join_dim: int):
+        super().__init__()
+        self.enc_ffn = nn.Linear(enc_dim, join_dim)
+        self.pred_ffn = nn.Linear(pred_dim, join_dim)
+        self.ffn_out = nn.Linear(join_dim, vocab)
+
+    def forward(self, enc_out: torch.Tensor, pred_out: torch.Tensor) -> torch.Tensor:
+        return joint_logits(enc_out, pred_out, self)
+
+
+def joint_logits(enc_out: torch.Tensor, pred_out: torch.Tensor, joint) -> torch.Tensor:
+    """[B,T,E], [B,U1,P] -> [B,T,U1,V] = ffn_out(tanh(enc_ffn(e)[:, :, None] + pred_ffn(p)[:, None]))."""
+    e = F.linear(enc_out, joint.enc_ffn.weight, joint.enc_ffn.bias)
+    p = F.linear(pred_out, joint.pred_ffn.weight, joint.pred_ffn.bias)
+    h = torch.tanh(e[:, :, None, :] + p[:, None, :, :])
+    return F.linear(h, joint.ffn_out.weight, joint.ffn_out.bias)
+
+
+class OraclePredictor(nn.Module):
+    """Embedding -> dropout -> LSTM stack -> Linear; names match RNNPredictor."""
+
+    def __init__(self, vocab: int, embed: int, out_dim: int, hidden: int, layers: int,
+                 embed_dropout: float = 0.1, dropout: float = 0.1):
+        super().__init__()
+        self.n_layers = layers
+        self.hidden_size = hidden
+        self.embed = nn.Embedding(vocab, embed)
+        self.dropout = nn.Dropout(embed_dropout)
+        self.rnn = nn.LSTM(input_size=embed, hidden_size=hidden, num_layers=layers, bias=True,
+                           batch_first=True, dropout=dropout)
+        self.projection = nn.Linear(hidden, out_dim)
+
+    def init_state(self, batch_size: int, device, method: str = "zero") -> List[torch.Tensor]:
+        z = torch.zeros(self.n_layers, batch_size, self.hidden_size, device=device)
+        return [z, z.clone()]
+
+    def forward(self, tokens: torch.Tensor, cache: Optional[List[torch.Tensor]] = None):
+        state = cache if cache is not None else self.init_state(tokens.size(0), tokens.device)
+        out, _ = self.rnn(self.dropout(self.embed(tokens)), (state[0], state[1]))
+        return self.projection(out)
+
+    def forward_step(self, token: torch.Tensor, padding: torch.Tensor, cache: List[torch.Tensor]):
+        h0, c0 = cache
+        out, (h1, c1) = self.rnn(self.dropout(self.embed(token)), (h0, c0))
+        out = self.projection(out)
+        # padding==1 keeps the old state (always 0 on the search paths)
+        h1 = padding * h0 + h1 * (1 - padding)
+        c1 = padding * c0 + c1 * (1 - padding)
+        return out, [h1, c1]
+
+    def cache_to_batch(self, caches):
+        return [torch.cat([c[0] for c in caches], dim=1), torch.cat([c[1] for c in caches], dim=1)]
+
+    def batch_to_cache(self, cache):
+        hs, cs = cache
+        return [[hs[:, i:i + 1], cs[:, i:i + 1]] for i in range(hs.size(1))]
+
+
+class OracleCTC(nn.Module):
+    def __init__(self, vocab: int, enc_dim: int):
+        super().__init__()
+        self.ctc_lo = nn.Linear(enc_dim, vocab)
+
+    def forward(self, hs_pad, hlens, ys_pad, ys_lens):
+        return ctc_forward(hs_pad, hlens, ys_pad, ys_lens, self)
+
+    def log_softmax(self, hs_pad):
+        return F.log_softmax(self.ctc_lo(hs_pad), dim=2)
+
+    def argmax(self, hs_pad):
+        return torch.argmax(self.ctc_lo(hs_pad), dim=2)
+
+
+def ctc_forward(hs_pad, hlens, ys_pad, ys_lens, ctc) -> torch.Tensor:
+    """sum_b nll_b / B with blank=0, zero_infinity=False (ctc.py:57-63)."""
+    logp = F.log_softmax(ctc.ctc_lo(hs_pad).transpose(0, 1), dim=2)  # [T,B,V]
+    total = F.ctc_loss(logp, ys_pad, hlens, ys_lens, blank=0, reduction="sum", zero_infinity=False)
+    return total / logp.size(1)
+
+
+class OracleModel(nn.Module):
+    """What the search functions read from the model: predictor, joint, ctc, blank."""
+
+    def __init__(self, vocab: int, enc_dim: int = 256, pred_dim: int = 256, join_dim: int = 512,
+                 embed: int = 256, hidden: int = 256, layers: int = 2, blank: int = 0):
+        super().__init__()
+        self.blank = blank
+        self.vocab_size = vocab
+        self.predictor = OraclePredictor(vocab, embed, pred_dim, hidden, layers)
+        self.joint = OracleJoint(vocab, enc_dim, pred_dim, join_dim)
+        self.ctc = OracleCTC(vocab, enc_dim)
+
+
+# --------------------------------------------------------------------------- losses
+def rnnt_targets(text: torch.Tensor, text_lengths: torch.Tensor, enc_lens: torch.Tensor,
+                 ignore_id: int = -1):
+    """int32 zero-padded targets and int32 lengths (transducer.py:137-141)."""
+    t = text.to(torch.int64)
+    t = torch.where(t == ignore_id, torch.zeros_like(t), t).to(torch.int32)
+    return t, enc_lens.to(torch.int32), text_lengths.to(torch.int32)
+
+
+def transducer_loss(model, enc_out, enc_lens, text, text_lengths, reduction="mean",
+                    ignore_id: int = -1) -> torch.Tensor:
+    """predictor -> joint -> torchaudio rnnt_loss, exactly the chain at transducer.py:124-147."""
+    import torchaudio
+    ys_in = add_blank(text, model.blank, ignore_id)
+    pred_out = model.predictor(ys_in)
+    logits = joint_logits(enc_out, pred_out, model.joint)
+    tgt, tl, ul = rnnt_targets(text, text_lengths, enc_lens, ignore_id)
+    return torchaudio.functional.rnnt_loss(logits, tgt, tl, ul, blank=model.blank, reduction=reduction)
+
+
+def transducer_score(model, enc_out, enc_lens, hyps_pad, hyps_lens, ignore_id: int = -1):
+    """-cost per hypothesis (transducer.py:277-302)."""
+    return -transducer_loss(model, enc_out, enc_lens, hyps_pad, hyps_lens, reduction="none",
+                            ignore_id=ignore_id)
+
+
+# --------------------------------------------------------------------------- greedy
+@torch.no_grad()
+def greedy_search(model, enc_out: torch.Tensor, enc_len: int, n_steps: int = 64,
+                  record_margin: bool = False):
+    """One utterance ([1,T,E]).  Returns the emitted token list (and, optionally, the
+    smallest top-1/top-2 log-prob margin seen, to attribute mismatches to ties)."""
+    dev = enc_out.device
+    blank = model.blank
+    pad = torch.zeros(1, 1, device=dev)
+    token = torch.tensor([[blank]], device=dev)
+    state = model.predictor.init_state(1, device=dev)
+    pending_state = state
+    pred_step = None
+    need_predictor = True
+    emitted_here = 0
+    t = 0
+    hyp: List[int] = []
+    min_margin = math.inf
+    while t < int(enc_len):
+        if need_predictor:
+            pred_step, pending_state = model.predictor.forward_step(token, pad, state)
+        logp = joint_logits(enc_out[:, t:t + 1, :], pred_step, model.joint).log_softmax(dim=-1)
+        flat = logp.reshape(-1)
+        k = int(flat.argmax())
+        if record_margin:
+            top2 = flat.topk(2).values
+            min_margin = min(min_margin, float(top2[0] - top2[1]))
+        if k != blank:
+            hyp.append(k)
+            need_predictor = True
+            emitted_here += 1
+            token = torch.tensor([[k]], device=dev)
+            state = pending_state
+        if k == blank or emitted_here >= n_steps:
+            if k == blank:
+                need_predictor = False
+            t += 1
+            emitted_here = 0
+    return (hyp, min_margin) if record_margin else hyp
+
+
+# --------------------------------------------------------------------------- beam
+class Hyp:
+    __slots__ = ("hyp", "score", "cache")
+
+    def __init__(self, hyp, score, cache):
+        self.hyp, self.score, self.cache = hyp, score, cache
+
+
+@torch.no_grad()
+def prefix_beam_search(model, enc_out: torch.Tensor, beam_size: int = 10, ctc_weight: float = 0.3,
+                       transducer_weight: float = 0.7) -> List[Hyp]:
+    """One utterance ([1,T,E]); exactly one expansion per frame; returns the beam
+    (each ``hyp`` starts with the blank the search was seeded with)."""
+    dev = enc_out.device
+    blank = model.blank
+    T = enc_out.size(1)
+    ctc_lp = model.ctc.log_softmax(enc_out).squeeze(0)  # [T,V]
+    beam = [Hyp([blank], 0.0, model.predictor.init_state(1, device=dev))]
+    for i in range(T):
+        last = torch.tensor([h.hyp[-1] for h in beam], dtype=torch.int, device=dev)
+        state = model.predictor.cache_to_batch([h.cache for h in beam])
+        base = torch.tensor([h.score for h in beam]).to(dev)  # python float -> fp32
+        pad = torch.zeros(last.size(0), 1, device=dev)
+        pred, new_state = model.predictor.forward_step(last.unsqueeze(-1), pad, state)
+        logp = joint_logits(enc_out[:, i:i + 1, :], pred, model.joint).log_softmax(dim=-1)
+        logp = logp.squeeze(1).squeeze(1)  # [N,V]
+        per_hyp_state = model.predictor.batch_to_cache(new_state)
+        fused = torch.log(transducer_weight * torch.exp(logp) + ctc_weight * torch.exp(ctc_lp[i].unsqueeze(0)))
+        top_lp, top_ix = fused.topk(beam_size)
+        cand = base.unsqueeze(1) + top_lp  # fp32
+        expanded: List[Hyp] = []
+        for j, h in enumerate(beam):
+            for k in range(beam_size):
+                sym = int(top_ix[j, k])
+                sc = cand[j, k].item()
+                if sym == blank:
+                    expanded.append(Hyp(list(h.hyp), sc, h.cache))
+                else:
+                    expanded.append(Hyp(h.hyp + [sym], sc, per_hyp_state[j]))
+        merged: List[Hyp] = [expanded[0]]
+        for cnd in expanded[1:]:
+            for kept in merged:
+                if kept.hyp == cnd.hyp:
+                    kept.score = log_add([kept.score, cnd.score])
+                    break
+            else:
+                merged.append(cnd)
+        merged.sort(key=lambda h: h.score, reverse=True)  # stable
+        beam = merged[:beam_size]
+    return beam
+
+
+def beam_search_best(model, enc_out, **kw) -> Tuple[List[int], float]:
+    """(hyp without the seed blank, score) as Transducer.beam_search returns (transducer.py:377)."""
+    beam = prefix_beam_search(model, enc_out, **kw)
+    return beam[0].hyp[1:], beam[0].score

@@ -1,0 +1,89 @@
+"""ctypes binding of libb200_transducer.so (the C ABI declared in include/b200_transducer.h).
+
+There is no CPU fallback: if the shared library is missing or a call fails, the
+wrappers raise.  PyTorch is used only for device memory and streams.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_char_p, c_float, c_int, c_size_t, c_uint64, c_void_p, c_double
+from pathlib import Path
+
+import torch
+
+_PKG = Path(__file__).resolve().parent
+LIB_PATH = _PKG / "libb200_transducer.so"
+
+F32, F16, BF16 = 0, 1, 2
+_DTYPES = {torch.float32: F32, torch.float16: F16, torch.bfloat16: BF16}
+
+_lib = None
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+def lib() -> ctypes.CDLL:
+    """Load the library once; fail loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise B200Error(
+                f"{LIB_PATH} not found: build it with `python -m wenet_celoss_b200.build` "
+                "(there is no CPU or PyTorch fallback for this path)")
+        _lib = ctypes.CDLL(str(LIB_PATH))
+        _declare(_lib)
+    return _lib
+
+
+def _declare(L: ctypes.CDLL) -> None:
+    L.b200_version.restype = c_int
+    L.b200_last_error.restype = c_char_p
+    L.b200_compiled_arch.restype = c_int
+    L.b200_launch_count.restype = c_uint64
+    # every compute entry point returns int status; arguments are passed as
+    # c_void_p / c_int / c_float explicitly at the call sites via _call().
+
+
+def dtype_code(t: torch.Tensor) -> int:
+    try:
+        return _DTYPES[t.dtype]
+    except KeyError:
+        raise B200Error(f"unsupported dtype {t.dtype}") from None
+
+
+def ptr(t) -> c_void_p:
+    if t is None:
+        return c_void_p(0)
+    return c_void_p(t.data_ptr())
+
+
+def stream_handle(device=None) -> c_void_p:
+    return c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def call(fn_name: str, *args) -> None:
+    """Invoke an int-returning entry point and raise on a non-zero status."""
+    L = lib()
+    fn = getattr(L, fn_name)
+    fn.restype = c_int
+    rc = fn(*args)
+    if rc != 0:
+        msg = L.b200_last_error().decode("utf-8", "replace")
+        raise B200Error(f"{fn_name} failed (status {rc}): {msg}")
+
+
+def launch_count() -> int:
+    return int(lib().b200_launch_count())
+
+
+def require_cuda(t: torch.Tensor, name: str) -> None:
+    if not t.is_cuda:
+        raise B200Error(f"{name} must be a CUDA tensor (no CPU path in wenet_celoss_b200)")
+
+
+i32 = c_int
+f32 = c_float
+f64 = c_double
+size_t = c_size_t
