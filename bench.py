@@ -1,0 +1,387 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the transducer hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
+
+Metric: RNN-T loss fwd+bwd utterances/second at B=32, T=500, U=100, V=5000 (cfg3 of
+BASELINE.json: bf16 logits).  One "step" = one forward+backward pass of the hot path
+over one synthetic batch.  Prints ONE JSON line on rank 0.
+
+Workloads (``--workload``):
+  rnnt_logits   drop-in rnnt_loss(logits, ...) over materialised bf16 logits resident in HBM
+                (HBM-bound kernels: log-sum-exp pass, lattice, gradient pass)
+
+``--impl reference`` times the reference's own CPU implementation of the path (the
+oracle port: torch joint + torchaudio.functional.rnnt_loss on the host cores) on a
+bounded sample of the same workload.  It is the only mode that executes oracle/.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+import torch  # noqa: E402
+
+CFG3 = dict(B=32, T=500, U=100, V=5000, E=256, P=256, J=512)
+METRIC = "rnnt_loss_fwd_bwd_utts_per_sec"
+UNIT = "utt/s"
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return dict(hbm=float(d["hbm_gbs"]), bf16=float(d["bf16_tflops"]),
+                    bf16_sustained=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+                    source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm=6650.0, bf16=1590.0, bf16_sustained=1400.0, source="fallback (B200_PROFILING.md)")
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clock / throttle-reason samples during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+            self.thr.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------- synthetic data
+def synth_lengths(B, T, U, gen, ragged):
+    if not ragged:
+        return torch.full((B,), T, dtype=torch.int32), torch.full((B,), U, dtype=torch.int32)
+    tl = torch.randint(int(0.6 * T), T + 1, (B,), generator=gen, dtype=torch.int32)
+    ul = torch.randint(int(0.5 * U), U + 1, (B,), generator=gen, dtype=torch.int32)
+    tl[0], ul[-1] = T, U
+    return tl, ul
+
+
+class RnntLogitsWorkload:
+    """rnnt_loss(logits, ...) fwd+bwd over materialised bf16 logits (HBM-resident)."""
+    name = "rnnt_logits"
+
+    def __init__(self, cfg, rank, ragged=False):
+        import wenet_celoss_b200 as pkg
+        self.pkg = pkg
+        self.cfg = cfg
+        B, T, U, V = cfg["B"], cfg["T"], cfg["U"], cfg["V"]
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        g = torch.Generator().manual_seed(1234 + rank)
+        self.tl_h, self.ul_h = synth_lengths(B, T, U, g, ragged)
+        self.targets_h = torch.randint(1, V, (B, U), generator=g, dtype=torch.int32)
+        gd = torch.Generator(device=self.dev).manual_seed(1234 + rank)
+        self.logits = torch.empty(B, T, U + 1, V, dtype=torch.bfloat16, device=self.dev)
+        for b in range(B):  # fill in slices: no fp32 temporary of the whole tensor
+            self.logits[b] = torch.randn(T, U + 1, V, generator=gd, device=self.dev, dtype=torch.float32)
+        self.logits.requires_grad_(True)
+        self.targets = self.targets_h.to(self.dev)
+        self.tl = self.tl_h.to(self.dev)
+        self.ul = self.ul_h.to(self.dev)
+        self.N = B * T * (U + 1) * V
+        self.elem = 2
+
+    def step(self):
+        self.logits.grad = None
+        loss = self.pkg.rnnt_loss(self.logits, self.targets, self.tl, self.ul, blank=0,
+                                  reduction="mean")
+        loss.backward()
+        return loss
+
+    def algorithmic_bytes(self):
+        return 3 * self.N * self.elem
+
+    def kernel_breakdown(self, iters=5):
+        """CUDA-event time of each C-ABI pass on the launching stream."""
+        from wenet_celoss_b200 import _lib
+        from wenet_celoss_b200._lib import f32, i32, ptr
+        from wenet_celoss_b200.rnnt import rnnt_grad_coef
+        B, T, U, V = (self.cfg[k] for k in "BTUV")
+        U1 = U + 1
+        x = self.logits.detach()
+        lat = torch.empty(5, B, T, U1, dtype=torch.float32, device=self.dev)
+        lse, lpb, lpe, alpha, beta = lat.unbind(0)
+        costs = torch.empty(B, dtype=torch.float32, device=self.dev)
+        dy = torch.full((B,), 1.0 / B, dtype=torch.float32, device=self.dev)
+        grad = torch.empty_like(x)
+        st = _lib.stream_handle(self.dev)
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)
+        coef_box = {}
+
+        def k_logprobs():
+            _lib.call("b200_rnnt_logprobs", ptr(x), i32(_lib.BF16), ptr(self.targets), ptr(self.tl),
+                      ptr(self.ul), i32(B), i32(T), i32(U1), i32(V), i32(0), ptr(lse), ptr(lpb),
+                      ptr(lpe), st)
+
+        def k_lattice():
+            _lib.call("b200_rnnt_lattice", ptr(lpb), ptr(lpe), ptr(self.tl), ptr(self.ul), i32(B),
+                      i32(T), i32(U1), ptr(alpha), ptr(beta), ptr(costs), st)
+
+        def k_coef():
+            coef_box["c"] = rnnt_grad_coef(lse, alpha, beta, costs, dy, self.targets, self.tl,
+                                           self.ul, 0)
+
+        def k_grad():
+            _lib.call("b200_rnnt_grad", ptr(x), i32(_lib.BF16), ptr(self.targets), ptr(coef_box["c"]),
+                      i32(B), i32(T), i32(U1), i32(V), i32(0), f32(-1.0), ptr(grad), st)
+
+        out = {}
+        for name, fn in (("rnnt_logprobs_kernel", k_logprobs), ("rnnt_lattice_kernel", k_lattice),
+                         ("rnnt_grad_coef_kernel", k_coef), ("rnnt_grad_kernel", k_grad)):
+            ts = []
+            for _ in range(iters + 1):
+                flush.zero_()  # evict L2 between timed launches (small-tensor kernels)
+                e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+                e0.record()
+                fn()
+                e1.record()
+                e1.synchronize()
+                ts.append(e0.elapsed_time(e1))
+            out[name] = statistics.mean(ts[1:])
+        return out
+
+
+# --------------------------------------------------------------------------- reference arm
+def reference_step(cfg, T_s, threads, seed=0):
+    """One fwd+bwd of the reference path (oracle port: torch joint + torchaudio CPU
+    rnnt_loss, wenet/transducer/transducer.py:132-147) on one utterance truncated to
+    T_s frames.  Returns seconds."""
+    import torchaudio
+    from oracle import reference as orc
+    torch.set_num_threads(threads)
+    g = torch.Generator().manual_seed(seed)
+    U, V, E, P, J = cfg["U"], cfg["V"], cfg["E"], cfg["P"], cfg["J"]
+    joint = orc.OracleJoint(V, E, P, J)
+    enc = torch.randn(1, T_s, E, generator=g, requires_grad=True)
+    pred = torch.randn(1, U + 1, P, generator=g, requires_grad=True)
+    tgt = torch.randint(1, V, (1, U), generator=g, dtype=torch.int32)
+    tl = torch.tensor([T_s], dtype=torch.int32)
+    ul = torch.tensor([U], dtype=torch.int32)
+    t0 = time.perf_counter()
+    logits = joint(enc, pred)
+    loss = torchaudio.functional.rnnt_loss(logits, tgt, tl, ul, blank=0, reduction="mean")
+    loss.backward()
+    return time.perf_counter() - t0
+
+
+def run_reference(args, cfg):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    budget_s = 120.0
+    T_s = 50
+    reference_step(cfg, T_s, threads)  # warms the thread pool / allocator
+    t_probe = reference_step(cfg, T_s, threads)
+    per_frame = t_probe / T_s
+    n_total = args.steps + args.warmup
+    T_s = int(max(10, min(cfg["T"], budget_s / max(n_total, 1) / per_frame)))
+    for _ in range(args.warmup):
+        reference_step(cfg, T_s, threads)
+    ts = [reference_step(cfg, T_s, threads, seed=i + 1) for i in range(args.steps)]
+    sec = sum(ts)
+    frac = T_s / cfg["T"]  # fraction of one utterance's lattice processed per step
+    value = args.steps * frac / sec
+    sample = (f"1 utterance x T={T_s} of {cfg['T']} frames (U={cfg['U']}, V={cfg['V']}), fp32, "
+              f"joint + torchaudio.functional.rnnt_loss fwd+bwd per step; utt/s scaled by T_s/T")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "rnnt_joint_loss_fwd_bwd B=32 T=500 U=100 V=5000 (cfg3)", **cfg},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------- main arm
+def cpu_baseline(cfg):
+    threads = os.cpu_count() or 1
+    T_s = 50
+    reference_step(cfg, T_s, threads)
+    t = reference_step(cfg, T_s, threads)
+    T_s = int(max(10, min(cfg["T"], 10.0 / (t / T_s))))
+    t = min(reference_step(cfg, T_s, threads, seed=1), reference_step(cfg, T_s, threads, seed=2))
+    return {"value": (T_s / cfg["T"]) / t, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"1 utterance x T={T_s}/{cfg['T']} frames, U={cfg['U']}, V={cfg['V']}, fp32 "
+                      f"torch joint + torchaudio rnnt_loss fwd+bwd on the host, best of 2, scaled by T_s/T"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="rnnt_logits")
+    ap.add_argument("--ragged", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    cfg = dict(CFG3)
+
+    if args.impl == "reference":
+        run_reference(args, cfg)
+        return
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py --impl b200 needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    import wenet_celoss_b200 as pkg
+    wl = RnntLogitsWorkload(cfg, rank, ragged=args.ragged)
+    pk = peaks()
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        wl.step()
+    sync_all()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    n0 = pkg.launch_count()
+    e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+    e0.record()
+    for _ in range(args.steps):
+        loss = wl.step()
+    e1.record()
+    sync_all()
+    ms = e0.elapsed_time(e1)
+    launches = pkg.launch_count() - n0
+    clocks = sampler.stop() if rank == 0 else None
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    B = cfg["B"]
+    value = world * B * args.steps / (ms * 1e-3)
+
+    # e2e: for the materialised-logits API the step's host-side inputs are the targets and
+    # lengths (logits are produced on the device by the joint); result read back = loss.
+    sync_all()
+    tgt_pin = wl.targets_h.pin_memory()
+    tl_pin, ul_pin = wl.tl_h.pin_memory(), wl.ul_h.pin_memory()
+    loss_pin = torch.empty((), dtype=torch.float32).pin_memory()
+    f0, f1 = torch.cuda.Event(True), torch.cuda.Event(True)
+    f0.record()
+    for _ in range(args.steps):
+        wl.targets.copy_(tgt_pin, non_blocking=True)
+        wl.tl.copy_(tl_pin, non_blocking=True)
+        wl.ul.copy_(ul_pin, non_blocking=True)
+        l = wl.step()
+        loss_pin.copy_(l.detach().float(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    f1.record()
+    sync_all()
+    ms_e2e = f0.elapsed_time(f1)
+    if dist is not None:
+        t = torch.tensor([ms_e2e], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_e2e = float(t.item())
+    e2e = {"value": world * B * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
+           "h2d_bytes_per_step": int(tgt_pin.numel() * 4 + tl_pin.numel() * 4 + ul_pin.numel() * 4),
+           "d2h_bytes_per_step": 4,
+           "note": "rnnt_loss(logits,...) API: logits are device-produced; host inputs are targets+lengths"}
+
+    if rank == 0:
+        kb = wl.kernel_breakdown()
+        dom = "rnnt_grad_kernel"
+        dom_bytes = 2 * wl.N * wl.elem
+        achieved = dom_bytes / (kb[dom] * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s",
+                "frac": achieved / pk["hbm"], "traffic": None, "peak_source": pk["source"],
+                "algorithmic_bytes_per_launch": dom_bytes,
+                "kernel_ms": kb,
+                "other": {"rnnt_logprobs_kernel": {
+                    "achieved": wl.N * wl.elem / (kb["rnnt_logprobs_kernel"] * 1e-3) / 1e9,
+                    "frac": wl.N * wl.elem / (kb["rnnt_logprobs_kernel"] * 1e-3) / 1e9 / pk["hbm"]}},
+                "step_frac_of_hbm_roofline": wl.algorithmic_bytes() / (ms / args.steps * 1e-3) / 1e9 / pk["hbm"]}
+        cb = None if args.no_cpu_baseline else cpu_baseline(cfg)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"{wl.name}: rnnt_loss fwd+bwd over materialised bf16 logits, "
+                                   "B=32 T=500 U=100 V=5000 per GPU (cfg3)",
+                       "global_batch": world * B, **cfg, "ragged": bool(args.ragged),
+                       "l2": "inputs (16.2 GB logits) larger than L2", "parallelism": f"dp{world}"},
+            "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cb,
+            "clocks": clocks, "loss": float(loss.item()),
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

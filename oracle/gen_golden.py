@@ -266,65 +266,74 @@ def main():
         **{"g.ctc." + n: p.grad.numpy() for n, p in ref_ctc.named_parameters()})
 
     # ------------------------------------------------------------------ (D) greedy, (E) beam
+    # Random-init weights make the search degenerate (every frame emits n_steps copies of
+    # one symbol).  "mixed" rescales a few weights so that blank and
+    # non-blank steps interleave; "degenerate" keeps the raw weights and hits the cap.
     Bs, Ts = 4, 30
-    encs = torch.randn(Bs, Ts, E, generator=g)
+    encs = torch.randn(Bs, Ts, E, generator=g) * 2.0
     lens = torch.tensor([30, 22, 27, 30])
-    results = {}
-    for tag, bias, n_steps in (("biased", 1.2, 64), ("degenerate", 0.0, 3)):
-        with torch.no_grad():
-            ref_joint.ffn_out.bias[0] += bias
-            om.joint.load_state_dict(ref_joint.state_dict())
+    base_sd = {"p": ref_pred.state_dict(), "j": ref_joint.state_dict()}
+    base_sd = {k: {n: t.clone() for n, t in v.items()} for k, v in base_sd.items()}
+    for tag, n_steps in (("mixed", 64), ("degenerate", 3)):
+        ref_pred.load_state_dict(base_sd["p"])
+        ref_joint.load_state_dict(base_sd["j"])
+        if tag == "mixed":
+            with torch.no_grad():
+                ref_joint.ffn_out.weight *= 3.0
+                ref_joint.ffn_out.bias[0] += 3.0
+                ref_pred.projection.weight *= 16.0
+                ref_pred.embed.weight *= 4.0
+        om.predictor.load_state_dict(ref_pred.state_dict())
+        om.joint.load_state_dict(ref_joint.state_dict())
+        sw = {}
+        sw.update(sd_np(ref_pred, "predictor."))
+        sw.update(sd_np(ref_joint, "joint."))
+        sw.update(sd_np(ref_ctc, "ctc."))
+        results = {}
         hyps_all, margins = [], []
+        upm = types.SimpleNamespace(blank=0, predictor=ref_pred, joint=ref_joint,
+                                    context_bias=types.SimpleNamespace(
+                                        forward_bias_hidden=lambda a, b_: None,
+                                        forward_encoder_bias=lambda h, x: x,
+                                        forward_predictor_bias=lambda h, x: x))
         for b in range(Bs):
             e1 = encs[b:b + 1, :int(lens[b])]
             with contextlib.redirect_stdout(io.StringIO()):
                 fork = fork_greedy(ref_model, e1, lens[b], torch.IntTensor([[0]]), torch.IntTensor([1]),
                                    n_steps=n_steps, context_filter_state='off',
                                    context_decoder_labels_padded=torch.IntTensor([[0]]))[0][0]
-            class _Up(torch.nn.Module):
-                pass
-            upm = types.SimpleNamespace(blank=0, predictor=ref_pred, joint=ref_joint,
-                                        context_bias=types.SimpleNamespace(
-                                            forward_bias_hidden=lambda a, b_: None,
-                                            forward_encoder_bias=lambda h, x: x,
-                                            forward_predictor_bias=lambda h, x: x))
             up = greedy_up.basic_greedy_search(upm, e1, lens[b], n_steps=n_steps)[0]
             mine, margin = orc.greedy_search(om, e1, int(lens[b]), n_steps=n_steps, record_margin=True)
             assert fork == up == mine, (tag, b, fork, up, mine)
             hyps_all.append(mine)
             margins.append(margin)
-        width = max(len(h) for h in hyps_all)
+        width = max(1, max(len(h) for h in hyps_all))
         arr = np.full((Bs, width), -1, dtype=np.int64)
         for b, h in enumerate(hyps_all):
             arr[b, :len(h)] = h
-        results[f"greedy_{tag}_hyps"] = arr
-        results[f"greedy_{tag}_margin"] = np.array(margins)
-        results[f"greedy_{tag}_bias0"] = ref_joint.ffn_out.bias.detach().numpy().copy()
-        results[f"greedy_{tag}_nsteps"] = np.int64(n_steps)
-        if tag == "biased":
-            beam_size = 4
-            bs = PrefixBeamSearch(PassThroughEncoder(), ref_pred, ref_joint, ref_ctc, 0)
-            nb_h = np.full((Bs, beam_size, Ts + 1), -1, dtype=np.int64)
-            nb_s = np.full((Bs, beam_size), -np.inf)
-            nb_n = np.zeros(Bs, dtype=np.int64)
-            for b in range(Bs):
-                e1 = encs[b:b + 1, :int(lens[b])]
-                with torch.no_grad():
-                    beam, _ = bs.prefix_beam_search(e1, lens[b:b + 1], beam_size=beam_size,
-                                                    ctc_weight=0.3, transducer_weight=0.7)
-                    mine_b = orc.prefix_beam_search(om, e1, beam_size=beam_size, ctc_weight=0.3,
-                                                    transducer_weight=0.7)
-                assert [s.hyp for s in beam] == [s.hyp for s in mine_b]
-                assert np.allclose([s.score for s in beam], [s.score for s in mine_b], rtol=1e-9)
-                nb_n[b] = len(beam)
-                for k, s in enumerate(beam):
-                    nb_h[b, k, :len(s.hyp) - 1] = s.hyp[1:]
-                    nb_s[b, k] = s.score
-            results.update(beam_hyps=nb_h, beam_scores=nb_s, beam_n=nb_n, beam_size=np.int64(beam_size))
-        with torch.no_grad():
-            ref_joint.ffn_out.bias[0] -= bias
-    np.savez_compressed(GOLD / "search_small.npz", dims=dims, enc=encs.numpy(), lens=lens.numpy(),
-                        **results, **{"w." + k: v for k, v in weights.items()})
+        results.update(greedy_hyps=arr, greedy_margin=np.array(margins), n_steps=np.int64(n_steps))
+        beam_size = 4
+        bs = PrefixBeamSearch(PassThroughEncoder(), ref_pred, ref_joint, ref_ctc, 0)
+        nb_h = np.full((Bs, beam_size, Ts + 1), -1, dtype=np.int64)
+        nb_s = np.full((Bs, beam_size), -np.inf)
+        nb_n = np.zeros(Bs, dtype=np.int64)
+        for b in range(Bs):
+            e1 = encs[b:b + 1, :int(lens[b])]
+            with torch.no_grad():
+                beam, _ = bs.prefix_beam_search(e1, lens[b:b + 1], beam_size=beam_size,
+                                                ctc_weight=0.3, transducer_weight=0.7)
+                mine_b = orc.prefix_beam_search(om, e1, beam_size=beam_size, ctc_weight=0.3,
+                                                transducer_weight=0.7)
+            assert [s.hyp for s in beam] == [s.hyp for s in mine_b]
+            assert np.allclose([s.score for s in beam], [s.score for s in mine_b], rtol=1e-9)
+            nb_n[b] = len(beam)
+            for k, s in enumerate(beam):
+                nb_h[b, k, :len(s.hyp) - 1] = s.hyp[1:]
+                nb_s[b, k] = s.score
+        results.update(beam_hyps=nb_h, beam_scores=nb_s, beam_n=nb_n, beam_size=np.int64(beam_size),
+                       ctc_weight=np.float64(0.3), transducer_weight=np.float64(0.7))
+        np.savez_compressed(GOLD / f"search_{tag}.npz", dims=dims, enc=encs.numpy(), lens=lens.numpy(),
+                            **results, **{"w." + k: v for k, v in sw.items()})
     print("golden fixtures written to", GOLD)
     for f in sorted(GOLD.glob("*.npz")):
         print(f"  {f.name}: {f.stat().st_size} bytes")

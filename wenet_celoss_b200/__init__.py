@@ -1,0 +1,12 @@
+"""wenet_celoss_b200 — B200-native (sm_100a) transducer hot path for WeNet-style models.
+
+Public surface mirrors the reference call sites (Vindicator645/wenet-celoss):
+  rnnt_loss(logits, targets, logit_lengths, target_lengths, blank, clamp, reduction)
+      torchaudio.functional.rnnt_loss as used at wenet/transducer/transducer.py:142
+Everything is backed by libb200_transducer.so (C ABI in include/b200_transducer.h);
+there is no CPU or PyTorch fallback.
+"""
+from ._lib import B200Error, launch_count, lib  # noqa: F401
+from .rnnt import rnnt_grad_coef, rnnt_lattice, rnnt_loss  # noqa: F401
+
+__all__ = ["rnnt_loss", "rnnt_lattice", "rnnt_grad_coef", "B200Error", "lib", "launch_count"]

@@ -74,7 +74,8 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
             print(out)
         stamp.write_text(want)
     if relink:
-        cmd = [nvcc, "-shared", "-o", str(LIB), *map(str, objs), "-lcudart", "-lcuda"]
+        cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", str(LIB),
+               *map(str, objs), "-lcudart", "-lcuda"]
         r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}")
