@@ -47,7 +47,7 @@ inline void count_launch(int n = 1) { g_launches.fetch_add((uint64_t)n, std::mem
 // ---- device helpers -------------------------------------------------------
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
-constexpr float kNegBig = -3.0e38f;  // finite stand-in for -inf in running maxima
+constexpr float kNegBig = -1.0e30f;  // finite stand-in for -inf in running maxima (x log2e must not overflow)
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
