@@ -94,6 +94,37 @@ int b200_rnnt_loss_fwd(const void* logits, int dtype, const int32_t* targets,
                        float* costs, float* lse, float* lp_blank, float* lp_emit,
                        float* alpha, float* beta, b200_stream_t stream);
 
+/* ---- CTC loss over logits ----------------------------------------------
+ * replaces, behind CTC.forward (wenet/transformer/ctc.py:46-64), the
+ * log_softmax (ctc.py:60) + torch.nn.CTCLoss(reduction='sum') (ctc.py:44,61) pair.
+ * logits [B,T,V] contiguous, batch-major (the module's own layout: no [T,B,V] copy),
+ * dtype f32/f16/bf16.  ys_pad [B,Lmax] int64 padded with -1 (as the reference passes
+ * it), hlens / ys_lens [B] int32.  Smax = 2*Lmax+1 (<= 1024).
+ * lse [B,T]; lp_ext, alpha, beta [B,T,Smax] f32; nll [B] f32; leader [B,Smax] int32.
+ */
+
+/* pass 1: lse per frame + log-probs of the blank-interleaved label sequence */
+int b200_ctc_logprobs(const void* logits, int dtype, const int64_t* ys_pad,
+                      const int32_t* hlens, const int32_t* ys_lens,
+                      int B, int T, int V, int Lmax, int blank,
+                      float* lse, float* lp_ext, b200_stream_t stream);
+
+/* pass 2: alpha / beta trellis over T, nll[b] (inf when no alignment exists:
+ * zero_infinity=False), and the duplicate-label leader table used by pass 3 */
+int b200_ctc_lattice(const float* lp_ext, const int64_t* ys_pad,
+                     const int32_t* hlens, const int32_t* ys_lens,
+                     int B, int T, int Lmax, int blank,
+                     float* alpha, float* beta, float* nll, int32_t* leader,
+                     b200_stream_t stream);
+
+/* pass 3: grad[b,t,c] = scale[b] * (softmax[t,c] - posterior of class c at t), 0 for t >= hlens[b] */
+int b200_ctc_grad(const void* logits, int dtype, const float* lse, const float* lp_ext,
+                  const float* alpha, const float* beta, const float* nll,
+                  const float* scale, const int64_t* ys_pad,
+                  const int32_t* hlens, const int32_t* ys_lens, const int32_t* leader,
+                  int B, int T, int V, int Lmax, int blank,
+                  void* grad, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -3,10 +3,13 @@
 Public surface mirrors the reference call sites (Vindicator645/wenet-celoss):
   rnnt_loss(logits, targets, logit_lengths, target_lengths, blank, clamp, reduction)
       torchaudio.functional.rnnt_loss as used at wenet/transducer/transducer.py:142
+  CTC(odim, encoder_output_size).forward(hs_pad, hlens, ys_pad, ys_lens)
+      wenet/transformer/ctc.py:46
 Everything is backed by libb200_transducer.so (C ABI in include/b200_transducer.h);
 there is no CPU or PyTorch fallback.
 """
 from ._lib import B200Error, launch_count, lib  # noqa: F401
+from .ctc import CTC, ctc_loss, patch_ctc  # noqa: F401
 from .rnnt import rnnt_grad_coef, rnnt_lattice, rnnt_loss  # noqa: F401
 
-__all__ = ["rnnt_loss", "rnnt_lattice", "rnnt_grad_coef", "B200Error", "lib", "launch_count"]
+__all__ = ["CTC", "ctc_loss", "patch_ctc", "rnnt_loss", "rnnt_lattice", "rnnt_grad_coef", "B200Error", "lib", "launch_count"]

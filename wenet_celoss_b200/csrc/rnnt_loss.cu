@@ -14,11 +14,10 @@
 // Roofline: pass 1 reads N*s bytes, pass 3 reads N*s and writes N*s (N = B*T*U1*V,
 // s = sizeof(logit)) -> HBM-bound; the lattice pass is a T+U-1 step dependency chain.
 #include "common.cuh"
+#include "row_ops.cuh"
 
 namespace b200 {
 
-constexpr int kRowWarps = 8;  // warps (= lattice cells) per CTA in the streaming passes
-constexpr int kUnroll = 4;    // 16-byte loads in flight per lane
 
 // ---------------------------------------------------------------------------
 // pass 1: one warp per lattice cell; online (max, sum-exp) over the V logits.
@@ -29,7 +28,6 @@ rnnt_logprobs_kernel(const T* __restrict__ logits, const int32_t* __restrict__ t
                      const int32_t* __restrict__ logit_len, const int32_t* __restrict__ target_len,
                      int B, int Tm, int U1, int V, int blank, float* __restrict__ lse,
                      float* __restrict__ lp_blank, float* __restrict__ lp_emit) {
-  constexpr int K = Elem<T>::kPerVec;
   const long long cells = (long long)B * Tm * U1;
   const long long cell = (long long)blockIdx.x * kRowWarps + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
@@ -41,50 +39,7 @@ rnnt_logprobs_kernel(const T* __restrict__ logits, const int32_t* __restrict__ t
   if (t >= Tb || u > Ub) return;  // padded cell: never read
 
   const T* row = logits + cell * V;
-  RowSegs<T> rs(row, V);
-  float m = kNegBig, s = 0.f;
-  for (int base = 0; base < rs.nseg; base += 32 * kUnroll) {
-    uint4 v[kUnroll];
-#pragma unroll
-    for (int j = 0; j < kUnroll; ++j) {
-      int idx = base + j * 32 + lane;
-      if (idx < rs.nseg) v[j] = ldg_stream16(rs.seg0 + idx);
-    }
-    float f[kUnroll][K];
-    float lmax = kNegBig;
-#pragma unroll
-    for (int j = 0; j < kUnroll; ++j) {
-      int idx = base + j * 32 + lane;
-      if (idx < rs.nseg) {
-        Elem<T>::unpack(v[j], f[j]);
-        if (idx == 0 || idx == rs.nseg - 1) {  // edge segments may hold neighbours' elements
-#pragma unroll
-          for (int k = 0; k < K; ++k) {
-            int e = idx * K - rs.head + k;
-            if (e < 0 || e >= V) f[j][k] = -INFINITY;
-          }
-        }
-      } else {
-#pragma unroll
-        for (int k = 0; k < K; ++k) f[j][k] = -INFINITY;
-      }
-#pragma unroll
-      for (int k = 0; k < K; ++k) lmax = fmaxf(lmax, f[j][k]);
-    }
-    float mn = fmaxf(m, lmax);
-    float mn2 = mn * kLog2e;
-    float acc = 0.f;
-#pragma unroll
-    for (int j = 0; j < kUnroll; ++j)
-#pragma unroll
-      for (int k = 0; k < K; ++k) acc += ex2_approx(fmaf(f[j][k], kLog2e, -mn2));
-    s = s * ex2_approx((m - mn) * kLog2e) + acc;
-    m = mn;
-  }
-  float M = warp_max(m);
-  s *= ex2_approx((m - M) * kLog2e);
-  float S = warp_sum(s);
-  float l = M + logf(S);
+  const float l = warp_row_lse<T>(row, V, lane);
   if (lane == 0) {
     lse[cell] = l;
     lp_blank[cell] = Elem<T>::to_float(row[blank]) - l;
@@ -289,7 +244,6 @@ __global__ void __launch_bounds__(kRowWarps * 32)
 rnnt_grad_kernel(const T* __restrict__ logits, const int32_t* __restrict__ targets,
                  const float4* __restrict__ coef, int B, int Tm, int U1, int V, int blank,
                  float clamp, T* __restrict__ grad) {
-  constexpr int K = Elem<T>::kPerVec;
   const long long cells = (long long)B * Tm * U1;
   const long long cell = (long long)blockIdx.x * kRowWarps + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
@@ -297,49 +251,11 @@ rnnt_grad_kernel(const T* __restrict__ logits, const int32_t* __restrict__ targe
   const float4 c = coef[cell];
   const T* row = logits + cell * V;
   T* grow = grad + cell * V;
-  RowSegs<T> rs(row, V);
   // grad has the same element offset as logits -> same 16-byte phase when the two
   // base pointers share alignment (checked on the host).
-  uint4* gseg0 = reinterpret_cast<uint4*>(reinterpret_cast<uintptr_t>(grow) & ~uintptr_t(15));
   const bool dead = (c.x == -INFINITY) || (c.w == 0.f);
-  const float c0 = c.x * kLog2e;
   const float scale = c.w;
-
-  for (int base = 0; base < rs.nseg; base += 32 * kUnroll) {
-    uint4 v[kUnroll];
-    if (!dead) {
-#pragma unroll
-      for (int j = 0; j < kUnroll; ++j) {
-        int idx = base + j * 32 + lane;
-        if (idx < rs.nseg) v[j] = ldg_stream16(rs.seg0 + idx);
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < kUnroll; ++j) {
-      int idx = base + j * 32 + lane;
-      if (idx >= rs.nseg) continue;
-      float f[K];
-      if (!dead) {
-        Elem<T>::unpack(v[j], f);
-#pragma unroll
-        for (int k = 0; k < K; ++k)
-          f[k] = clampf(scale * ex2_approx(fmaf(f[k], kLog2e, c0)), clamp);
-      } else {
-#pragma unroll
-        for (int k = 0; k < K; ++k) f[k] = 0.f;
-      }
-      const int e0 = idx * K - rs.head;
-      if (e0 >= 0 && e0 + K <= V) {
-        stg_stream16(gseg0 + idx, Elem<T>::pack(f));
-      } else {  // edge segment shared with a neighbouring row: element stores only
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-          int e = e0 + k;
-          if (e >= 0 && e < V) grow[e] = Elem<T>::from_float(f[k]);
-        }
-      }
-    }
-  }
+  warp_row_softmax_store<T>(row, grow, V, lane, dead, c.x * kLog2e, scale, clamp);
   if (dead) return;
   __syncwarp();  // order the streaming stores before the two fix-ups below
   if (lane == 0) {

@@ -102,7 +102,8 @@ class _RnntLossFn(torch.autograd.Function):
         ctx.save_for_backward(logits, targets, logit_lengths, target_lengths, lse, alpha, beta, costs)
         ctx.blank = blank
         ctx.clamp = clamp
-        return costs.to(logits.dtype)
+        # torchaudio returns costs in the logits dtype (f32/f16); bf16 (extension) stays f32
+        return costs.to(torch.float16) if logits.dtype == torch.float16 else costs
 
     @staticmethod
     def backward(ctx, dy):
