@@ -157,6 +157,7 @@ class RnntLogitsWorkload:
         lse, lpb, lpe, alpha, beta = lat.unbind(0)
         costs = torch.empty(B, dtype=torch.float32, device=self.dev)
         dy = torch.full((B,), 1.0 / B, dtype=torch.float32, device=self.dev)
+        doff = torch.empty(B, 2, T + U1, dtype=torch.float64, device=self.dev)
         grad = torch.empty_like(x)
         st = _lib.stream_handle(self.dev)
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)
@@ -169,10 +170,10 @@ class RnntLogitsWorkload:
 
         def k_lattice():
             _lib.call("b200_rnnt_lattice", ptr(lpb), ptr(lpe), ptr(self.tl), ptr(self.ul), i32(B),
-                      i32(T), i32(U1), ptr(alpha), ptr(beta), ptr(costs), st)
+                      i32(T), i32(U1), ptr(alpha), ptr(beta), ptr(costs), ptr(doff), st)
 
         def k_coef():
-            coef_box["c"] = rnnt_grad_coef(lse, alpha, beta, costs, dy, self.targets, self.tl,
+            coef_box["c"] = rnnt_grad_coef(lse, alpha, beta, doff, dy, self.targets, self.tl,
                                            self.ul, 0)
 
         def k_grad():

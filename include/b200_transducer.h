@@ -64,18 +64,21 @@ int b200_rnnt_logprobs(const void* logits, int dtype, const int32_t* targets,
                        float* lse, float* lp_blank, float* lp_emit,
                        b200_stream_t stream);
 
-/* pass 2: alpha / beta lattices by anti-diagonal wavefront; costs[b] = -beta[b,0,0] */
+/* pass 2: alpha / beta lattices by anti-diagonal wavefront; costs[b] = -beta[b,0,0].
+ * alpha/beta are stored RESCALED: true alpha[b,t,u] = alpha[b,t,u] + diag_off[b][0][t+u]
+ * (beta: diag_off[b][1][t+u]); diag_off is [B][2][T+U1] fp64 and slot
+ * diag_off[b][0][T+U1-1] holds the log-likelihood of utterance b in fp64. */
 int b200_rnnt_lattice(const float* lp_blank, const float* lp_emit,
                       const int32_t* logit_len, const int32_t* target_len,
                       int B, int T, int U1,
-                      float* alpha, float* beta, float* costs,
+                      float* alpha, float* beta, float* costs, double* diag_off,
                       b200_stream_t stream);
 
 /* pass 2b: per-cell gradient coefficients {c0, cb, ce, scale} (float4 per cell):
  *   grad[v] = scale * ( exp(x[v]+c0) - [v==blank] exp(x[v]+cb) - [v==y_u] exp(x[v]+ce) )
  * with scale = dy[b]; padded cells get c0=cb=ce=-inf (gradient exactly 0). */
 int b200_rnnt_grad_coef(const float* lse, const float* alpha, const float* beta,
-                        const float* costs, const float* dy,
+                        const double* diag_off, const float* dy,
                         const int32_t* targets,
                         const int32_t* logit_len, const int32_t* target_len,
                         int B, int T, int U1, int blank,
@@ -92,7 +95,7 @@ int b200_rnnt_loss_fwd(const void* logits, int dtype, const int32_t* targets,
                        const int32_t* logit_len, const int32_t* target_len,
                        int B, int T, int U1, int V, int blank,
                        float* costs, float* lse, float* lp_blank, float* lp_emit,
-                       float* alpha, float* beta, b200_stream_t stream);
+                       float* alpha, float* beta, double* diag_off, b200_stream_t stream);
 
 /* ---- CTC loss over logits ----------------------------------------------
  * replaces, behind CTC.forward (wenet/transformer/ctc.py:46-64), the
@@ -110,16 +113,18 @@ int b200_ctc_logprobs(const void* logits, int dtype, const int64_t* ys_pad,
                       float* lse, float* lp_ext, b200_stream_t stream);
 
 /* pass 2: alpha / beta trellis over T, nll[b] (inf when no alignment exists:
- * zero_infinity=False), and the duplicate-label leader table used by pass 3 */
+ * zero_infinity=False), and the duplicate-label leader table used by pass 3.
+ * alpha/beta are stored RESCALED: true alpha_t(s) = alpha[b,t,s] + frame_off[b][0][t]
+ * (beta: frame_off[b][1][t]); frame_off is [B][2][T+1] fp64, frame_off[b][0][T] = log-likelihood. */
 int b200_ctc_lattice(const float* lp_ext, const int64_t* ys_pad,
                      const int32_t* hlens, const int32_t* ys_lens,
                      int B, int T, int Lmax, int blank,
                      float* alpha, float* beta, float* nll, int32_t* leader,
-                     b200_stream_t stream);
+                     double* frame_off, b200_stream_t stream);
 
 /* pass 3: grad[b,t,c] = scale[b] * (softmax[t,c] - posterior of class c at t), 0 for t >= hlens[b] */
 int b200_ctc_grad(const void* logits, int dtype, const float* lse, const float* lp_ext,
-                  const float* alpha, const float* beta, const float* nll,
+                  const float* alpha, const float* beta, const double* frame_off,
                   const float* scale, const int64_t* ys_pad,
                   const int32_t* hlens, const int32_t* ys_lens, const int32_t* leader,
                   int B, int T, int V, int Lmax, int blank,

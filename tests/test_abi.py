@@ -41,7 +41,7 @@ def test_argument_errors_do_not_need_a_gpu():
     from wenet_celoss_b200 import _lib
     L = _lib.lib()
     L.b200_rnnt_lattice.restype = ctypes.c_int
-    rc = L.b200_rnnt_lattice(None, None, None, None, 1, 1, 1, None, None, None, None)
+    rc = L.b200_rnnt_lattice(None, None, None, None, 1, 1, 1, None, None, None, None, None)
     assert rc == 1
     assert b"null pointer" in L.b200_last_error()
 

@@ -82,12 +82,12 @@ def test_fp32_vs_aten_and_c_oracle(shape):
         n64[b], g64[b] = n1[0], g1[0]
     np.testing.assert_allclose(nll, ref.detach().numpy(), rtol=1e-4)
     np.testing.assert_allclose(nll, n64, rtol=1e-4)
-    floor = np.abs(ta - g64).max()
-    assert np.abs(grad - g64).max() <= max(2.0 * floor, 2e-6)
-    np.testing.assert_allclose(grad, ta, rtol=1e-4, atol=1e-6 + 4.0 * floor)
+    # per-frame rescaled trellis (fp64 offsets): tracks the fp64 oracle directly
+    np.testing.assert_allclose(grad, g64, rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(grad, ta, rtol=1e-4, atol=2e-6)
     for b in range(B):
         assert np.all(grad[b, hl[b]:] == 0)
-    assert np.abs(grad.sum(-1)).max() < 1e-4
+    assert np.abs(grad.sum(-1)).max() < 1e-5  # sum_c grad = scale*(1 - sum_s posterior)
 
 
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
@@ -143,11 +143,11 @@ def test_properties_at_full_size():
     (nll.sum() / B).backward()
     grad = logits.grad
     assert torch.all(torch.isfinite(nll)) and torch.all(nll > 0)
-    assert grad.sum(-1).abs().max() < 1e-5
+    assert grad.sum(-1).abs().max() < 1e-5  # (1 - sum_s posterior)/B
     for b in (0, 17, 63):
         assert torch.count_nonzero(grad[b, int(hl[b]):]) == 0
     b = 17
     n64, g64 = ctc_loss_c(logits.detach()[b:b + 1].cpu(), ys[b:b + 1].cpu(), hl[b:b + 1].cpu(),
                           yl[b:b + 1].cpu(), blank=0, scale=1.0 / B)
     np.testing.assert_allclose(nll[b].item(), n64[0], rtol=1e-4)
-    np.testing.assert_allclose(grad[b].cpu().numpy(), g64[0], rtol=1e-3, atol=1e-6)
+    np.testing.assert_allclose(grad[b].cpu().numpy(), g64[0], rtol=1e-4, atol=1e-6)

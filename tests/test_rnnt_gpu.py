@@ -83,13 +83,12 @@ def test_fp32_vs_torchaudio_and_c_oracle(shape, ragged):
     c64, g64, _, _ = rnnt_loss_c(logits, targets, tl, ul, blank=0, dy=dy.double().numpy())
     np.testing.assert_allclose(costs, ref.detach().numpy(), rtol=1e-4)
     np.testing.assert_allclose(costs, c64, rtol=1e-4)
-    # fp32 log-space noise floor: alpha+beta+cost cancel at magnitude ~cost, so torchaudio's
-    # own gradient sits ~cost*2^-23 (relative) from the fp64 answer.  We ask to be as close
-    # to fp64 as torchaudio is (x2), and within rtol 1e-4 of torchaudio above that floor.
+    # Our lattice is rescaled per anti-diagonal (fp64 offsets), so it tracks the fp64 oracle
+    # to rtol 1e-4 / atol 1e-6.  torchaudio's fp32 log-space carries a cost*2^-23 noise
+    # floor (alpha+beta+cost cancel at magnitude ~cost); allow for ITS distance to fp64.
+    np.testing.assert_allclose(grad, g64, rtol=1e-4, atol=1e-6)
     floor = np.abs(ta - g64).max()
-    assert np.abs(grad - g64).max() <= max(2.0 * floor, 1e-6)
-    np.testing.assert_allclose(grad, ta, rtol=1e-4, atol=1e-6 + 4.0 * floor)
-    np.testing.assert_allclose(grad, g64, rtol=1e-4, atol=1e-6 + 4.0 * floor)
+    np.testing.assert_allclose(grad, ta, rtol=1e-4, atol=1e-6 + 2.0 * floor)
     for b in range(B):  # padded cells: exactly zero
         assert np.all(grad[b, tl[b]:] == 0) and np.all(grad[b, :, ul[b] + 1:] == 0)
 

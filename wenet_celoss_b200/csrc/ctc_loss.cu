@@ -13,7 +13,9 @@
 //
 // HBM layout: logits/grad [B,T,V] in the module's natural batch-major layout (no [T,B,V]
 // transpose copy); lse [B,T]; lp_ext / alpha / beta [B,T,Smax] f32 with Smax = 2*Lmax+1;
-// leader [B,Smax] int32 (first state carrying the same label, for duplicate labels).
+// leader [B,Smax] int32 (first state carrying the same label, for duplicate labels);
+// frame_off [B][2][T+1] fp64: alpha/beta are stored rescaled, alpha_t(s) = alpha_hat + off[b][0][t],
+// beta likewise with off[b][1][t]; off[b][0][T] = log-likelihood (fp64).
 // Roofline: passes 1 and 3 stream 3*B*T*V*s bytes (HBM-bound); the trellis is a T-step chain.
 #include "common.cuh"
 #include "row_ops.cuh"
@@ -62,6 +64,18 @@ ctc_logprobs_kernel(const T* __restrict__ logits, const long long* __restrict__ 
 // One thread per extended state; previous frame in shared memory (ping-pong).
 // ---------------------------------------------------------------------------
 constexpr int kCtcPf = 4;
+constexpr int kCtcRenorm = 8;
+
+// block-wide max (one __syncthreads inside); red = 32 floats of shared scratch
+__device__ __forceinline__ float block_max_ctc(float v, float* red) {
+  v = warp_max(v);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  const int nw = (blockDim.x + 31) >> 5;
+  float m = red[0];
+  for (int i = 1; i < nw; ++i) m = fmaxf(m, red[i]);
+  return m;
+}
 
 __device__ __forceinline__ float lae3(float a, float b, float c) {
   float m = fmaxf(a, fmaxf(b, c));
@@ -74,8 +88,9 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
                                    const int32_t* __restrict__ hlens,
                                    const int32_t* __restrict__ ys_lens, int Tm, int Lmax, int blank,
                                    float* __restrict__ alpha, float* __restrict__ beta,
-                                   float* __restrict__ nll, int32_t* __restrict__ leader) {
-  extern __shared__ float sm[];  // [2][Smax+4] floats, then [Smax] ints
+                                   float* __restrict__ nll, int32_t* __restrict__ leader,
+                                   double* __restrict__ frame_off) {
+  extern __shared__ float sm[];  // [2][Smax+4] floats, [32] reduction scratch, then [Smax] ints
   const int b = blockIdx.x;
   const int s = threadIdx.x;
   const int Smax = 2 * Lmax + 1;
@@ -84,7 +99,10 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
   const int stride = Smax + 4;
   float* buf0 = sm + 2;  // indices -2 .. Smax+1 addressable
   float* buf1 = sm + stride + 2;
-  int* lab = reinterpret_cast<int*>(sm + 2 * stride);
+  float* red = sm + 2 * stride;
+  int* lab = reinterpret_cast<int*>(sm + 2 * stride + 32);
+  double* offs = frame_off + ((long long)b * 2 + blockIdx.y) * (Tm + 1);
+  double run = 0.0;  // running offset: alpha_t(s) = alpha_hat_t(s) + off_a[t] (same for beta)
   const long long* ys = ys_pad + (long long)b * Lmax;
   for (int i = s; i < 2 * stride; i += blockDim.x) sm[i] = -INFINITY;
   for (int i = s; i < Smax; i += blockDim.x) lab[i] = (i < S) ? ext_label(ys, i, blank) : -1;
@@ -110,7 +128,10 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
       leader[(long long)b * Smax + s] = ld;
     }
     if (Tb <= 0) {
-      if (s == 0) nll[b] = (L == 0) ? 0.f : INFINITY;
+      if (s == 0) {
+        nll[b] = (L == 0) ? 0.f : INFINITY;
+        offs[Tm] = (L == 0) ? 0.0 : (double)-INFINITY;
+      }
       return;
     }
     float* al = alpha + off;
@@ -122,6 +143,7 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
       prev[s] = v;
       al[s] = v;
     }
+    if (s == 0) offs[0] = 0.0;
     __syncthreads();
     float r[kCtcPf];
 #pragma unroll
@@ -137,11 +159,20 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
       for (int k = 0; k < kCtcPf; ++k) {
         int t = t0 + k;
         if (t < Tb) {  // block-uniform
+          float v = -INFINITY;
+          if (mine) v = lae3(prev[s], prev[s - 1], skip_ok ? prev[s - 2] : -INFINITY) + r[k];
+          if (t % kCtcRenorm == 0) {  // block-uniform: pull the frame maximum into the fp64 offset
+            float M = block_max_ctc(v, red);
+            if (M != -INFINITY) {
+              v -= M;
+              run += (double)M;
+            }
+          }
           if (mine) {
-            float v = lae3(prev[s], prev[s - 1], skip_ok ? prev[s - 2] : -INFINITY) + r[k];
             cur[s] = v;
             al[(long long)t * Smax + s] = v;
           }
+          if (s == 0) offs[t] = run;
           __syncthreads();
           float* tmp = prev;
           prev = cur;
@@ -151,7 +182,11 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
 #pragma unroll
       for (int k = 0; k < kCtcPf; ++k) r[k] = nr[k];
     }
-    if (s == 0) nll[b] = -log_add_exp(prev[S - 1], S > 1 ? prev[S - 2] : -INFINITY);
+    if (s == 0) {
+      double ll = (double)log_add_exp(prev[S - 1], S > 1 ? prev[S - 2] : -INFINITY) + run;
+      nll[b] = (float)(-ll);
+      offs[Tm] = ll;  // [b][0][T] = log-likelihood in fp64
+    }
   } else {
     if (Tb <= 0) return;
     float* be = beta + off;
@@ -163,6 +198,7 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
       prev[s] = v;
       be[(long long)(Tb - 1) * Smax + s] = v;
     }
+    if (s == 0) offs[Tb - 1] = 0.0;
     __syncthreads();
     float r[kCtcPf];
 #pragma unroll
@@ -181,11 +217,20 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
       for (int k = 0; k < kCtcPf; ++k) {
         int t = t0 - k;
         if (t >= 0) {  // block-uniform
+          float v = -INFINITY;
+          if (mine) v = lae3(prev[s], prev[s + 1], skip_ok ? prev[s + 2] : -INFINITY) + r[k];
+          if (t % kCtcRenorm == 0) {  // block-uniform
+            float M = block_max_ctc(v, red);
+            if (M != -INFINITY) {
+              v -= M;
+              run += (double)M;
+            }
+          }
           if (mine) {
-            float v = lae3(prev[s], prev[s + 1], skip_ok ? prev[s + 2] : -INFINITY) + r[k];
             cur[s] = v;
             be[(long long)t * Smax + s] = v;
           }
+          if (s == 0) offs[t] = run;
           __syncthreads();
           float* tmp = prev;
           prev = cur;
@@ -206,7 +251,7 @@ template <typename T>
 __global__ void __launch_bounds__(kRowWarps * 32)
 ctc_grad_kernel(const T* __restrict__ logits, const float* __restrict__ lse,
                 const float* __restrict__ lp_ext, const float* __restrict__ alpha,
-                const float* __restrict__ beta, const float* __restrict__ nll,
+                const float* __restrict__ beta, const double* __restrict__ frame_off,
                 const float* __restrict__ scale, const long long* __restrict__ ys_pad,
                 const int32_t* __restrict__ hlens, const int32_t* __restrict__ ys_lens,
                 const int32_t* __restrict__ leader, int B, int Tm, int V, int Lmax, int blank,
@@ -229,7 +274,10 @@ ctc_grad_kernel(const T* __restrict__ logits, const float* __restrict__ lse,
   }
   const int S = 2 * ys_lens[b] + 1;
   const float l = lse[rowi];
-  const float nl = nll[b];
+  // alpha_hat + beta_hat + (off_a[t] + off_b[t] - ll): the bracket is O(1) because
+  // sum_s alpha_t(s) beta_t(s) / y_t(l'_s) = exp(ll) for every t
+  const double* oa = frame_off + (long long)b * 2 * (Tm + 1);
+  const float nl = (float)(oa[t] + oa[Tm + 1 + t] - oa[Tm]);
   const float* al = alpha + rowi * Smax;
   const float* be = beta + rowi * Smax;
   const float* lp = lp_ext + rowi * Smax;
@@ -312,28 +360,28 @@ extern "C" int b200_ctc_logprobs(const void* logits, int dtype, const int64_t* y
 extern "C" int b200_ctc_lattice(const float* lp_ext, const int64_t* ys_pad, const int32_t* hlens,
                                 const int32_t* ys_lens, int B, int T, int Lmax, int blank,
                                 float* alpha, float* beta, float* nll, int32_t* leader,
-                                b200_stream_t stream) {
+                                double* frame_off, b200_stream_t stream) {
   if (int rc = ctc_check("b200_ctc_lattice", B, T, blank + 1, Lmax, blank)) return rc;
-  B200_CHECK_ARG(lp_ext && hlens && ys_lens && alpha && beta && nll && leader &&
+  B200_CHECK_ARG(lp_ext && hlens && ys_lens && alpha && beta && nll && leader && frame_off &&
                      (Lmax == 0 || ys_pad),
                  "b200_ctc_lattice: null pointer");
   const int Smax = 2 * Lmax + 1;
   const int threads = ((Smax + 31) / 32) * 32;
-  const size_t smem = (2 * (size_t)(Smax + 4)) * sizeof(float) + (size_t)Smax * sizeof(int);
+  const size_t smem = (2 * (size_t)(Smax + 4) + 32) * sizeof(float) + (size_t)Smax * sizeof(int);
   ctc_lattice_kernel<<<dim3(B, 2), threads, smem, (cudaStream_t)stream>>>(
       lp_ext, reinterpret_cast<const long long*>(ys_pad), hlens, ys_lens, T, Lmax, blank, alpha,
-      beta, nll, leader);
+      beta, nll, leader, frame_off);
   B200_CHECK_LAUNCH("ctc_lattice_kernel");
   return B200_OK;
 }
 
 extern "C" int b200_ctc_grad(const void* logits, int dtype, const float* lse, const float* lp_ext,
-                             const float* alpha, const float* beta, const float* nll,
+                             const float* alpha, const float* beta, const double* frame_off,
                              const float* scale, const int64_t* ys_pad, const int32_t* hlens,
                              const int32_t* ys_lens, const int32_t* leader, int B, int T, int V,
                              int Lmax, int blank, void* grad, b200_stream_t stream) {
   if (int rc = ctc_check("b200_ctc_grad", B, T, V, Lmax, blank)) return rc;
-  B200_CHECK_ARG(logits && lse && lp_ext && alpha && beta && nll && scale && hlens && ys_lens &&
+  B200_CHECK_ARG(logits && lse && lp_ext && alpha && beta && frame_off && scale && hlens && ys_lens &&
                      leader && grad && (Lmax == 0 || ys_pad),
                  "b200_ctc_grad: null pointer");
   B200_CHECK_ARG(((reinterpret_cast<uintptr_t>(logits) ^ reinterpret_cast<uintptr_t>(grad)) & 15) == 0,
@@ -347,17 +395,17 @@ extern "C" int b200_ctc_grad(const void* logits, int dtype, const float* lse, co
   switch (dtype) {
     case B200_F32:
       ctc_grad_kernel<float><<<grid, kRowWarps * 32, smem, st>>>(
-          (const float*)logits, lse, lp_ext, alpha, beta, nll, scale, ys, hlens, ys_lens, leader, B,
+          (const float*)logits, lse, lp_ext, alpha, beta, frame_off, scale, ys, hlens, ys_lens, leader, B,
           T, V, Lmax, blank, (float*)grad);
       break;
     case B200_F16:
       ctc_grad_kernel<__half><<<grid, kRowWarps * 32, smem, st>>>(
-          (const __half*)logits, lse, lp_ext, alpha, beta, nll, scale, ys, hlens, ys_lens, leader, B,
+          (const __half*)logits, lse, lp_ext, alpha, beta, frame_off, scale, ys, hlens, ys_lens, leader, B,
           T, V, Lmax, blank, (__half*)grad);
       break;
     case B200_BF16:
       ctc_grad_kernel<__nv_bfloat16><<<grid, kRowWarps * 32, smem, st>>>(
-          (const __nv_bfloat16*)logits, lse, lp_ext, alpha, beta, nll, scale, ys, hlens, ys_lens,
+          (const __nv_bfloat16*)logits, lse, lp_ext, alpha, beta, frame_off, scale, ys, hlens, ys_lens,
           leader, B, T, V, Lmax, blank, (__nv_bfloat16*)grad);
       break;
     default:

@@ -55,16 +55,38 @@ rnnt_logprobs_kernel(const T* __restrict__ logits, const int32_t* __restrict__ t
 // pass 2: anti-diagonal wavefront.  grid (B, 2): y==0 alpha, y==1 beta.
 // One thread per u; the previous diagonal lives in shared memory (ping-pong),
 // one __syncthreads per diagonal; log-prob loads run kPf diagonals ahead.
+//
+// Rescaling: every path crosses each anti-diagonal exactly once, so a per-diagonal
+// offset can be pulled out of alpha and beta without changing any posterior.  Every
+// kRenorm diagonals the block subtracts the diagonal's maximum and adds it to a
+// running fp64 offset:  alpha(t,u) = alpha_hat(t,u) + off_a[t+u]  (same for beta).
+// The stored fp32 values stay O(10) in magnitude, which removes the cost-sized
+// cancellation alpha+beta-cost that limits plain fp32 log-space to ~cost*2^-23.
+// diag_off layout: [B][2][T+U1] fp64; [b][0][d] alpha offsets, [b][1][d] beta offsets,
+// [b][0][T+U1-1] = log-likelihood of utterance b.
 // ---------------------------------------------------------------------------
 constexpr int kPf = 4;
+constexpr int kRenorm = 8;
+
+// max over the block of v (threads that do not take part pass -inf); all threads return it.
+// Contains one __syncthreads; `red` needs 32 floats.
+__device__ __forceinline__ float block_max(float v, float* red) {
+  v = warp_max(v);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  const int nw = (blockDim.x + 31) >> 5;
+  float m = red[0];
+  for (int i = 1; i < nw; ++i) m = fmaxf(m, red[i]);
+  return m;
+}
 
 __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
                                     const float* __restrict__ lp_emit,
                                     const int32_t* __restrict__ logit_len,
                                     const int32_t* __restrict__ target_len, int Tm, int U1,
                                     float* __restrict__ alpha, float* __restrict__ beta,
-                                    float* __restrict__ costs) {
-  extern __shared__ float diag[];  // [2][U1 + 2]
+                                    float* __restrict__ costs, double* __restrict__ diag_off) {
+  extern __shared__ float diag[];  // [2][U1 + 2] + 32 (reduction scratch)
   const int b = blockIdx.x;
   const int u = threadIdx.x;
   const int Tb = logit_len[b], Ub = target_len[b];
@@ -72,10 +94,16 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
   const float* lpb = lp_blank + off;
   const float* lpe = lp_emit + off;
   const int stride = U1 + 2;
+  const int nd = Tm + U1;  // slots per offset row
   float* buf0 = diag + 1;  // index -1 .. U1 addressable
   float* buf1 = diag + stride + 1;
+  float* red = diag + 2 * stride;
+  double* offs = diag_off + ((long long)b * 2 + blockIdx.y) * nd;
   if (Tb <= 0 || Ub < 0 || Ub >= U1 || Tb > Tm) {
-    if (u == 0 && blockIdx.y == 1) costs[b] = 0.f;
+    if (u == 0 && blockIdx.y == 1) {
+      costs[b] = 0.f;
+      diag_off[(long long)b * 2 * nd + nd - 1] = 0.0;
+    }
     return;
   }
   const int D = Tb + Ub;  // number of anti-diagonals (d = 0 .. D-1)
@@ -85,6 +113,7 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
   }
   __syncthreads();
   const bool mine = (u <= Ub);
+  double run = 0.0;  // running offset, tracked identically by every thread
 
   if (blockIdx.y == 0) {
     // ---------------- alpha: d ascending ----------------
@@ -92,6 +121,7 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
     if (u == 0) {
       buf0[0] = 0.f;
       al[0] = 0.f;
+      offs[0] = 0.0;
     }
     __syncthreads();
     float* prev = buf0;
@@ -117,14 +147,19 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
         int d = d0 + k;
         if (d < D) {  // block-uniform
           int t = d - u;
-          if (mine) {
-            float v = -INFINITY;
-            if (t >= 0 && t < Tb) {
-              v = log_add_exp(prev[u] + rb[k], prev[u - 1] + re[k]);
-              al[(long long)t * U1 + u] = v;
+          const bool live = mine && t >= 0 && t < Tb;
+          float v = -INFINITY;
+          if (live) v = log_add_exp(prev[u] + rb[k], prev[u - 1] + re[k]);
+          if (d % kRenorm == 0) {  // block-uniform
+            float M = block_max(v, red);
+            if (M != -INFINITY) {
+              v -= M;
+              run += (double)M;
             }
-            cur[u] = v;
           }
+          if (mine) cur[u] = v;
+          if (live) al[(long long)t * U1 + u] = v;
+          if (u == 0) offs[d] = run;
           __syncthreads();
           float* tmp = prev;
           prev = cur;
@@ -146,7 +181,11 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
       float v = lpb[(long long)(Tb - 1) * U1 + Ub];
       buf0[Ub] = v;
       be[(long long)(Tb - 1) * U1 + Ub] = v;
-      if (D == 1) costs[b] = -v;
+      offs[D - 1] = 0.0;
+      if (D == 1) {
+        costs[b] = -v;
+        diag_off[(long long)b * 2 * nd + nd - 1] = (double)v;
+      }
     }
     __syncthreads();
     float rb[kPf], re[kPf];
@@ -170,15 +209,26 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
         int d = d0 - k;
         if (d >= 0) {  // block-uniform
           int t = d - u;
-          if (mine) {
-            float v = -INFINITY;
-            if (t >= 0 && t < Tb) {
-              v = log_add_exp(prev[u] + rb[k], prev[u + 1] + re[k]);
-              be[(long long)t * U1 + u] = v;
-              if (d == 0) costs[b] = -v;
+          const bool live = mine && t >= 0 && t < Tb;
+          float v = -INFINITY;
+          if (live) v = log_add_exp(prev[u] + rb[k], prev[u + 1] + re[k]);
+          if (d % kRenorm == 0 && d != 0) {  // block-uniform
+            float M = block_max(v, red);
+            if (M != -INFINITY) {
+              v -= M;
+              run += (double)M;
             }
-            cur[u] = v;
           }
+          if (mine) cur[u] = v;
+          if (live) {
+            be[(long long)t * U1 + u] = v;
+            if (d == 0) {
+              double ll = (double)v + run;
+              costs[b] = (float)(-ll);
+              diag_off[(long long)b * 2 * nd + nd - 1] = ll;
+            }
+          }
+          if (u == 0) offs[d] = run;
           __syncthreads();
           float* tmp = prev;
           prev = cur;
@@ -199,7 +249,8 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
 // ---------------------------------------------------------------------------
 __global__ void rnnt_grad_coef_kernel(const float* __restrict__ lse, const float* __restrict__ alpha,
                                       const float* __restrict__ beta,
-                                      const float* __restrict__ costs, const float* __restrict__ dy,
+                                      const double* __restrict__ diag_off,
+                                      const float* __restrict__ dy,
                                       const int32_t* __restrict__ targets,
                                       const int32_t* __restrict__ logit_len,
                                       const int32_t* __restrict__ target_len, int B, int Tm, int U1,
@@ -213,19 +264,26 @@ __global__ void rnnt_grad_coef_kernel(const float* __restrict__ lse, const float
   const int Tb = logit_len[b], Ub = target_len[b];
   float4 c = make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f);
   if (t < Tb && u <= Ub) {
-    // c = alpha + cost - lse ; gradient terms are exp(x + c + beta_*)
-    const float base = alpha[cell] + costs[b] - lse[cell];
-    c.x = base + beta[cell];
+    const int nd = Tm + U1;
+    const double* oa = diag_off + (long long)b * 2 * nd;
+    const double* ob = oa + nd;
+    const double ll = oa[nd - 1];
+    const int d = t + u;
+    // gradient terms are exp(x - lse + alpha + beta_* - ll); offsets combine in fp64,
+    // the per-diagonal sums are O(1) because sum over a diagonal of alpha*beta = exp(ll)
+    const float base = alpha[cell] - lse[cell];
+    const float k0 = (float)(oa[d] + ob[d] - ll);
+    c.x = base + beta[cell] + k0;
     const bool last_t = (t == Tb - 1);
     if (last_t && u == Ub)
-      c.y = base;
+      c.y = base + (float)(oa[d] - ll);
     else if (!last_t)
-      c.y = base + beta[cell + U1];
+      c.y = base + beta[cell + U1] + (float)(oa[d] + ob[d + 1] - ll);
     if (u < Ub) {
       int y = targets[(long long)b * (U1 - 1) + u];
       // if/else-if order of the reference: a target equal to blank only gets the
       // emit term when no blank term applied (t == Tb-1, u < Ub).
-      if (!(y == blank && !last_t)) c.z = base + beta[cell + 1];
+      if (!(y == blank && !last_t)) c.z = base + beta[cell + 1] + (float)(oa[d] + ob[d + 1] - ll);
     }
     c.w = dy[b];
   }
@@ -327,26 +385,27 @@ extern "C" int b200_rnnt_logprobs(const void* logits, int dtype, const int32_t* 
 
 extern "C" int b200_rnnt_lattice(const float* lp_blank, const float* lp_emit,
                                  const int32_t* logit_len, const int32_t* target_len, int B, int T,
-                                 int U1, float* alpha, float* beta, float* costs,
+                                 int U1, float* alpha, float* beta, float* costs, double* diag_off,
                                  b200_stream_t stream) {
   if (int rc = check_shape("b200_rnnt_lattice", B, T, U1, 1)) return rc;
-  B200_CHECK_ARG(lp_blank && lp_emit && logit_len && target_len && alpha && beta && costs,
+  B200_CHECK_ARG(lp_blank && lp_emit && logit_len && target_len && alpha && beta && costs &&
+                     diag_off,
                  "b200_rnnt_lattice: null pointer");
   B200_CHECK_ARG(U1 <= 1024, "b200_rnnt_lattice: U+1 = %d > 1024 not supported", U1);
   const int threads = ((U1 + 31) / 32) * 32;
-  const size_t smem = 2 * (size_t)(U1 + 2) * sizeof(float);
+  const size_t smem = (2 * (size_t)(U1 + 2) + 32) * sizeof(float);
   rnnt_lattice_kernel<<<dim3(B, 2), threads, smem, (cudaStream_t)stream>>>(
-      lp_blank, lp_emit, logit_len, target_len, T, U1, alpha, beta, costs);
+      lp_blank, lp_emit, logit_len, target_len, T, U1, alpha, beta, costs, diag_off);
   B200_CHECK_LAUNCH("rnnt_lattice_kernel");
   return B200_OK;
 }
 
 extern "C" int b200_rnnt_grad_coef(const float* lse, const float* alpha, const float* beta,
-                                   const float* costs, const float* dy, const int32_t* targets,
+                                   const double* diag_off, const float* dy, const int32_t* targets,
                                    const int32_t* logit_len, const int32_t* target_len, int B, int T,
                                    int U1, int blank, float* coef, b200_stream_t stream) {
   if (int rc = check_shape("b200_rnnt_grad_coef", B, T, U1, 1)) return rc;
-  B200_CHECK_ARG(lse && alpha && beta && costs && dy && logit_len && target_len && coef,
+  B200_CHECK_ARG(lse && alpha && beta && diag_off && dy && logit_len && target_len && coef,
                  "b200_rnnt_grad_coef: null pointer");
   B200_CHECK_ARG(U1 == 1 || targets, "b200_rnnt_grad_coef: null targets");
   B200_CHECK_ARG((reinterpret_cast<uintptr_t>(coef) & 15) == 0,
@@ -354,7 +413,7 @@ extern "C" int b200_rnnt_grad_coef(const float* lse, const float* alpha, const f
   const long long cells = (long long)B * T * U1;
   const unsigned grid = (unsigned)((cells + 255) / 256);
   rnnt_grad_coef_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
-      lse, alpha, beta, costs, dy, targets, logit_len, target_len, B, T, U1, blank,
+      lse, alpha, beta, diag_off, dy, targets, logit_len, target_len, B, T, U1, blank,
       reinterpret_cast<float4*>(coef));
   B200_CHECK_LAUNCH("rnnt_grad_coef_kernel");
   return B200_OK;
@@ -398,10 +457,10 @@ extern "C" int b200_rnnt_loss_fwd(const void* logits, int dtype, const int32_t* 
                                   const int32_t* logit_len, const int32_t* target_len, int B, int T,
                                   int U1, int V, int blank, float* costs, float* lse,
                                   float* lp_blank, float* lp_emit, float* alpha, float* beta,
-                                  b200_stream_t stream) {
+                                  double* diag_off, b200_stream_t stream) {
   int rc = b200_rnnt_logprobs(logits, dtype, targets, logit_len, target_len, B, T, U1, V, blank, lse,
                               lp_blank, lp_emit, stream);
   if (rc) return rc;
   return b200_rnnt_lattice(lp_blank, lp_emit, logit_len, target_len, B, T, U1, alpha, beta, costs,
-                           stream);
+                           diag_off, stream);
 }

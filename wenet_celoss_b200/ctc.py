@@ -31,18 +31,21 @@ class _CtcLossFn(torch.autograd.Function):
             lp_ext, alpha, beta = lat.unbind(0)
             nll = torch.empty(B, dtype=torch.float32, device=dev)
             leader = torch.empty(B, Smax, dtype=torch.int32, device=dev)
+            frame_off = torch.zeros(B, 2, T + 1, dtype=torch.float64, device=dev)
             dt = i32(_lib.dtype_code(logits))
             _lib.call("b200_ctc_logprobs", ptr(logits), dt, ptr(ys_pad), ptr(hlens), ptr(ys_lens),
                       i32(B), i32(T), i32(V), i32(Lmax), i32(blank), ptr(lse), ptr(lp_ext), st)
             _lib.call("b200_ctc_lattice", ptr(lp_ext), ptr(ys_pad), ptr(hlens), ptr(ys_lens), i32(B),
-                      i32(T), i32(Lmax), i32(blank), ptr(alpha), ptr(beta), ptr(nll), ptr(leader), st)
-        ctx.save_for_backward(logits, ys_pad, hlens, ys_lens, lse, lp_ext, alpha, beta, nll, leader)
+                      i32(T), i32(Lmax), i32(blank), ptr(alpha), ptr(beta), ptr(nll), ptr(leader),
+                      ptr(frame_off), st)
+        ctx.save_for_backward(logits, ys_pad, hlens, ys_lens, lse, lp_ext, alpha, beta, frame_off,
+                              leader)
         ctx.blank = blank
         return nll
 
     @staticmethod
     def backward(ctx, dy):
-        logits, ys_pad, hlens, ys_lens, lse, lp_ext, alpha, beta, nll, leader = ctx.saved_tensors
+        logits, ys_pad, hlens, ys_lens, lse, lp_ext, alpha, beta, frame_off, leader = ctx.saved_tensors
         B, T, V = logits.shape
         Lmax = ys_pad.size(1)
         dev = logits.device
@@ -50,7 +53,7 @@ class _CtcLossFn(torch.autograd.Function):
             scale = dy.detach().to(torch.float32).contiguous()
             grad = torch.empty_like(logits)
             _lib.call("b200_ctc_grad", ptr(logits), i32(_lib.dtype_code(logits)), ptr(lse),
-                      ptr(lp_ext), ptr(alpha), ptr(beta), ptr(nll), ptr(scale), ptr(ys_pad),
+                      ptr(lp_ext), ptr(alpha), ptr(beta), ptr(frame_off), ptr(scale), ptr(ys_pad),
                       ptr(hlens), ptr(ys_lens), ptr(leader), i32(B), i32(T), i32(V), i32(Lmax),
                       i32(ctx.blank), ptr(grad), _lib.stream_handle(dev))
         return grad, None, None, None, None

@@ -65,22 +65,24 @@ def _validate(logits, targets, logit_lengths, target_lengths, blank):
 
 
 def rnnt_lattice(lp_blank, lp_emit, logit_lengths, target_lengths):
-    """alpha, beta [B,T,U1] and costs [B] from per-cell blank / emit log-probs."""
+    """Rescaled alpha, beta [B,T,U1], costs [B] and the fp64 per-diagonal offsets
+    [B,2,T+U1] (see include/b200_transducer.h) from per-cell blank / emit log-probs."""
     B, T, U1 = lp_blank.shape
     alpha = torch.empty_like(lp_blank)
     beta = torch.empty_like(lp_blank)
     costs = torch.empty(B, dtype=torch.float32, device=lp_blank.device)
+    diag_off = torch.empty(B, 2, T + U1, dtype=torch.float64, device=lp_blank.device)
     _lib.call("b200_rnnt_lattice", ptr(lp_blank), ptr(lp_emit), ptr(logit_lengths),
               ptr(target_lengths), i32(B), i32(T), i32(U1), ptr(alpha), ptr(beta), ptr(costs),
-              _lib.stream_handle(lp_blank.device))
-    return alpha, beta, costs
+              ptr(diag_off), _lib.stream_handle(lp_blank.device))
+    return alpha, beta, costs, diag_off
 
 
-def rnnt_grad_coef(lse, alpha, beta, costs, dy, targets, logit_lengths, target_lengths, blank):
+def rnnt_grad_coef(lse, alpha, beta, diag_off, dy, targets, logit_lengths, target_lengths, blank):
     """float4 per lattice cell: {c0, cb, ce, scale} (see include/b200_transducer.h)."""
     B, T, U1 = lse.shape
     coef = torch.empty(B, T, U1, 4, dtype=torch.float32, device=lse.device)
-    _lib.call("b200_rnnt_grad_coef", ptr(lse), ptr(alpha), ptr(beta), ptr(costs), ptr(dy),
+    _lib.call("b200_rnnt_grad_coef", ptr(lse), ptr(alpha), ptr(beta), ptr(diag_off), ptr(dy),
               ptr(targets), ptr(logit_lengths), ptr(target_lengths), i32(B), i32(T), i32(U1),
               i32(blank), ptr(coef), _lib.stream_handle(lse.device))
     return coef
@@ -96,10 +98,13 @@ class _RnntLossFn(torch.autograd.Function):
             lat = torch.empty(5, B, T, U1, dtype=torch.float32, device=dev)
             lse, lpb, lpe, alpha, beta = lat.unbind(0)
             costs = torch.empty(B, dtype=torch.float32, device=dev)
+            diag_off = torch.empty(B, 2, T + U1, dtype=torch.float64, device=dev)
             _lib.call("b200_rnnt_loss_fwd", ptr(logits), i32(_lib.dtype_code(logits)), ptr(targets),
                       ptr(logit_lengths), ptr(target_lengths), i32(B), i32(T), i32(U1), i32(V),
-                      i32(blank), ptr(costs), ptr(lse), ptr(lpb), ptr(lpe), ptr(alpha), ptr(beta), st)
-        ctx.save_for_backward(logits, targets, logit_lengths, target_lengths, lse, alpha, beta, costs)
+                      i32(blank), ptr(costs), ptr(lse), ptr(lpb), ptr(lpe), ptr(alpha), ptr(beta),
+                      ptr(diag_off), st)
+        ctx.save_for_backward(logits, targets, logit_lengths, target_lengths, lse, alpha, beta,
+                              diag_off)
         ctx.blank = blank
         ctx.clamp = clamp
         # torchaudio returns costs in the logits dtype (f32/f16); bf16 (extension) stays f32
@@ -107,12 +112,12 @@ class _RnntLossFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
-        logits, targets, logit_lengths, target_lengths, lse, alpha, beta, costs = ctx.saved_tensors
+        logits, targets, logit_lengths, target_lengths, lse, alpha, beta, diag_off = ctx.saved_tensors
         B, T, U1, V = logits.shape
         dev = logits.device
         with torch.cuda.device(dev):
             dyf = dy.detach().to(torch.float32).contiguous()
-            coef = rnnt_grad_coef(lse, alpha, beta, costs, dyf, targets, logit_lengths,
+            coef = rnnt_grad_coef(lse, alpha, beta, diag_off, dyf, targets, logit_lengths,
                                   target_lengths, ctx.blank)
             grad = torch.empty_like(logits)
             _lib.call("b200_rnnt_grad", ptr(logits), i32(_lib.dtype_code(logits)), ptr(targets),
