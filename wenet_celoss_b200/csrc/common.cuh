@@ -79,6 +79,20 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// Lagged block maximum for the rescaled lattices: at step i every warp publishes the max
+// of the values it just produced (before the step's __syncthreads); at step i+1 all
+// threads read the other parity slot.  No extra barrier.  red = [2][32] floats.
+__device__ __forceinline__ void lagged_max_write(float v, float* red, int parity) {
+  v = warp_max(v);
+  if ((threadIdx.x & 31) == 0) red[parity * 32 + (threadIdx.x >> 5)] = v;
+}
+__device__ __forceinline__ float lagged_max_read(const float* red, int parity) {
+  const int nw = (blockDim.x + 31) >> 5;
+  float m = red[parity * 32];
+  for (int i = 1; i < nw; ++i) m = fmaxf(m, red[parity * 32 + i]);
+  return m == -INFINITY ? 0.f : m;
+}
+
 // streaming 16-byte global load: read once, do not pollute L1
 __device__ __forceinline__ uint4 ldg_stream16(const void* p) {
   uint4 r;

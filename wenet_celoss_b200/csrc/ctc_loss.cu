@@ -64,18 +64,6 @@ ctc_logprobs_kernel(const T* __restrict__ logits, const long long* __restrict__ 
 // One thread per extended state; previous frame in shared memory (ping-pong).
 // ---------------------------------------------------------------------------
 constexpr int kCtcPf = 4;
-constexpr int kCtcRenorm = 8;
-
-// block-wide max (one __syncthreads inside); red = 32 floats of shared scratch
-__device__ __forceinline__ float block_max_ctc(float v, float* red) {
-  v = warp_max(v);
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-  __syncthreads();
-  const int nw = (blockDim.x + 31) >> 5;
-  float m = red[0];
-  for (int i = 1; i < nw; ++i) m = fmaxf(m, red[i]);
-  return m;
-}
 
 __device__ __forceinline__ float lae3(float a, float b, float c) {
   float m = fmaxf(a, fmaxf(b, c));
@@ -90,7 +78,7 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
                                    float* __restrict__ alpha, float* __restrict__ beta,
                                    float* __restrict__ nll, int32_t* __restrict__ leader,
                                    double* __restrict__ frame_off) {
-  extern __shared__ float sm[];  // [2][Smax+4] floats, [32] reduction scratch, then [Smax] ints
+  extern __shared__ float sm[];  // [2][Smax+4] floats, [2][32] lagged-max scratch, then [Smax] ints
   const int b = blockIdx.x;
   const int s = threadIdx.x;
   const int Smax = 2 * Lmax + 1;
@@ -100,7 +88,7 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
   float* buf0 = sm + 2;  // indices -2 .. Smax+1 addressable
   float* buf1 = sm + stride + 2;
   float* red = sm + 2 * stride;
-  int* lab = reinterpret_cast<int*>(sm + 2 * stride + 32);
+  int* lab = reinterpret_cast<int*>(sm + 2 * stride + 64);
   double* offs = frame_off + ((long long)b * 2 + blockIdx.y) * (Tm + 1);
   double run = 0.0;  // running offset: alpha_t(s) = alpha_hat_t(s) + off_a[t] (same for beta)
   const long long* ys = ys_pad + (long long)b * Lmax;
@@ -138,11 +126,15 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
     const bool skip_ok = mine && s >= 2 && my != blank && my != lab[s - 2];
     float* prev = buf0;
     float* cur = buf1;
-    if (mine) {
-      float v = (s <= 1) ? lp[s] : -INFINITY;
-      prev[s] = v;
-      al[s] = v;
+    {
+      float v = (mine && s <= 1) ? lp[s] : -INFINITY;
+      if (mine) {
+        prev[s] = v;
+        al[s] = v;
+      }
+      lagged_max_write(v, red, 0);
     }
+    int it = 1;
     if (s == 0) offs[0] = 0.0;
     __syncthreads();
     float r[kCtcPf];
@@ -161,12 +153,12 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
         if (t < Tb) {  // block-uniform
           float v = -INFINITY;
           if (mine) v = lae3(prev[s], prev[s - 1], skip_ok ? prev[s - 2] : -INFINITY) + r[k];
-          if (t % kCtcRenorm == 0) {  // block-uniform: pull the frame maximum into the fp64 offset
-            float M = block_max_ctc(v, red);
-            if (M != -INFINITY) {
-              v -= M;
-              run += (double)M;
-            }
+          {  // pull the previous frame's maximum into the fp64 offset (no extra barrier)
+            const float M = lagged_max_read(red, (it - 1) & 1);
+            v -= M;
+            run += (double)M;
+            lagged_max_write(v, red, it & 1);
+            ++it;
           }
           if (mine) {
             cur[s] = v;
@@ -193,11 +185,15 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
     const bool skip_ok = mine && s + 2 < S && lab[s + 2] != blank && lab[s + 2] != my;
     float* prev = buf0;
     float* cur = buf1;
-    if (mine) {
-      float v = (s >= S - 2) ? lp[(long long)(Tb - 1) * Smax + s] : -INFINITY;
-      prev[s] = v;
-      be[(long long)(Tb - 1) * Smax + s] = v;
+    {
+      float v = (mine && s >= S - 2) ? lp[(long long)(Tb - 1) * Smax + s] : -INFINITY;
+      if (mine) {
+        prev[s] = v;
+        be[(long long)(Tb - 1) * Smax + s] = v;
+      }
+      lagged_max_write(v, red, 0);
     }
+    int it = 1;
     if (s == 0) offs[Tb - 1] = 0.0;
     __syncthreads();
     float r[kCtcPf];
@@ -219,12 +215,12 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
         if (t >= 0) {  // block-uniform
           float v = -INFINITY;
           if (mine) v = lae3(prev[s], prev[s + 1], skip_ok ? prev[s + 2] : -INFINITY) + r[k];
-          if (t % kCtcRenorm == 0) {  // block-uniform
-            float M = block_max_ctc(v, red);
-            if (M != -INFINITY) {
-              v -= M;
-              run += (double)M;
-            }
+          {
+            const float M = lagged_max_read(red, (it - 1) & 1);
+            v -= M;
+            run += (double)M;
+            lagged_max_write(v, red, it & 1);
+            ++it;
           }
           if (mine) {
             cur[s] = v;
@@ -367,7 +363,7 @@ extern "C" int b200_ctc_lattice(const float* lp_ext, const int64_t* ys_pad, cons
                  "b200_ctc_lattice: null pointer");
   const int Smax = 2 * Lmax + 1;
   const int threads = ((Smax + 31) / 32) * 32;
-  const size_t smem = (2 * (size_t)(Smax + 4) + 32) * sizeof(float) + (size_t)Smax * sizeof(int);
+  const size_t smem = (2 * (size_t)(Smax + 4) + 64) * sizeof(float) + (size_t)Smax * sizeof(int);
   ctc_lattice_kernel<<<dim3(B, 2), threads, smem, (cudaStream_t)stream>>>(
       lp_ext, reinterpret_cast<const long long*>(ys_pad), hlens, ys_lens, T, Lmax, blank, alpha,
       beta, nll, leader, frame_off);

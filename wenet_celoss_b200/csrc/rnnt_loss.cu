@@ -57,28 +57,15 @@ rnnt_logprobs_kernel(const T* __restrict__ logits, const int32_t* __restrict__ t
 // one __syncthreads per diagonal; log-prob loads run kPf diagonals ahead.
 //
 // Rescaling: every path crosses each anti-diagonal exactly once, so a per-diagonal
-// offset can be pulled out of alpha and beta without changing any posterior.  Every
-// kRenorm diagonals the block subtracts the diagonal's maximum and adds it to a
-// running fp64 offset:  alpha(t,u) = alpha_hat(t,u) + off_a[t+u]  (same for beta).
+// offset can be pulled out of alpha and beta without changing any posterior.  On every
+// diagonal the block subtracts the previous diagonal's maximum (published through shared
+// memory one step earlier, so no extra barrier) and adds it to a running fp64 offset:  alpha(t,u) = alpha_hat(t,u) + off_a[t+u]  (same for beta).
 // The stored fp32 values stay O(10) in magnitude, which removes the cost-sized
 // cancellation alpha+beta-cost that limits plain fp32 log-space to ~cost*2^-23.
 // diag_off layout: [B][2][T+U1] fp64; [b][0][d] alpha offsets, [b][1][d] beta offsets,
 // [b][0][T+U1-1] = log-likelihood of utterance b.
 // ---------------------------------------------------------------------------
 constexpr int kPf = 4;
-constexpr int kRenorm = 8;
-
-// max over the block of v (threads that do not take part pass -inf); all threads return it.
-// Contains one __syncthreads; `red` needs 32 floats.
-__device__ __forceinline__ float block_max(float v, float* red) {
-  v = warp_max(v);
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-  __syncthreads();
-  const int nw = (blockDim.x + 31) >> 5;
-  float m = red[0];
-  for (int i = 1; i < nw; ++i) m = fmaxf(m, red[i]);
-  return m;
-}
 
 __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
                                     const float* __restrict__ lp_emit,
@@ -86,7 +73,7 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
                                     const int32_t* __restrict__ target_len, int Tm, int U1,
                                     float* __restrict__ alpha, float* __restrict__ beta,
                                     float* __restrict__ costs, double* __restrict__ diag_off) {
-  extern __shared__ float diag[];  // [2][U1 + 2] + 32 (reduction scratch)
+  extern __shared__ float diag[];  // [2][U1 + 2] + [2][32] (lagged-max scratch)
   const int b = blockIdx.x;
   const int u = threadIdx.x;
   const int Tb = logit_len[b], Ub = target_len[b];
@@ -123,6 +110,8 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
       al[0] = 0.f;
       offs[0] = 0.0;
     }
+    lagged_max_write(u == 0 ? 0.f : -INFINITY, red, 0);
+    int it = 1;
     __syncthreads();
     float* prev = buf0;
     float* cur = buf1;
@@ -150,12 +139,12 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
           const bool live = mine && t >= 0 && t < Tb;
           float v = -INFINITY;
           if (live) v = log_add_exp(prev[u] + rb[k], prev[u - 1] + re[k]);
-          if (d % kRenorm == 0) {  // block-uniform
-            float M = block_max(v, red);
-            if (M != -INFINITY) {
-              v -= M;
-              run += (double)M;
-            }
+          {
+            const float M = lagged_max_read(red, (it - 1) & 1);
+            v -= M;
+            run += (double)M;
+            lagged_max_write(v, red, it & 1);
+            ++it;
           }
           if (mine) cur[u] = v;
           if (live) al[(long long)t * U1 + u] = v;
@@ -187,6 +176,8 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
         diag_off[(long long)b * 2 * nd + nd - 1] = (double)v;
       }
     }
+    lagged_max_write(u == Ub ? lpb[(long long)(Tb - 1) * U1 + Ub] : -INFINITY, red, 0);
+    int it = 1;
     __syncthreads();
     float rb[kPf], re[kPf];
     auto fetch = [&](int d, float& vb, float& ve) {
@@ -212,12 +203,12 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
           const bool live = mine && t >= 0 && t < Tb;
           float v = -INFINITY;
           if (live) v = log_add_exp(prev[u] + rb[k], prev[u + 1] + re[k]);
-          if (d % kRenorm == 0 && d != 0) {  // block-uniform
-            float M = block_max(v, red);
-            if (M != -INFINITY) {
-              v -= M;
-              run += (double)M;
-            }
+          {
+            const float M = lagged_max_read(red, (it - 1) & 1);
+            v -= M;
+            run += (double)M;
+            lagged_max_write(v, red, it & 1);
+            ++it;
           }
           if (mine) cur[u] = v;
           if (live) {
@@ -393,7 +384,7 @@ extern "C" int b200_rnnt_lattice(const float* lp_blank, const float* lp_emit,
                  "b200_rnnt_lattice: null pointer");
   B200_CHECK_ARG(U1 <= 1024, "b200_rnnt_lattice: U+1 = %d > 1024 not supported", U1);
   const int threads = ((U1 + 31) / 32) * 32;
-  const size_t smem = (2 * (size_t)(U1 + 2) + 32) * sizeof(float);
+  const size_t smem = (2 * (size_t)(U1 + 2) + 64) * sizeof(float);
   rnnt_lattice_kernel<<<dim3(B, 2), threads, smem, (cudaStream_t)stream>>>(
       lp_blank, lp_emit, logit_len, target_len, T, U1, alpha, beta, costs, diag_off);
   B200_CHECK_LAUNCH("rnnt_lattice_kernel");
