@@ -130,6 +130,33 @@ int b200_ctc_grad(const void* logits, int dtype, const float* lse, const float* 
                   int B, int T, int V, int Lmax, int blank,
                   void* grad, b200_stream_t stream);
 
+/* ---- Fused joint + RNN-T loss (logits never materialised) ----------------
+ * replaces wenet/transducer/transducer.py:132-147: TransducerJoint.forward
+ * (wenet/transducer/joint.py:58-69: broadcast add, tanh, ffn_out) fused with the
+ * log-softmax statistics / logits-gradient of torchaudio.functional.rnnt_loss.
+ * e [B*T, J], p [B*U1, J] fp32 = outputs of enc_ffn / pred_ffn (joint.py:55-56, library
+ * GEMMs on the caller's side); w_bf16 [V, J] bf16 = ffn_out.weight; bias_pad
+ * [ceil(V/256)*256] fp32 zero padded = ffn_out.bias.  J multiple of 64, <= 512.
+ * Tensor-core kernel (tcgen05 / TMEM / TMA); max_ctas <= 0 means one CTA per SM.
+ */
+
+/* forward: per lattice cell lse over V and the blank / target log-probs [B,T,U1] */
+int b200_joint_fwd(const float* e, const float* p, const void* w_bf16, const float* bias_pad,
+                   const int32_t* targets, const int32_t* logit_len, const int32_t* target_len,
+                   int B, int T, int U1, int V, int J, int blank,
+                   float* lse, float* lp_blank, float* lp_emit,
+                   int max_ctas, b200_stream_t stream);
+
+/* backward, one chunk of cells [cell0, cell0+ncells) (cell = (b*T+t)*U1+u): recompute the
+ * logits tile and write G = d loss / d logits (bf16, [ncells, ldg], ldg % 8 == 0) from the
+ * coefficients of b200_rnnt_grad_coef; optionally also H = tanh(e+p) in bf16 [ncells, ldh]. */
+int b200_joint_grad_chunk(const float* e, const float* p, const void* w_bf16,
+                          const float* bias_pad, const int32_t* targets, const float* coef,
+                          int B, int T, int U1, int V, int J, int blank,
+                          long long cell0, long long ncells,
+                          void* G, int ldg, void* H, int ldh,
+                          int max_ctas, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

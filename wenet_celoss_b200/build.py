@@ -46,7 +46,8 @@ def _digest(paths) -> str:
 def build_library(force: bool = False, verbose: bool = False) -> Path:
     """Compile every csrc/*.cu for sm_100a and link the shared library."""
     sources = sorted(CSRC.glob("*.cu"))
-    headers = sorted(CSRC.glob("*.cuh")) + sorted((ROOT / "include").glob("*.h"))
+    headers = (sorted(CSRC.glob("*.cuh")) + sorted(CSRC.glob("*.inc")) +
+               sorted((ROOT / "include").glob("*.h")))
     OBJ_DIR.mkdir(exist_ok=True)
     hdr_digest = _digest(headers)
     nvcc = _nvcc()
@@ -75,7 +76,7 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
         stamp.write_text(want)
     if relink:
         cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", str(LIB),
-               *map(str, objs), "-lcudart", "-lcuda"]
+               *map(str, objs), "-lcudart"]
         r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}")

@@ -1,0 +1,238 @@
+// Fused transducer joint: logits tile = tanh(e[b,t,:] + p[b,u,:]) . W_out^T + b_out on the
+// 5th-gen tensor cores (tcgen05.mma, accumulators in TMEM), with the epilogue consuming the
+// tile straight out of TMEM so the [B,T,U+1,V] logits never reach HBM.
+//
+// Replaces, at wenet/transducer/transducer.py:132-147, the chain
+//   TransducerJoint.forward (wenet/transducer/joint.py:58-69: broadcast add, tanh, ffn_out)
+//   + the log-softmax statistics / gradient of torchaudio.functional.rnnt_loss.
+// enc_ffn / pred_ffn (joint.py:55-56) stay library GEMMs in the Python wrapper and arrive
+// here as e [B*T, J] and p [B*U1, J] (fp32).
+//
+// One persistent CTA per SM walks M-tiles of 128 lattice cells (cell = (b*T + t)*U1 + u):
+//   warps 8-11  build the A tile H = tanh(e+p) in bf16, K-major SWIZZLE_128B, 8 k-blocks
+//   warp  0     TMA-loads W_out tiles [256 vocab rows x 64 k] (bf16) into a 3-stage ring
+//   warp  1     one thread issues tcgen05.mma (M=128, N=256, K=16), two TMEM accumulators
+//   warps 4-7   epilogue, one thread per cell row, tcgen05.ld 32 columns at a time:
+//     MODE_FWD   online (max, sum-exp) over V, picks the blank and target logits
+//                -> lse, lp_blank, lp_emit  (3 floats per cell leave the CTA)
+//     MODE_GRAD  G = scale*(exp(x+c0) - [v==blank]exp(x+cb) - [v==y]exp(x+ce)) in bf16 into a
+//                bounded scratch chunk that feeds the two plain backward GEMMs
+// Roofline: tensor pipe. 2*128*256*64 flop per pipeline stage; algorithmic flops per launch
+// = 2 * cells * J * V.
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace b200 {
+namespace jf {
+
+constexpr int kTileM = 128;
+constexpr int kTileN = 256;
+constexpr int kBlockK = 64;   // bf16 elements per 128-byte swizzle row
+constexpr int kMaxKB = 8;     // J <= 512
+constexpr int kStages = 3;
+constexpr int kABlockBytes = kTileM * kBlockK * 2;   // 16 KB per k-block
+constexpr int kABytes = kMaxKB * kABlockBytes;       // 128 KB
+constexpr int kWStageBytes = kTileN * kBlockK * 2;   // 32 KB
+constexpr int kThreads = 384;
+constexpr int kTmemCols = 512;
+constexpr int kSmemBytes = kABytes + kStages * kWStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+
+enum { MODE_FWD = 0, MODE_GRAD = 1 };
+
+struct Params {
+  const float* e;       // [B*T, J]
+  const float* p;       // [B*U1, J]
+  const float* bias;    // [NT*256] zero padded
+  const int32_t* targets;
+  const int32_t* logit_len;
+  const int32_t* target_len;
+  int B, T, U1, V, J, blank;
+  long long cell0, ncells, total_cells;
+  // MODE_FWD
+  float* lse;
+  float* lp_blank;
+  float* lp_emit;
+  // MODE_GRAD
+  const float4* coef;
+  __nv_bfloat16* G;  // [ncells, ldg]
+  int ldg;
+  __nv_bfloat16* H;  // optional [ncells, ldh]: the bf16 activations, for the dW GEMM
+  int ldh;
+};
+
+struct Barriers {
+  uint64_t full[kStages];
+  uint64_t empty[kStages];
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  uint64_t a_ready[kMaxKB];
+  uint64_t a_free[kMaxKB];
+  uint32_t tmem_base;
+};
+
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kThreads, 1)
+joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B operands need 1024-B alignment
+  uint8_t* smem = smem_raw + (base - raw);
+  const uint32_t sA = base;
+  const uint32_t sW = base + kABytes;
+  Barriers* bars = reinterpret_cast<Barriers*>(smem + kABytes + kStages * kWStageBytes);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int nkb = P.J / kBlockK;
+  const int NT = (P.V + kTileN - 1) / kTileN;
+  const int ntiles = (int)((P.ncells + kTileM - 1) / kTileM);
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kStages; ++i) {
+      ptx::mbar_init(ptx::smem_u32(&bars->full[i]), 1);
+      ptx::mbar_init(ptx::smem_u32(&bars->empty[i]), 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(ptx::smem_u32(&bars->tmem_full[i]), 1);
+      ptx::mbar_init(ptx::smem_u32(&bars->tmem_empty[i]), 128);
+    }
+    for (int i = 0; i < kMaxKB; ++i) {
+      ptx::mbar_init(ptx::smem_u32(&bars->a_ready[i]), 4);
+      ptx::mbar_init(ptx::smem_u32(&bars->a_free[i]), 1);
+    }
+    ptx::fence_barrier_init();
+    ptx::prefetch_tensormap(&w_map);
+  }
+  if (warp == 2) {
+    ptx::tmem_alloc(ptx::smem_u32(&bars->tmem_base), kTmemCols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = bars->tmem_base;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0, ph = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
+        for (int n = 0; n < NT; ++n)
+          for (int kb = 0; kb < nkb; ++kb) {
+            ptx::mbar_wait(ptx::smem_u32(&bars->empty[stage]), ph ^ 1);
+            const uint32_t fb = ptx::smem_u32(&bars->full[stage]);
+            ptx::mbar_arrive_expect_tx(fb, kWStageBytes);
+            ptx::tma_load_2d(sW + stage * kWStageBytes, &w_map, fb, kb * kBlockK, n * kTileN);
+            if (++stage == kStages) {
+              stage = 0;
+              ph ^= 1;
+            }
+          }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(kTileM, kTileN);
+      int stage = 0, ph = 0, acc = 0, acc_ph = 0, it = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        for (int n = 0; n < NT; ++n) {
+          ptx::mbar_wait(ptx::smem_u32(&bars->tmem_empty[acc]), acc_ph ^ 1);
+          ptx::tc_fence_after();
+          const uint32_t d_tmem = tmem + acc * kTileN;
+          for (int kb = 0; kb < nkb; ++kb) {
+            if (n == 0) ptx::mbar_wait(ptx::smem_u32(&bars->a_ready[kb]), it & 1);
+            ptx::mbar_wait(ptx::smem_u32(&bars->full[stage]), ph);
+            ptx::tc_fence_after();
+            const uint64_t da = ptx::make_sw128_kmajor_desc(sA + kb * kABlockBytes);
+            const uint64_t db = ptx::make_sw128_kmajor_desc(sW + stage * kWStageBytes);
+#pragma unroll
+            for (int k = 0; k < kBlockK / 16; ++k)  // +32 bytes (>>4 = 2) per K=16 step
+              ptx::umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            ptx::umma_commit(ptx::smem_u32(&bars->empty[stage]));
+            if (n == NT - 1) ptx::umma_commit(ptx::smem_u32(&bars->a_free[kb]));
+            if (++stage == kStages) {
+              stage = 0;
+              ph ^= 1;
+            }
+          }
+          ptx::umma_commit(ptx::smem_u32(&bars->tmem_full[acc]));
+          acc ^= 1;
+          if (acc == 0) acc_ph ^= 1;
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 8) {
+    // ===================== A-tile builders: H = tanh(e + p) -> bf16, swizzled =====================
+    const int bw = warp - 8;       // rows bw*32 .. bw*32+31
+    const int rr = lane >> 3;      // row within a group of 4
+    const int cc = lane & 7;       // 16-byte chunk within the 128-byte row
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      long long eoff[8], poff[8];
+      long long rowg[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int r = bw * 32 + i * 4 + rr;
+        long long local = (long long)tile * kTileM + r;
+        rowg[i] = local < P.ncells ? local : -1;
+        long long cell = P.cell0 + local;
+        if (cell >= P.total_cells) cell = P.total_cells - 1;
+        const long long bt = cell / P.U1;
+        const int u = (int)(cell - bt * P.U1);
+        const int b = (int)(bt / P.T);
+        eoff[i] = bt * P.J;
+        poff[i] = ((long long)b * P.U1 + u) * P.J;
+      }
+      for (int kb = 0; kb < nkb; ++kb) {
+        ptx::mbar_wait(ptx::smem_u32(&bars->a_free[kb]), (it & 1) ^ 1);
+        const int k0 = kb * kBlockK + cc * 8;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = bw * 32 + i * 4 + rr;
+          const float4* ep = reinterpret_cast<const float4*>(P.e + eoff[i] + k0);
+          const float4* pp = reinterpret_cast<const float4*>(P.p + poff[i] + k0);
+          const float4 e0 = __ldg(ep), e1 = __ldg(ep + 1);
+          const float4 p0 = __ldg(pp), p1 = __ldg(pp + 1);
+          uint4 h;
+          h.x = pack_bf16x2(tanh_approx(e0.x + p0.x), tanh_approx(e0.y + p0.y));
+          h.y = pack_bf16x2(tanh_approx(e0.z + p0.z), tanh_approx(e0.w + p0.w));
+          h.z = pack_bf16x2(tanh_approx(e1.x + p1.x), tanh_approx(e1.y + p1.y));
+          h.w = pack_bf16x2(tanh_approx(e1.z + p1.z), tanh_approx(e1.w + p1.w));
+          uint8_t* dst = smem + kb * kABlockBytes + r * 128 + ((cc ^ (r & 7)) << 4);
+          *reinterpret_cast<uint4*>(dst) = h;
+          if (MODE == MODE_GRAD && P.H != nullptr && rowg[i] >= 0)
+            *reinterpret_cast<uint4*>(P.H + rowg[i] * P.ldh + k0) = h;
+        }
+        ptx::fence_proxy_async();  // generic-proxy stores -> visible to the tensor core
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bars->a_ready[kb]));
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+#include "joint_fused_epilogue.inc"
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem, kTmemCols);
+  }
+}
+
+}  // namespace jf
+}  // namespace b200
+
+#include "joint_fused_host.inc"
