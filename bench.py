@@ -196,6 +196,49 @@ class RnntLogitsWorkload:
         return out
 
 
+
+    # ---- contract hooks -------------------------------------------------------------
+    dtype = "bf16"
+
+    def e2e_setup(self):
+        self.tgt_pin = self.targets_h.pin_memory()
+        self.tl_pin, self.ul_pin = self.tl_h.pin_memory(), self.ul_h.pin_memory()
+        self.loss_pin = torch.empty((), dtype=torch.float32).pin_memory()
+
+    def e2e_step(self):
+        self.targets.copy_(self.tgt_pin, non_blocking=True)
+        self.tl.copy_(self.tl_pin, non_blocking=True)
+        self.ul.copy_(self.ul_pin, non_blocking=True)
+        l = self.step()
+        self.loss_pin.copy_(l.detach().float(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    def e2e_bytes(self):
+        return int(4 * (self.tgt_pin.numel() + self.tl_pin.numel() + self.ul_pin.numel())), 4
+
+    e2e_note = "rnnt_loss(logits,...) API: logits are device-produced; host inputs are targets+lengths"
+
+    def roofline(self, pk, ms_step):
+        kb = self.kernel_breakdown()
+        dom = "rnnt_grad_kernel"
+        dom_bytes = 2 * self.N * self.elem
+        achieved = dom_bytes / (kb[dom] * 1e-3) / 1e9
+        lp = self.N * self.elem / (kb["rnnt_logprobs_kernel"] * 1e-3) / 1e9
+        return {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s",
+                "frac": achieved / pk["hbm"], "traffic": None, "peak_source": pk["source"],
+                "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms": kb,
+                "other": {"rnnt_logprobs_kernel": {"achieved": lp, "frac": lp / pk["hbm"]}},
+                "step_frac_of_hbm_roofline":
+                    self.algorithmic_bytes() / (ms_step * 1e-3) / 1e9 / pk["hbm"]}
+
+    def describe(self):
+        return ("rnnt_logits: rnnt_loss fwd+bwd over materialised bf16 logits, B=32 T=500 U=100 "
+                "V=5000 per GPU (cfg3)", "inputs (16.2 GB logits) larger than L2")
+
+    def allreduce(self, dist):
+        return None  # independent utterances, no data-path collective
+
+
 # --------------------------------------------------------------------------- reference arm
 def reference_step(cfg, T_s, threads, seed=0):
     """One fwd+bwd of the reference path (oracle port: torch joint + torchaudio CPU
@@ -253,6 +296,157 @@ def run_reference(args, cfg):
     print(json.dumps(line), flush=True)
 
 
+# --------------------------------------------------------------------------- fused workload
+class _Joint(torch.nn.Module):
+    """Parameter container with the reference TransducerJoint's names (joint.py:34-43)."""
+
+    def __init__(self, V, E, P, J):
+        super().__init__()
+        self.enc_ffn = torch.nn.Linear(E, J)
+        self.pred_ffn = torch.nn.Linear(P, J)
+        self.ffn_out = torch.nn.Linear(J, V)
+
+
+class RnntFusedWorkload:
+    """Headline: joint + RNN-T loss fwd+bwd from encoder / predictor outputs (cfg3), logits
+    never materialised; gradients w.r.t. enc_out, pred_out and all joint parameters."""
+    name = "rnnt_fused"
+    dtype = "bf16"
+
+    def __init__(self, cfg, rank, ragged=False):
+        import wenet_celoss_b200 as pkg
+        self.pkg = pkg
+        self.cfg = cfg
+        B, T, U, V, E, P, J = (cfg[k] for k in ("B", "T", "U", "V", "E", "P", "J"))
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        torch.manual_seed(1234)  # identical replicated weights on every rank
+        self.joint = _Joint(V, E, P, J).to(self.dev)
+        g = torch.Generator().manual_seed(1234 + rank)
+        self.tl_h, self.ul_h = synth_lengths(B, T, U, g, ragged)
+        self.targets_h = torch.randint(1, V, (B, U), generator=g, dtype=torch.int32)
+        self.enc_h = torch.randn(B, T, E, generator=g)
+        self.pred_h = torch.randn(B, U + 1, P, generator=g)
+        self.enc = self.enc_h.to(self.dev).requires_grad_(True)
+        self.pred = self.pred_h.to(self.dev).requires_grad_(True)
+        self.targets = self.targets_h.to(self.dev)
+        self.tl = self.tl_h.to(self.dev)
+        self.ul = self.ul_h.to(self.dev)
+        self.cells = B * T * (U + 1)
+        self.params = list(self.joint.parameters())
+
+    def step(self):
+        self.enc.grad = None
+        self.pred.grad = None
+        for p in self.params:
+            p.grad = None
+        loss = self.pkg.fused_joint_rnnt_loss(self.joint, self.enc, self.pred, self.targets, self.tl,
+                                              self.ul, blank=0, reduction="mean")
+        loss.backward()
+        return loss
+
+    def allreduce(self, dist):
+        """What DDP does for these parameters (wenet/bin/train.py:231): one flat all-reduce of the
+        joint weight gradients + the scalar loss over NCCL."""
+        flat = torch.cat([p.grad.reshape(-1) for p in self.params])
+        dist.all_reduce(flat)
+        return flat
+
+    def e2e_setup(self):
+        self.pins = [t.pin_memory() for t in (self.enc_h, self.pred_h, self.targets_h, self.tl_h,
+                                              self.ul_h)]
+        self.loss_pin = torch.empty((), dtype=torch.float32).pin_memory()
+
+    def e2e_step(self):
+        with torch.no_grad():
+            for dst, src in zip((self.enc, self.pred, self.targets, self.tl, self.ul), self.pins):
+                dst.copy_(src, non_blocking=True)
+        l = self.step()
+        self.loss_pin.copy_(l.detach().float(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    def e2e_bytes(self):
+        return int(sum(t.numel() * t.element_size() for t in self.pins)), 4
+
+    e2e_note = ("fused_joint_rnnt_loss API: encoder/predictor outputs, targets and lengths copied "
+                "from pinned host memory every step; loss read back")
+
+    def kernel_breakdown(self, iters=3):
+        from wenet_celoss_b200 import _lib
+        from wenet_celoss_b200._lib import i32, ptr
+        from wenet_celoss_b200.joint import _i64, _pad_bias, joint_logprobs
+        from wenet_celoss_b200.rnnt import rnnt_grad_coef, rnnt_lattice
+        cfg = self.cfg
+        B, T, U, V, J = (cfg[k] for k in ("B", "T", "U", "V", "J"))
+        U1 = U + 1
+        with torch.no_grad():
+            e = self.joint.enc_ffn(self.enc).float().contiguous()
+            p = self.joint.pred_ffn(self.pred).float().contiguous()
+            w = self.joint.ffn_out.weight.to(torch.bfloat16).contiguous()
+            bias = _pad_bias(self.joint.ffn_out.bias, V)
+        st = _lib.stream_handle(self.dev)
+        box = {}
+
+        def k_fwd():
+            box["lat"] = joint_logprobs(e, p, w, bias, self.targets, self.tl, self.ul, V, 0)
+
+        def k_lat():
+            box["ab"] = rnnt_lattice(box["lat"][1], box["lat"][2], self.tl, self.ul)
+
+        per_utt = T * U1
+        ldg, ldh = (V + 7) // 8 * 8, J + 8
+        G = torch.empty(per_utt, ldg, dtype=torch.bfloat16, device=self.dev)
+        H = torch.zeros(per_utt, ldh, dtype=torch.bfloat16, device=self.dev)
+        dy = torch.full((B,), 1.0 / B, device=self.dev)
+
+        def k_grad():
+            _lib.call("b200_joint_grad_chunk", ptr(e), ptr(p), ptr(w), ptr(bias), ptr(self.targets),
+                      ptr(box["coef"]), i32(B), i32(T), i32(U1), i32(V), i32(J), i32(0), _i64(0),
+                      _i64(per_utt), ptr(G), i32(ldg), ptr(H), i32(ldh), i32(0), st)
+
+        out = {}
+        k_fwd(); k_lat()
+        alpha, beta, costs, doff = box["ab"]
+        box["coef"] = rnnt_grad_coef(box["lat"][0], alpha, beta, doff, dy, self.targets, self.tl, self.ul, 0)
+        for name, fn in (("joint_kernel<FWD> (all cells)", k_fwd), ("rnnt_lattice_kernel", k_lat),
+                         ("joint_kernel<GRAD> (1 utterance chunk)", k_grad)):
+            ts = []
+            for _ in range(iters + 1):
+                e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+                e0.record()
+                fn()
+                e1.record()
+                e1.synchronize()
+                ts.append(e0.elapsed_time(e1))
+            out[name] = statistics.mean(ts[1:])
+        return out
+
+    def roofline(self, pk, ms_step):
+        kb = self.kernel_breakdown()
+        cfg = self.cfg
+        flops_fwd = 2.0 * self.cells * cfg["J"] * cfg["V"]
+        t_fwd = kb["joint_kernel<FWD> (all cells)"]
+        achieved = flops_fwd / (t_fwd * 1e-3) / 1e12
+        flops_chunk = 2.0 * cfg["T"] * (cfg["U"] + 1) * cfg["J"] * cfg["V"]
+        ach_g = flops_chunk / (kb["joint_kernel<GRAD> (1 utterance chunk)"] * 1e-3) / 1e12
+        counted = 6.0 * self.cells * cfg["J"] * cfg["V"]
+        return {"bound": "tensor", "kernel": "joint_kernel<FWD>", "achieved": achieved,
+                "peak": pk["bf16"], "unit": "TFLOP/s", "frac": achieved / pk["bf16"], "traffic": None,
+                "peak_source": pk["source"] + " (burst: kernel timed alone)",
+                "algorithmic_flops_per_launch": flops_fwd, "kernel_ms": kb,
+                "other": {"joint_kernel<GRAD>": {"achieved": ach_g, "frac": ach_g / pk["bf16"]}},
+                "step_frac_of_tensor_roofline":
+                    counted / (ms_step * 1e-3) / 1e12 / pk["bf16_sustained"],
+                "step_counted_flops": counted}
+
+    def describe(self):
+        return ("rnnt_fused: joint (enc_ffn, pred_ffn, tanh, ffn_out) + RNN-T loss fwd+bwd, logits "
+                "never materialised, B=32 T=500 U=100 V=5000 J=512 per GPU (cfg3), bf16 MMA operands",
+                "L2 flushed by the step itself: each step streams >16 GB of gradient scratch")
+
+
+WORKLOADS = {"rnnt_logits": RnntLogitsWorkload, "rnnt_fused": RnntFusedWorkload}
+
+
 # --------------------------------------------------------------------------- main arm
 def cpu_baseline(cfg):
     threads = os.cpu_count() or 1
@@ -272,7 +466,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="rnnt_logits")
+    ap.add_argument("--workload", default="rnnt_fused", choices=sorted(WORKLOADS))
     ap.add_argument("--ragged", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -295,7 +489,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     import wenet_celoss_b200 as pkg
-    wl = RnntLogitsWorkload(cfg, rank, ragged=args.ragged)
+    wl = WORKLOADS[args.workload](cfg, rank, ragged=args.ragged)
     pk = peaks()
 
     def sync_all():
@@ -304,8 +498,21 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
+    def max_over_ranks(ms):
+        if dist is None:
+            return ms
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def full_step():
+        loss = wl.step()
+        if dist is not None:
+            wl.allreduce(dist)
+        return loss
+
     for _ in range(args.warmup):
-        wl.step()
+        full_step()
     sync_all()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -314,68 +521,42 @@ def main():
     e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
     e0.record()
     for _ in range(args.steps):
-        loss = wl.step()
+        loss = full_step()
     e1.record()
     sync_all()
-    ms = e0.elapsed_time(e1)
+    ms = max_over_ranks(e0.elapsed_time(e1))
     launches = pkg.launch_count() - n0
     clocks = sampler.stop() if rank == 0 else None
-    if dist is not None:
-        t = torch.tensor([ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
     B = cfg["B"]
     value = world * B * args.steps / (ms * 1e-3)
 
-    # e2e: for the materialised-logits API the step's host-side inputs are the targets and
-    # lengths (logits are produced on the device by the joint); result read back = loss.
+    # e2e: same step through the public API with host buffers (pinned), H2D + D2H inside
+    wl.e2e_setup()
+    wl.e2e_step()
     sync_all()
-    tgt_pin = wl.targets_h.pin_memory()
-    tl_pin, ul_pin = wl.tl_h.pin_memory(), wl.ul_h.pin_memory()
-    loss_pin = torch.empty((), dtype=torch.float32).pin_memory()
     f0, f1 = torch.cuda.Event(True), torch.cuda.Event(True)
     f0.record()
     for _ in range(args.steps):
-        wl.targets.copy_(tgt_pin, non_blocking=True)
-        wl.tl.copy_(tl_pin, non_blocking=True)
-        wl.ul.copy_(ul_pin, non_blocking=True)
-        l = wl.step()
-        loss_pin.copy_(l.detach().float(), non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        wl.e2e_step()
+        if dist is not None:
+            wl.allreduce(dist)
     f1.record()
     sync_all()
-    ms_e2e = f0.elapsed_time(f1)
-    if dist is not None:
-        t = torch.tensor([ms_e2e], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_e2e = float(t.item())
+    ms_e2e = max_over_ranks(f0.elapsed_time(f1))
+    h2d, d2h = wl.e2e_bytes()
     e2e = {"value": world * B * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
-           "h2d_bytes_per_step": int(tgt_pin.numel() * 4 + tl_pin.numel() * 4 + ul_pin.numel() * 4),
-           "d2h_bytes_per_step": 4,
-           "note": "rnnt_loss(logits,...) API: logits are device-produced; host inputs are targets+lengths"}
+           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "note": wl.e2e_note}
 
     if rank == 0:
-        kb = wl.kernel_breakdown()
-        dom = "rnnt_grad_kernel"
-        dom_bytes = 2 * wl.N * wl.elem
-        achieved = dom_bytes / (kb[dom] * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s",
-                "frac": achieved / pk["hbm"], "traffic": None, "peak_source": pk["source"],
-                "algorithmic_bytes_per_launch": dom_bytes,
-                "kernel_ms": kb,
-                "other": {"rnnt_logprobs_kernel": {
-                    "achieved": wl.N * wl.elem / (kb["rnnt_logprobs_kernel"] * 1e-3) / 1e9,
-                    "frac": wl.N * wl.elem / (kb["rnnt_logprobs_kernel"] * 1e-3) / 1e9 / pk["hbm"]}},
-                "step_frac_of_hbm_roofline": wl.algorithmic_bytes() / (ms / args.steps * 1e-3) / 1e9 / pk["hbm"]}
+        roof = wl.roofline(pk, ms / args.steps)
         cb = None if args.no_cpu_baseline else cpu_baseline(cfg)
+        desc, l2 = wl.describe()
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"{wl.name}: rnnt_loss fwd+bwd over materialised bf16 logits, "
-                                   "B=32 T=500 U=100 V=5000 per GPU (cfg3)",
-                       "global_batch": world * B, **cfg, "ragged": bool(args.ragged),
-                       "l2": "inputs (16.2 GB logits) larger than L2", "parallelism": f"dp{world}"},
+            "scaling": "weak", "vs_baseline": None, "dtype": wl.dtype, "data": "synthetic",
+            "config": {"workload": desc, "global_batch": world * B, **cfg,
+                       "ragged": bool(args.ragged), "l2": l2, "parallelism": f"dp{world}"},
             "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cb,
             "clocks": clocks, "loss": float(loss.item()),
         }
