@@ -393,7 +393,7 @@ class RnntFusedWorkload:
             box["ab"] = rnnt_lattice(box["lat"][1], box["lat"][2], self.tl, self.ul)
 
         per_utt = T * U1
-        ldg, ldh = (V + 7) // 8 * 8, J + 8
+        ldg, ldh = (V + 15) // 16 * 16, J + 8
         G = torch.empty(per_utt, ldg, dtype=torch.bfloat16, device=self.dev)
         H = torch.zeros(per_utt, ldh, dtype=torch.bfloat16, device=self.dev)
         dy = torch.full((B,), 1.0 / B, device=self.dev)

@@ -148,7 +148,7 @@ int b200_joint_fwd(const float* e, const float* p, const void* w_bf16, const flo
                    int max_ctas, b200_stream_t stream);
 
 /* backward, one chunk of cells [cell0, cell0+ncells) (cell = (b*T+t)*U1+u): recompute the
- * logits tile and write G = d loss / d logits (bf16, [ncells, ldg], ldg % 8 == 0) from the
+ * logits tile and write G = d loss / d logits (bf16, [ncells, ldg], ldg % 16 == 0) from the
  * coefficients of b200_rnnt_grad_coef; optionally also H = tanh(e+p) in bf16 [ncells, ldh]. */
 int b200_joint_grad_chunk(const float* e, const float* p, const void* w_bf16,
                           const float* bias_pad, const int32_t* targets, const float* coef,
@@ -156,6 +156,12 @@ int b200_joint_grad_chunk(const float* e, const float* p, const void* w_bf16,
                           long long cell0, long long ncells,
                           void* G, int ldg, void* H, int ldh,
                           int max_ctas, b200_stream_t stream);
+
+/* backward tail: dZ = dH * (1 - H^2), d e[b,t,:] = sum_u dZ, d p[b,u,:] += sum_t dZ
+ * (autograd through joint.py:58-68) for nb whole utterances: dH [nb*T*U1, J] fp32,
+ * H [nb*T*U1, ldh] bf16, de [nb,T,J] (written), dp [nb,U1,J] (accumulated: zero it first). */
+int b200_joint_dz_reduce(const float* dH, const void* H, int ldh, int nb, int T, int U1, int J,
+                         float* de, float* dp, b200_stream_t stream);
 
 #ifdef __cplusplus
 }

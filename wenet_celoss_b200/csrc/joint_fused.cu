@@ -9,10 +9,12 @@
 // here as e [B*T, J] and p [B*U1, J] (fp32).
 //
 // One persistent CTA per SM walks M-tiles of 128 lattice cells (cell = (b*T + t)*U1 + u):
-//   warps 8-11  build the A tile H = tanh(e+p) in bf16, K-major SWIZZLE_128B, 8 k-blocks
+//   warps 12-15 build the A tile H = tanh(e+p) in bf16, K-major SWIZZLE_128B, 8 k-blocks
 //   warp  0     TMA-loads W_out tiles [256 vocab rows x 64 k] (bf16) into a 3-stage ring
 //   warp  1     one thread issues tcgen05.mma (M=128, N=256, K=16), two TMEM accumulators
-//   warps 4-7   epilogue, one thread per cell row, tcgen05.ld 32 columns at a time:
+//   warps 4-11  epilogue: two warps per TMEM lane quarter (= two per SM sub-partition, so one
+//               hides the other's TMEM / MUFU latency), each thread owns one cell row and
+//               half of the 256 columns of every N tile, tcgen05.ld 32 columns at a time:
 //     MODE_FWD   online (max, sum-exp) over V, picks the blank and target logits
 //                -> lse, lp_blank, lp_emit  (3 floats per cell leave the CTA)
 //     MODE_GRAD  G = scale*(exp(x+c0) - [v==blank]exp(x+cb) - [v==y]exp(x+ce)) in bf16 into a
@@ -33,9 +35,13 @@ constexpr int kStages = 3;
 constexpr int kABlockBytes = kTileM * kBlockK * 2;   // 16 KB per k-block
 constexpr int kABytes = kMaxKB * kABlockBytes;       // 128 KB
 constexpr int kWStageBytes = kTileN * kBlockK * 2;   // 32 KB
-constexpr int kThreads = 384;
+constexpr int kThreads = 512;
+constexpr int kEpiThreads = 256;   // warps 4..11
+constexpr int kBuilderWarp0 = 12;  // warps 12..15
 constexpr int kTmemCols = 512;
-constexpr int kSmemBytes = kABytes + kStages * kWStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int kXchgBytes = kTileM * 3 * 4;  // forward statistics handed between column halves
+constexpr int kSmemBytes =
+    kABytes + kStages * kWStageBytes + 1024 /*align*/ + 256 /*barriers*/ + kXchgBytes;
 
 enum { MODE_FWD = 0, MODE_GRAD = 1 };
 
@@ -90,6 +96,7 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
   const uint32_t sA = base;
   const uint32_t sW = base + kABytes;
   Barriers* bars = reinterpret_cast<Barriers*>(smem + kABytes + kStages * kWStageBytes);
+  float* xchg = reinterpret_cast<float*>(smem + kABytes + kStages * kWStageBytes + 256);
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int nkb = P.J / kBlockK;
@@ -103,7 +110,7 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
     }
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(ptx::smem_u32(&bars->tmem_full[i]), 1);
-      ptx::mbar_init(ptx::smem_u32(&bars->tmem_empty[i]), 128);
+      ptx::mbar_init(ptx::smem_u32(&bars->tmem_empty[i]), kEpiThreads);
     }
     for (int i = 0; i < kMaxKB; ++i) {
       ptx::mbar_init(ptx::smem_u32(&bars->a_ready[i]), 4);
@@ -172,9 +179,9 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
       }
     }
     __syncwarp();
-  } else if (warp >= 8) {
+  } else if (warp >= kBuilderWarp0) {
     // ===================== A-tile builders: H = tanh(e + p) -> bf16, swizzled =====================
-    const int bw = warp - 8;       // rows bw*32 .. bw*32+31
+    const int bw = warp - kBuilderWarp0;  // rows bw*32 .. bw*32+31
     const int rr = lane >> 3;      // row within a group of 4
     const int cc = lane & 7;       // 16-byte chunk within the 128-byte row
     int it = 0;

@@ -31,7 +31,21 @@ from ._lib import i32, ptr
 from .rnnt import rnnt_grad_coef, rnnt_lattice
 
 _TILE_N = 256
-CHUNK_CELLS = 1 << 16  # scratch bound for the backward pass (cells per chunk, whole utterances)
+_TILE_M = 128
+SCRATCH_BYTES = 2 << 30  # bound on the bf16 G scratch of the backward pass
+
+
+def _chunk_utts(B: int, per_utt: int, ldg: int, sms: int) -> int:
+    """Utterances per backward chunk: whole utterances, G scratch <= SCRATCH_BYTES, and as
+    few idle SMs in the last wave of 128-cell tiles as possible."""
+    cap = max(1, min(B, SCRATCH_BYTES // (per_utt * ldg * 2)))
+    best, best_eff = 1, 0.0
+    for nb in range(1, cap + 1):
+        tiles = -(-nb * per_utt // _TILE_M)
+        eff = tiles / (sms * -(-tiles // sms))
+        if eff > best_eff + 1e-3:
+            best, best_eff = nb, eff
+    return best
 
 
 def _i64(v):
@@ -93,15 +107,16 @@ class _FusedJointLossFn(torch.autograd.Function):
             coef = rnnt_grad_coef(lse, alpha, beta, diag_off, dyf, targets, logit_lengths,
                                   target_lengths, blank)
             per_utt = T * U1
-            nb = max(1, min(B, CHUNK_CELLS // per_utt))
-            ldg = (V + 7) // 8 * 8
+            ldg = (V + 15) // 16 * 16  # 32-byte rows: the epilogue stores 32 bytes per thread
             ldh = J + 8
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            nb = _chunk_utts(B, per_utt, ldg, sms)
             G = torch.empty(nb * per_utt, ldg, dtype=torch.bfloat16, device=dev)
             H = torch.zeros(nb * per_utt, ldh, dtype=torch.bfloat16, device=dev)
             H[:, J] = 1.0  # ones column: d b_out falls out of the dW GEMM
             dW_aug = torch.zeros(V, ldh, dtype=torch.float32, device=dev)
             de = torch.empty(B, T, J, dtype=torch.float32, device=dev)
-            dp = torch.empty(B, U1, J, dtype=torch.float32, device=dev)
+            dp = torch.zeros(B, U1, J, dtype=torch.float32, device=dev)
             for b0 in range(0, B, nb):
                 b1 = min(B, b0 + nb)
                 n = (b1 - b0) * per_utt
@@ -112,10 +127,8 @@ class _FusedJointLossFn(torch.autograd.Function):
                 Gv = G[:n, :V]
                 dH = torch.mm(Gv, w_bf16, out_dtype=torch.float32)        # [n, J]
                 dW_aug += torch.mm(Gv.t(), H[:n], out_dtype=torch.float32)  # [V, J+8]
-                h = H[:n, :J].float()
-                dz = (dH * (1.0 - h * h)).view(b1 - b0, T, U1, J)
-                de[b0:b1] = dz.sum(2)
-                dp[b0:b1] = dz.sum(1)
+                _lib.call("b200_joint_dz_reduce", ptr(dH), ptr(H), i32(ldh), i32(b1 - b0), i32(T),
+                          i32(U1), i32(J), ptr(de[b0:b1]), ptr(dp[b0:b1]), st)
         dt_e, dt_p, dt_w, dt_b = ctx.in_dtypes
         return (de.to(dt_e), dp.to(dt_p), dW_aug[:, :J].to(dt_w), dW_aug[:, J].to(dt_b), None, None,
                 None, None)
