@@ -163,6 +163,25 @@ int b200_joint_grad_chunk(const float* e, const float* p, const void* w_bf16,
 int b200_joint_dz_reduce(const float* dH, const void* H, int ldh, int nb, int T, int U1, int J,
                          float* de, float* dp, b200_stream_t stream);
 
+/* ---- Batched RNN-T greedy search ------------------------------------------
+ * replaces the Python loop of wenet/transducer/search/greedy_search.py:34-176 (core
+ * algorithm: "greedy_search copy.py":6-63): per lattice step predictor.forward_step
+ * (predictor.py:180-200), joint (joint.py:45-70), log_softmax/argmax, and the host-side
+ * token / frame bookkeeping - for a whole batch, without host round trips.
+ * enc_proj [B,T,J] fp32 = enc_ffn(encoder_out); lens [B]; embed [V,Emb];
+ * lstm = HOST array of 4*L device pointers {w_ih, w_hh, b_ih, b_hh} per layer (PyTorch
+ * nn.LSTM layout, gate order i,f,g,o); w_c [J,H], b_c [J] = pred_ffn o projection;
+ * w_out [V,J], b_out [V] = ffn_out.  tokens [B,max_tokens] / n_tok [B] receive the
+ * hypotheses.  Blocks until every utterance has consumed its frames (the only entry
+ * point that synchronises the stream: termination is data dependent). */
+size_t b200_greedy_workspace_bytes(int B, int V, int H, int L, int J);
+int b200_rnnt_greedy(const float* enc_proj, const int32_t* lens, int B, int T,
+                     const float* embed, const float* const* lstm,
+                     const float* w_c, const float* b_c, const float* w_out, const float* b_out,
+                     int V, int Emb, int H, int L, int J, int blank, int n_steps,
+                     int32_t* tokens, int32_t* n_tok, int max_tokens,
+                     void* workspace, size_t ws_bytes, int* rounds_out, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -79,6 +79,8 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+constexpr int kLag = 4;  // lattice steps between rescalings (power of two)
+
 // Lagged block maximum for the rescaled lattices: at step i every warp publishes the max
 // of the values it just produced (before the step's __syncthreads); at step i+1 all
 // threads read the other parity slot.  No extra barrier.  red = [2][32] floats.

@@ -134,7 +134,7 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
       }
       lagged_max_write(v, red, 0);
     }
-    int it = 1;
+    int it = kLag;
     if (s == 0) offs[0] = 0.0;
     __syncthreads();
     float r[kCtcPf];
@@ -154,10 +154,13 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
           float v = -INFINITY;
           if (mine) v = lae3(prev[s], prev[s - 1], skip_ok ? prev[s - 2] : -INFINITY) + r[k];
           {  // pull the previous frame's maximum into the fp64 offset (no extra barrier)
-            const float M = lagged_max_read(red, (it - 1) & 1);
-            v -= M;
-            run += (double)M;
-            lagged_max_write(v, red, it & 1);
+            // every kLag-th step: subtract the maximum published kLag steps ago
+            if ((it & (kLag - 1)) == 0) {
+              const float M = lagged_max_read(red, ((it / kLag) - 1) & 1);
+              v -= M;
+              run += (double)M;
+              lagged_max_write(v, red, (it / kLag) & 1);
+            }
             ++it;
           }
           if (mine) {
@@ -193,7 +196,7 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
       }
       lagged_max_write(v, red, 0);
     }
-    int it = 1;
+    int it = kLag;
     if (s == 0) offs[Tb - 1] = 0.0;
     __syncthreads();
     float r[kCtcPf];
@@ -216,10 +219,13 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
           float v = -INFINITY;
           if (mine) v = lae3(prev[s], prev[s + 1], skip_ok ? prev[s + 2] : -INFINITY) + r[k];
           {
-            const float M = lagged_max_read(red, (it - 1) & 1);
-            v -= M;
-            run += (double)M;
-            lagged_max_write(v, red, it & 1);
+            // every kLag-th step: subtract the maximum published kLag steps ago
+            if ((it & (kLag - 1)) == 0) {
+              const float M = lagged_max_read(red, ((it / kLag) - 1) & 1);
+              v -= M;
+              run += (double)M;
+              lagged_max_write(v, red, (it / kLag) & 1);
+            }
             ++it;
           }
           if (mine) {

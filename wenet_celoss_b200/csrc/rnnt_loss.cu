@@ -111,7 +111,7 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
       offs[0] = 0.0;
     }
     lagged_max_write(u == 0 ? 0.f : -INFINITY, red, 0);
-    int it = 1;
+    int it = kLag;
     __syncthreads();
     float* prev = buf0;
     float* cur = buf1;
@@ -140,10 +140,13 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
           float v = -INFINITY;
           if (live) v = log_add_exp(prev[u] + rb[k], prev[u - 1] + re[k]);
           {
-            const float M = lagged_max_read(red, (it - 1) & 1);
-            v -= M;
-            run += (double)M;
-            lagged_max_write(v, red, it & 1);
+            // every kLag-th step: subtract the maximum published kLag steps ago
+            if ((it & (kLag - 1)) == 0) {
+              const float M = lagged_max_read(red, ((it / kLag) - 1) & 1);
+              v -= M;
+              run += (double)M;
+              lagged_max_write(v, red, (it / kLag) & 1);
+            }
             ++it;
           }
           if (mine) cur[u] = v;
@@ -177,7 +180,7 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
       }
     }
     lagged_max_write(u == Ub ? lpb[(long long)(Tb - 1) * U1 + Ub] : -INFINITY, red, 0);
-    int it = 1;
+    int it = kLag;
     __syncthreads();
     float rb[kPf], re[kPf];
     auto fetch = [&](int d, float& vb, float& ve) {
@@ -204,10 +207,13 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
           float v = -INFINITY;
           if (live) v = log_add_exp(prev[u] + rb[k], prev[u + 1] + re[k]);
           {
-            const float M = lagged_max_read(red, (it - 1) & 1);
-            v -= M;
-            run += (double)M;
-            lagged_max_write(v, red, it & 1);
+            // every kLag-th step: subtract the maximum published kLag steps ago
+            if ((it & (kLag - 1)) == 0) {
+              const float M = lagged_max_read(red, ((it / kLag) - 1) & 1);
+              v -= M;
+              run += (double)M;
+              lagged_max_write(v, red, (it / kLag) & 1);
+            }
             ++it;
           }
           if (mine) cur[u] = v;

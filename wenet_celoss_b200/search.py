@@ -1,0 +1,108 @@
+"""Batched RNN-T greedy search (and, below, prefix beam search) on the device.
+
+Mirrors the reference entry points
+  wenet/transducer/search/greedy_search.py:34   basic_greedy_search(model, encoder_out, encoder_out_lens, ..., n_steps=64)
+  wenet/transducer/search/greedy_search copy.py:6 (the same algorithm without hot-word gating)
+and adds the batched form the reference lacks (it asserts batch == 1,
+wenet/transducer/transducer.py:545): ``greedy_search_batch(model, encoder_out [B,T,E],
+encoder_out_lens [B])`` returns B token lists.  ``model`` is anything exposing what the
+reference functions read: ``model.predictor`` (``embed``, ``rnn`` = nn.LSTM, ``projection``),
+``model.joint`` (``enc_ffn``, ``pred_ffn``, ``ffn_out``) and ``model.blank``.
+
+The hot-word gate / "go-back" of the fork (greedy_search.py:100-144) is out of scope
+(SURVEY.md §8f rank 1); ``context_filter_state='on'`` raises.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List
+
+import torch
+
+from . import _lib
+from ._lib import i32, ptr
+
+
+def _model_tensors(model):
+    pred, joint = model.predictor, model.joint
+    rnn = getattr(pred, "rnn", None)
+    if not isinstance(rnn, torch.nn.LSTM) or rnn.bidirectional or not rnn.bias or rnn.proj_size != 0:
+        raise NotImplementedError("device search implements the LSTM RNNPredictor only "
+                                  "(wenet/transducer/predictor.py:58-200, rnn_type='lstm')")
+    for name in ("enc_ffn", "pred_ffn", "ffn_out"):
+        if getattr(joint, name, None) is None:
+            raise NotImplementedError(f"device search needs joint.{name} (prejoin_linear=True)")
+    f32 = lambda t: t.detach().to(torch.float32).contiguous()
+    L, H = rnn.num_layers, rnn.hidden_size
+    lstm = []
+    for l in range(L):
+        lstm += [f32(getattr(rnn, f"weight_ih_l{l}")), f32(getattr(rnn, f"weight_hh_l{l}")),
+                 f32(getattr(rnn, f"bias_ih_l{l}")), f32(getattr(rnn, f"bias_hh_l{l}"))]
+    # projection followed by pred_ffn has no non-linearity in between: compose once in fp64
+    wp, bp = pred.projection.weight.detach().double(), pred.projection.bias.detach().double()
+    wf, bf = joint.pred_ffn.weight.detach().double(), joint.pred_ffn.bias.detach().double()
+    w_c = (wf @ wp).to(torch.float32).contiguous()
+    b_c = (wf @ bp + bf).to(torch.float32).contiguous()
+    return dict(embed=f32(pred.embed.weight), lstm=lstm, w_c=w_c, b_c=b_c,
+                w_out=f32(joint.ffn_out.weight), b_out=f32(joint.ffn_out.bias), L=L, H=H,
+                Emb=pred.embed.weight.shape[1], J=joint.ffn_out.in_features,
+                V=joint.ffn_out.out_features)
+
+
+def _enc_proj(model, encoder_out: torch.Tensor) -> torch.Tensor:
+    """enc_ffn(encoder_out) in full fp32 (one library GEMM, joint.py:55)."""
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        w, b = model.joint.enc_ffn.weight, model.joint.enc_ffn.bias
+        return torch.nn.functional.linear(encoder_out.float(), w.float(), b.float()).contiguous()
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+
+
+@torch.no_grad()
+def greedy_search_batch(model, encoder_out: torch.Tensor, encoder_out_lens: torch.Tensor,
+                        n_steps: int = 64, return_rounds: bool = False):
+    """Greedy RNN-T decode of a batch: encoder_out [B,T,E] -> B lists of token ids."""
+    _lib.require_cuda(encoder_out, "encoder_out")
+    if encoder_out.dim() != 3:
+        raise RuntimeError("encoder_out must be 3-D (batch, time, dim)")
+    dev = encoder_out.device
+    B, T, _ = encoder_out.shape
+    m = _model_tensors(model)
+    with torch.cuda.device(dev):
+        lens = encoder_out_lens.reshape(-1).to(device=dev, dtype=torch.int32).clamp(max=T).contiguous()
+        if lens.numel() != B:
+            raise RuntimeError("encoder_out_lens must have one entry per utterance")
+        enc_proj = _enc_proj(model, encoder_out)
+        max_tokens = int(min(T * n_steps, 1 << 20))
+        tokens = torch.empty(B, max_tokens, dtype=torch.int32, device=dev)
+        n_tok = torch.zeros(B, dtype=torch.int32, device=dev)
+        L_ = _lib.lib()
+        L_.b200_greedy_workspace_bytes.restype = ctypes.c_size_t
+        ws_bytes = L_.b200_greedy_workspace_bytes(B, m["V"], m["H"], m["L"], m["J"])
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        ptrs = (ctypes.c_void_p * (4 * m["L"]))(*[t.data_ptr() for t in m["lstm"]])
+        rounds = ctypes.c_int(0)
+        _lib.call("b200_rnnt_greedy", ptr(enc_proj), ptr(lens), i32(B), i32(T), ptr(m["embed"]), ptrs,
+                  ptr(m["w_c"]), ptr(m["b_c"]), ptr(m["w_out"]), ptr(m["b_out"]), i32(m["V"]),
+                  i32(m["Emb"]), i32(m["H"]), i32(m["L"]), i32(m["J"]), i32(int(model.blank)),
+                  i32(n_steps), ptr(tokens), ptr(n_tok), i32(max_tokens), ptr(ws),
+                  ctypes.c_size_t(ws_bytes), ctypes.byref(rounds), _lib.stream_handle(dev))
+        n_host = n_tok.cpu().tolist()  # one D2H copy of the results at the end
+        width = max(n_host) if n_host else 0
+        tok_host = tokens[:, :max(width, 1)].cpu().tolist()
+    hyps = [tok_host[b][:min(n_host[b], max_tokens)] for b in range(B)]
+    return (hyps, rounds.value) if return_rounds else hyps
+
+
+def basic_greedy_search(model, encoder_out: torch.Tensor, encoder_out_lens, context_list=None,
+                        context_lengths=None, n_steps: int = 64, context_filter_state: str = "off",
+                        context_decoder_labels_padded=None) -> List[List[int]]:
+    """Single-utterance entry point with the reference's argument order; returns ``[hyps]``."""
+    if context_filter_state == "on":
+        raise NotImplementedError("hot-word gated decoding (greedy_search.py:100-144) is out of scope")
+    if encoder_out.size(0) != 1:
+        raise RuntimeError("basic_greedy_search takes one utterance; use greedy_search_batch")
+    lens = torch.as_tensor(encoder_out_lens).reshape(-1)[:1]
+    return [greedy_search_batch(model, encoder_out, lens, n_steps=n_steps)[0]]
