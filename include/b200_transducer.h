@@ -182,6 +182,24 @@ int b200_rnnt_greedy(const float* enc_proj, const int32_t* lens, int B, int T,
                      int32_t* tokens, int32_t* n_tok, int max_tokens,
                      void* workspace, size_t ws_bytes, int* rounds_out, b200_stream_t stream);
 
+/* ---- Batched RNN-T prefix beam search ---------------------------------------
+ * replaces PrefixBeamSearch.prefix_beam_search (wenet/transducer/search/
+ * prefix_beam_search.py:42-148) for a batch: per frame predictor step + joint + log_softmax
+ * on every live hypothesis, CTC shallow fusion (:99-101), top-k (:104), N*N expansion
+ * (:108-127), prefix merge with fp64 log_add (:130-142), stable sort + prune (:145-146).
+ * ctc_lp [B,T,V] fp32 = CTC.log_softmax(encoder_out) (ctc.py:66-74); other operands as for
+ * b200_rnnt_greedy.  beam <= 16.  Outputs: out_hyp [B,beam,T+2] (each hypothesis starts
+ * with the seed blank, padded with -1), out_len [B,beam], out_score [B,beam] fp64,
+ * out_n [B] = hypotheses in the final beam.  Fully asynchronous on the stream. */
+size_t b200_beam_workspace_bytes(int B, int T, int V, int H, int L, int J, int beam);
+int b200_rnnt_beam(const float* enc_proj, const float* ctc_lp, const int32_t* lens, int B, int T,
+                   const float* embed, const float* const* lstm,
+                   const float* w_c, const float* b_c, const float* w_out, const float* b_out,
+                   int V, int Emb, int H, int L, int J, int blank,
+                   int beam, float ctc_weight, float transducer_weight,
+                   int32_t* out_hyp, int32_t* out_len, double* out_score, int32_t* out_n,
+                   void* workspace, size_t ws_bytes, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -64,3 +64,43 @@ def test_greedy_full_dims_vs_oracle():
     for b in range(B):
         assert got[b] == want[b], f"utt {b}: min top-2 margin in the oracle run {margins[b]:.3e}"
     assert rounds >= 40
+
+
+@pytest.mark.parametrize("tag", ["mixed", "degenerate"])
+def test_beam_golden(golden, tag):
+    from wenet_celoss_b200 import prefix_beam_search_batch
+    d = golden(f"search_{tag}")
+    m = load_oracle_model(d).to(DEV)
+    enc = torch.from_numpy(d["enc"]).to(DEV)
+    lens = torch.from_numpy(d["lens"]).to(DEV)
+    K = int(d["beam_size"])
+    beams = prefix_beam_search_batch(m, enc, lens, beam_size=K, ctc_weight=float(d["ctc_weight"]),
+                                     transducer_weight=float(d["transducer_weight"]))
+    for b in range(enc.size(0)):
+        assert len(beams[b]) == d["beam_n"][b]
+        for k, s in enumerate(beams[b]):
+            assert s.hyp[0] == 0 and s.hyp[1:] == _unpad(d["beam_hyps"][b, k]), (tag, b, k)
+            np.testing.assert_allclose(s.score, d["beam_scores"][b, k], rtol=1e-5)
+
+
+def test_beam_full_dims_vs_oracle():
+    from wenet_celoss_b200 import PrefixBeamSearch, prefix_beam_search_batch
+    m = _search_model(600, seed=8)
+    g = torch.Generator().manual_seed(9)
+    B, T = 3, 24
+    enc = torch.randn(B, T, 256, generator=g) * 2.0
+    lens = torch.tensor([24, 17, 24])
+    md = copy.deepcopy(m).to(DEV)
+    beams = prefix_beam_search_batch(md, enc.to(DEV), lens.to(DEV), beam_size=10)
+    for b in range(B):
+        want = orc.prefix_beam_search(m, enc[b:b + 1, :lens[b]], beam_size=10)
+        assert [s.hyp for s in beams[b]] == [s.hyp for s in want], b
+        np.testing.assert_allclose([s.score for s in beams[b]], [s.score for s in want], rtol=1e-5)
+
+    class Enc(torch.nn.Module):  # pass-through encoder, as in oracle/gen_golden.py
+        def forward(self, xs, lens, chunk=-1, left=-1):
+            return xs, None
+    bs = PrefixBeamSearch(Enc(), md.predictor, md.joint, md.ctc, 0)
+    beam, enc_out = bs.prefix_beam_search(enc[0:1].to(DEV), torch.tensor([T]), beam_size=10)
+    want = orc.prefix_beam_search(m, enc[0:1], beam_size=10)
+    assert beam[0].hyp == want[0].hyp and enc_out.shape == (1, T, 256)

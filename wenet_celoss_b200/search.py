@@ -106,3 +106,82 @@ def basic_greedy_search(model, encoder_out: torch.Tensor, encoder_out_lens, cont
         raise RuntimeError("basic_greedy_search takes one utterance; use greedy_search_batch")
     lens = torch.as_tensor(encoder_out_lens).reshape(-1)[:1]
     return [greedy_search_batch(model, encoder_out, lens, n_steps=n_steps)[0]]
+
+
+# --------------------------------------------------------------------------- prefix beam search
+class Sequence:
+    """Hypothesis record with the reference's fields (prefix_beam_search.py:7-19).  ``hyp``
+    starts with the seed blank; ``cache`` is not populated (callers only read ``hyp`` and
+    ``score``: transducer.py:377,444-445)."""
+    __slots__ = ("hyp", "score", "cache")
+
+    def __init__(self, hyp, score, cache=None):
+        self.hyp, self.score, self.cache = hyp, score, cache
+
+
+@torch.no_grad()
+def prefix_beam_search_batch(model, encoder_out: torch.Tensor, encoder_out_lens: torch.Tensor,
+                             beam_size: int = 10, ctc_weight: float = 0.3,
+                             transducer_weight: float = 0.7) -> List[List[Sequence]]:
+    """RNN-T prefix beam search with CTC shallow fusion for a batch: encoder_out [B,T,E] ->
+    per utterance the final beam (best first), exactly one expansion per frame."""
+    _lib.require_cuda(encoder_out, "encoder_out")
+    dev = encoder_out.device
+    B, T, _ = encoder_out.shape
+    m = _model_tensors(model)
+    with torch.cuda.device(dev):
+        lens = encoder_out_lens.reshape(-1).to(device=dev, dtype=torch.int32).clamp(max=T).contiguous()
+        if lens.numel() != B:
+            raise RuntimeError("encoder_out_lens must have one entry per utterance")
+        enc_proj = _enc_proj(model, encoder_out)
+        prev = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = False
+        try:  # CTC.log_softmax (ctc.py:66-74): library GEMM + log_softmax, once per utterance
+            ctc_lp = model.ctc.log_softmax(encoder_out.float()).float().contiguous()
+        finally:
+            torch.backends.cuda.matmul.allow_tf32 = prev
+        ML = T + 2
+        out_hyp = torch.empty(B, beam_size, ML, dtype=torch.int32, device=dev)
+        out_len = torch.empty(B, beam_size, dtype=torch.int32, device=dev)
+        out_score = torch.empty(B, beam_size, dtype=torch.float64, device=dev)
+        out_n = torch.empty(B, dtype=torch.int32, device=dev)
+        L_ = _lib.lib()
+        L_.b200_beam_workspace_bytes.restype = ctypes.c_size_t
+        ws_bytes = L_.b200_beam_workspace_bytes(B, T, m["V"], m["H"], m["L"], m["J"], beam_size)
+        if ws_bytes == 0:
+            raise _lib.B200Error("b200_beam_workspace_bytes: bad shape")
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        ptrs = (ctypes.c_void_p * (4 * m["L"]))(*[t.data_ptr() for t in m["lstm"]])
+        _lib.call("b200_rnnt_beam", ptr(enc_proj), ptr(ctc_lp), ptr(lens), i32(B), i32(T),
+                  ptr(m["embed"]), ptrs, ptr(m["w_c"]), ptr(m["b_c"]), ptr(m["w_out"]), ptr(m["b_out"]),
+                  i32(m["V"]), i32(m["Emb"]), i32(m["H"]), i32(m["L"]), i32(m["J"]),
+                  i32(int(model.blank)), i32(beam_size), ctypes.c_float(ctc_weight),
+                  ctypes.c_float(transducer_weight), ptr(out_hyp), ptr(out_len), ptr(out_score),
+                  ptr(out_n), ptr(ws), ctypes.c_size_t(ws_bytes), _lib.stream_handle(dev))
+        n = out_n.cpu().tolist()
+        lens_h = out_len.cpu().tolist()
+        scores = out_score.cpu().tolist()
+        width = max(max(r) for r in lens_h) if B else 0
+        hyps = out_hyp[:, :, :max(width, 1)].cpu().tolist()
+    return [[Sequence(hyps[b][k][:lens_h[b][k]], scores[b][k]) for k in range(n[b])] for b in range(B)]
+
+
+class PrefixBeamSearch:
+    """Same constructor and method as the reference class (prefix_beam_search.py:22-148)."""
+
+    def __init__(self, encoder, predictor, joint, ctc, blank):
+        self.encoder, self.predictor, self.joint, self.ctc, self.blank = encoder, predictor, joint, ctc, blank
+
+    def prefix_beam_search(self, speech, speech_lengths, decoding_chunk_size: int = -1,
+                           beam_size: int = 5, num_decoding_left_chunks: int = -1,
+                           simulate_streaming: bool = False, ctc_weight: float = 0.3,
+                           transducer_weight: float = 0.7):
+        assert speech.shape[0] == speech_lengths.shape[0]
+        assert decoding_chunk_size != 0
+        encoder_out, _ = self.encoder(speech, speech_lengths, decoding_chunk_size,
+                                      num_decoding_left_chunks)
+        # the reference runs all maxlen frames of its single utterance (:75)
+        lens = torch.full((encoder_out.size(0),), encoder_out.size(1), dtype=torch.int32)
+        beams = prefix_beam_search_batch(self, encoder_out, lens, beam_size, ctc_weight,
+                                         transducer_weight)
+        return (beams[0] if encoder_out.size(0) == 1 else beams), encoder_out
