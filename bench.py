@@ -444,6 +444,91 @@ class RnntFusedWorkload:
                 "L2 flushed by the step itself: each step streams >16 GB of gradient scratch")
 
 
+# --------------------------------------------------------------------------- other rows of the path
+class _Predictor(torch.nn.Module):
+    """RNNPredictor parameter layout (wenet/transducer/predictor.py:58-86)."""
+
+    def __init__(self, V, emb, out, hidden, layers):
+        super().__init__()
+        self.embed = torch.nn.Embedding(V, emb)
+        self.rnn = torch.nn.LSTM(emb, hidden, layers, batch_first=True)
+        self.projection = torch.nn.Linear(hidden, out)
+
+
+class _SearchModel(torch.nn.Module):
+    def __init__(self, cfg):
+        super().__init__()
+        import wenet_celoss_b200 as pkg
+        V, E, P, J = cfg["V"], cfg["E"], cfg["P"], cfg["J"]
+        self.blank = 0
+        self.predictor = _Predictor(V, 256, P, 256, 2)
+        self.joint = _Joint(V, E, P, J)
+        self.ctc = pkg.CTC(V, E)
+        with torch.no_grad():  # random-init weights emit n_steps symbols per frame (SURVEY 7.3-7):
+            self.joint.ffn_out.weight.mul_(3.0)   # rescale so blank / non-blank steps interleave
+            self.joint.ffn_out.bias[0] += 5.0
+            self.predictor.projection.weight.mul_(16.0)
+            self.predictor.embed.weight.mul_(4.0)
+
+
+def extra_rows(cfg, dev, pk):
+    """Secondary numbers of the same hot path (BASELINE configs 4 and 5), timed with CUDA events."""
+    import wenet_celoss_b200 as pkg
+    out = {}
+    torch.manual_seed(4321)
+    g = torch.Generator().manual_seed(4321)
+
+    def timed(fn, reps=3):
+        fn()
+        ts = []
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+            e0.record()
+            r = fn()
+            e1.record()
+            e1.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        return statistics.median(ts), r
+
+    # cfg4: greedy + beam(10) over synthetic encoder outputs B=64 T=500 V=5000
+    B4, T4 = 64, 500
+    model = _SearchModel(cfg).to(dev).eval()
+    enc = (torch.randn(B4, T4, cfg["E"], generator=g) * 2.0).to(dev)
+    lens = torch.full((B4,), T4, dtype=torch.int32, device=dev)
+    ms, (hyps, rounds) = timed(lambda: pkg.greedy_search_batch(model, enc, lens, n_steps=64,
+                                                               return_rounds=True))
+    ntok = sum(len(h) for h in hyps)
+    out["greedy"] = {"value": B4 / (ms * 1e-3), "unit": "utt/s", "ms": ms, "rounds": rounds,
+                     "symbols_per_frame": ntok / (B4 * T4),
+                     "workload": "cfg4: B=64 T=500 V=5000 greedy, random-init predictor/joint"}
+    ms, beams = timed(lambda: pkg.prefix_beam_search_batch(model, enc, lens, beam_size=10), reps=2)
+    out["beam10"] = {"value": B4 / (ms * 1e-3), "unit": "utt/s", "ms": ms,
+                     "workload": "cfg4: B=64 T=500 V=5000 prefix beam search, beam=10, ctc 0.3 / rnnt 0.7"}
+    # cfg5: CTC module fwd+bwd B=64 T=1000 V=5000
+    B5, T5, L5, V = 64, 1000, 100, cfg["V"]
+    ctc = pkg.CTC(V, cfg["E"]).to(dev)
+    hs = torch.randn(B5, T5, cfg["E"], generator=g).to(dev).requires_grad_(True)
+    yl = torch.randint(50, L5 + 1, (B5,), generator=g)
+    ys = torch.randint(1, V, (B5, L5), generator=g)
+    ys = torch.where(torch.arange(L5)[None] < yl[:, None], ys, torch.full_like(ys, -1)).to(dev)
+    hl = torch.full((B5,), T5, dtype=torch.int32, device=dev)
+    yl = yl.to(dev)
+
+    def ctc_step():
+        hs.grad = None
+        for p_ in ctc.parameters():
+            p_.grad = None
+        l = ctc(hs, hl, ys, yl)
+        l.backward()
+        return l
+    ms, _ = timed(ctc_step, reps=5)
+    out["ctc"] = {"value": B5 / (ms * 1e-3), "unit": "utt/s", "ms": ms,
+                  "frac_of_hbm_roofline_module": 3.0 * B5 * T5 * V * 4 / (ms * 1e-3) / 1e9 / pk["hbm"],
+                  "workload": "cfg5: CTC.forward+backward B=64 T=1000 V=5000 L<=100 fp32 (incl. ctc_lo GEMMs)"}
+    return out
+
+
+
 WORKLOADS = {"rnnt_logits": RnntLogitsWorkload, "rnnt_fused": RnntFusedWorkload}
 
 
@@ -469,6 +554,7 @@ def main():
     ap.add_argument("--workload", default="rnnt_fused", choices=sorted(WORKLOADS))
     ap.add_argument("--ragged", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     cfg = dict(CFG3)
@@ -560,6 +646,11 @@ def main():
             "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cb,
             "clocks": clocks, "loss": float(loss.item()),
         }
+        if not args.no_extras and world == 1:
+            try:
+                line["extra"] = extra_rows(cfg, wl.dev, pk)
+            except Exception as exc:  # secondary rows never hide the headline
+                line["extra"] = {"error": repr(exc)}
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()

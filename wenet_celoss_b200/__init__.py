@@ -5,6 +5,11 @@ Public surface mirrors the reference call sites (Vindicator645/wenet-celoss):
       torchaudio.functional.rnnt_loss as used at wenet/transducer/transducer.py:142
   CTC(odim, encoder_output_size).forward(hs_pad, hlens, ys_pad, ys_lens)
       wenet/transformer/ctc.py:46
+  fused_joint_rnnt_loss(joint, enc_out, pred_out, targets, logit_lengths, target_lengths, blank, reduction)
+      wenet/transducer/transducer.py:132-147 (joint + rnnt_loss without materialised logits)
+  greedy_search_batch / basic_greedy_search, prefix_beam_search_batch / PrefixBeamSearch
+      wenet/transducer/search/greedy_search.py:34, prefix_beam_search.py:42
+  patch_transducer(model)  rebinds Transducer.forward / greedy_search / beam_search
 Everything is backed by libb200_transducer.so (C ABI in include/b200_transducer.h);
 there is no CPU or PyTorch fallback.
 """
@@ -13,6 +18,7 @@ from .ctc import CTC, ctc_loss, patch_ctc  # noqa: F401
 from .joint import fused_joint_rnnt_loss, joint_logprobs  # noqa: F401
 from .search import (PrefixBeamSearch, Sequence, basic_greedy_search,  # noqa: F401
                      greedy_search_batch, prefix_beam_search_batch)
+from .transducer import add_blank, patch_transducer, rnnt_targets  # noqa: F401
 from .rnnt import rnnt_grad_coef, rnnt_lattice, rnnt_loss  # noqa: F401
 
-__all__ = ["prefix_beam_search_batch", "PrefixBeamSearch", "Sequence", "greedy_search_batch", "basic_greedy_search", "fused_joint_rnnt_loss", "CTC", "ctc_loss", "patch_ctc", "rnnt_loss", "rnnt_lattice", "rnnt_grad_coef", "B200Error", "lib", "launch_count"]
+__all__ = ["patch_transducer", "add_blank", "rnnt_targets", "prefix_beam_search_batch", "PrefixBeamSearch", "Sequence", "greedy_search_batch", "basic_greedy_search", "fused_joint_rnnt_loss", "CTC", "ctc_loss", "patch_ctc", "rnnt_loss", "rnnt_lattice", "rnnt_grad_coef", "B200Error", "lib", "launch_count"]

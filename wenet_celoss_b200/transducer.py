@@ -1,0 +1,147 @@
+"""Model-level drop-in for the reference ``Transducer`` (wenet/transducer/transducer.py).
+
+``patch_transducer(model)`` rebinds, on an existing reference ``Transducer`` instance (or
+any module with ``encoder``, ``predictor``, ``joint``, ``ctc``, ``blank``, ...), the methods
+on the hot path to their sm_100a versions and leaves everything else untouched:
+
+  forward               transducer.py:79-270   same signature, same loss dict keys
+                        ``loss, loss_att, loss_ctc, loss_rnnt, hw_loss``; joint + rnnt_loss
+                        (:132-147) -> fused_joint_rnnt_loss, self.ctc(...) (:159) -> CTC kernels
+  greedy_search         transducer.py:515-598  batched (the reference asserts batch == 1)
+  beam_search           transducer.py:332-377  returns (hyp, score) of the best hypothesis
+  _cal_transducer_score transducer.py:277-302  -cost per hypothesis, forward only
+
+Out of scope and kept as in the reference object: encoder, attention decoder
+(``_calc_att_loss``), context biasing (called exactly where the reference calls it, so an
+identity or a real ``ContextBias`` both work) and the hot-word CE loss (``hw_weight`` must be
+0: SURVEY.md §8f rank 1).
+"""
+from __future__ import annotations
+
+import types
+from typing import Dict, Optional
+
+import torch
+
+from .ctc import patch_ctc
+from .joint import fused_joint_rnnt_loss
+from .search import greedy_search_batch, prefix_beam_search_batch
+
+IGNORE_ID = -1
+
+
+def add_blank(ys_pad: torch.Tensor, blank: int, ignore_id: int) -> torch.Tensor:
+    """[B,L] -> [B,L+1]: blank prepended, padding replaced by blank (wenet/utils/common.py:56-87)."""
+    head = torch.full((ys_pad.size(0), 1), blank, dtype=ys_pad.dtype, device=ys_pad.device)
+    out = torch.cat([head, ys_pad], dim=1)
+    return torch.where(out == ignore_id, torch.full_like(out, blank), out)
+
+
+def rnnt_targets(text: torch.Tensor, text_lengths: torch.Tensor, encoder_out_lens: torch.Tensor,
+                 ignore_id: int = IGNORE_ID):
+    """The int32 / zero-padded views torchaudio wants (transducer.py:137-141)."""
+    t = text.to(torch.int64)
+    t = torch.where(t == ignore_id, torch.zeros_like(t), t).to(torch.int32).contiguous()
+    return t, encoder_out_lens.to(torch.int32).contiguous(), text_lengths.to(torch.int32).contiguous()
+
+
+def _bias(model, name, *args):
+    cb = getattr(model, "context_bias", None)
+    if cb is None:
+        return None
+    return getattr(cb, name)(*args)
+
+
+def transducer_forward(self, speech: torch.Tensor, speech_lengths: torch.Tensor, text: torch.Tensor,
+                       text_lengths: torch.Tensor, context_list=None, context_lengths=None,
+                       hw_label=None) -> Dict[str, Optional[torch.Tensor]]:
+    assert text_lengths.dim() == 1, text_lengths.shape
+    assert (speech.shape[0] == speech_lengths.shape[0] == text.shape[0] == text_lengths.shape[0]), (
+        speech.shape, speech_lengths.shape, text.shape, text_lengths.shape)
+    if getattr(self, "hw_weight", 0.0) not in (0, 0.0):
+        raise NotImplementedError("hw_loss (transducer.py:170-262) is out of scope: set hw_weight=0")
+    ignore_id = getattr(self, "ignore_id", IGNORE_ID)
+    bias_hidden = _bias(self, "forward_bias_hidden", context_list, context_lengths)
+    encoder_out, encoder_mask = self.encoder(speech, speech_lengths)
+    encoder_out_lens = encoder_mask.squeeze(1).sum(1)
+    if getattr(self, "context_bias", None) is not None:
+        encoder_out, _ = self.context_bias.forward_encoder_bias(bias_hidden, encoder_out)
+    ys_in_pad = add_blank(text, self.blank, ignore_id)
+    predictor_out = self.predictor(ys_in_pad)
+    if getattr(self, "context_bias", None) is not None:
+        predictor_out, _ = self.context_bias.forward_predictor_bias(bias_hidden, predictor_out)
+    rnnt_text, enc_lens32, text_lens32 = rnnt_targets(text, text_lengths, encoder_out_lens, ignore_id)
+    loss = fused_joint_rnnt_loss(self.joint, encoder_out, predictor_out, rnnt_text, enc_lens32,
+                                 text_lens32, blank=self.blank, reduction="mean")
+    loss_rnnt = loss
+    loss = self.transducer_weight * loss
+    loss_att: Optional[torch.Tensor] = None
+    if getattr(self, "attention_decoder_weight", 0.0) != 0.0 and getattr(self, "decoder", None) is not None:
+        loss_att, _ = self._calc_att_loss(encoder_out, encoder_mask, text, text_lengths)
+    loss_ctc: Optional[torch.Tensor] = None
+    if self.ctc_weight != 0.0 and self.ctc is not None:
+        loss_ctc = self.ctc(encoder_out, enc_lens32, text, text_lengths)
+    if loss_ctc is not None:
+        loss = loss + self.ctc_weight * loss_ctc.sum()
+    if loss_att is not None:
+        loss = loss + self.attention_decoder_weight * loss_att.sum()
+    return {"loss": loss, "loss_att": loss_att, "loss_ctc": loss_ctc, "loss_rnnt": loss_rnnt,
+            "hw_loss": None}
+
+
+@torch.no_grad()
+def transducer_score(self, encoder_out: torch.Tensor, encoder_mask: torch.Tensor,
+                     hyps_lens: torch.Tensor, hyps_pad: torch.Tensor) -> torch.Tensor:
+    ignore_id = getattr(self, "ignore_id", IGNORE_ID)
+    hyps_pad_blank = add_blank(hyps_pad, self.blank, ignore_id)
+    xs_in_lens = encoder_mask.squeeze(1).sum(1).int()
+    predictor_out = self.predictor(hyps_pad_blank)
+    rnnt_text, xs32, hl32 = rnnt_targets(hyps_pad, hyps_lens, xs_in_lens, ignore_id)
+    cost = fused_joint_rnnt_loss(self.joint, encoder_out, predictor_out, rnnt_text, xs32, hl32,
+                                 blank=self.blank, reduction="none")
+    return cost * -1
+
+
+@torch.no_grad()
+def transducer_greedy_search(self, speech: torch.Tensor, speech_lengths: torch.Tensor,
+                             decoding_chunk_size: int = -1, num_decoding_left_chunks: int = -1,
+                             simulate_streaming: bool = False, n_steps: int = 64, **_unused):
+    """Batched greedy decode: returns one token list per utterance."""
+    assert speech.shape[0] == speech_lengths.shape[0]
+    assert decoding_chunk_size != 0
+    encoder_out, encoder_mask = self.encoder(speech, speech_lengths, decoding_chunk_size,
+                                             num_decoding_left_chunks)
+    encoder_out_lens = encoder_mask.squeeze(1).sum(1)
+    if getattr(self, "context_bias", None) is not None and _unused.get("context_list") is not None:
+        bias_hidden = self.context_bias.forward_bias_hidden(_unused["context_list"],
+                                                            _unused.get("context_lengths"))
+        encoder_out, _ = self.context_bias.forward_encoder_bias(bias_hidden, encoder_out)
+    return greedy_search_batch(self, encoder_out, encoder_out_lens, n_steps=n_steps)
+
+
+@torch.no_grad()
+def transducer_beam_search(self, speech: torch.Tensor, speech_lengths: torch.Tensor,
+                           decoding_chunk_size: int = -1, beam_size: int = 5,
+                           num_decoding_left_chunks: int = -1, simulate_streaming: bool = False,
+                           ctc_weight: float = 0.3, transducer_weight: float = 0.7):
+    """(best hyp without the seed blank, score), as transducer.py:377; a batch returns a list."""
+    encoder_out, encoder_mask = self.encoder(speech, speech_lengths, decoding_chunk_size,
+                                             num_decoding_left_chunks)
+    lens = encoder_mask.squeeze(1).sum(1)
+    beams = prefix_beam_search_batch(self, encoder_out, lens, beam_size, ctc_weight, transducer_weight)
+    out = [(b[0].hyp[1:], b[0].score) for b in beams]
+    return out[0] if len(out) == 1 else out
+
+
+def patch_transducer(model: torch.nn.Module) -> torch.nn.Module:
+    """Rebind the hot-path methods of a reference ``Transducer`` instance in place."""
+    for attr in ("encoder", "predictor", "joint", "blank"):
+        if not hasattr(model, attr):
+            raise TypeError(f"patch_transducer expects a Transducer-like module (missing .{attr})")
+    if getattr(model, "ctc", None) is not None:
+        patch_ctc(model.ctc)
+    model.forward = types.MethodType(transducer_forward, model)
+    model._cal_transducer_score = types.MethodType(transducer_score, model)
+    model.greedy_search = types.MethodType(transducer_greedy_search, model)
+    model.beam_search = types.MethodType(transducer_beam_search, model)
+    return model
