@@ -35,10 +35,12 @@ class TinyTransducer(torch.nn.Module):
 
 def _model(V=200, seed=0):
     torch.manual_seed(seed)
-    om = orc.OracleModel(V, 32, 32, 64, 32, 32, 2, blank=0).eval()
+    om = orc.OracleModel(V, 32, 32, 64, 32, 32, 2, blank=0)
+    om.predictor.dropout.p = 0.0   # training mode (cuDNN LSTM backward needs it) without noise
+    om.predictor.rnn.dropout = 0.0
     with torch.no_grad():
         om.joint.ffn_out.weight.mul_(3.0)
-    return om
+    return om.train()
 
 
 def test_forward_loss_dict_and_grads():
