@@ -389,8 +389,15 @@ class RnntFusedWorkload:
         def k_fwd():
             box["lat"] = joint_logprobs(e, p, w, bias, self.targets, self.tl, self.ul, V, 0)
 
+        lat_out = [torch.empty(B, T, U1, device=self.dev), torch.empty(B, T, U1, device=self.dev),
+                   torch.empty(B, device=self.dev),
+                   torch.empty(B, 2, T + U1, dtype=torch.float64, device=self.dev)]
+
         def k_lat():
-            box["ab"] = rnnt_lattice(box["lat"][1], box["lat"][2], self.tl, self.ul)
+            _lib.call("b200_rnnt_lattice", ptr(box["lat"][1]), ptr(box["lat"][2]), ptr(self.tl),
+                      ptr(self.ul), i32(B), i32(T), i32(U1), ptr(lat_out[0]), ptr(lat_out[1]),
+                      ptr(lat_out[2]), ptr(lat_out[3]), st)
+            box["ab"] = lat_out
 
         per_utt = T * U1
         ldg, ldh = (V + 15) // 16 * 16, J + 8

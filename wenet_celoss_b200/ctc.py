@@ -121,7 +121,9 @@ class CTC(torch.nn.Module):
 def patch_ctc(module: torch.nn.Module) -> torch.nn.Module:
     """Swap the forward of an existing reference ``CTC`` instance (anything with
     ``ctc_lo`` and ``dropout_rate``) for the sm_100a path; parameters untouched."""
-    if not hasattr(module, "ctc_lo") or not hasattr(module, "dropout_rate"):
-        raise TypeError("patch_ctc expects a wenet CTC module (ctc_lo, dropout_rate)")
+    if not hasattr(module, "ctc_lo"):
+        raise TypeError("patch_ctc expects a wenet CTC module (ctc_lo)")
+    if not hasattr(module, "dropout_rate"):
+        module.dropout_rate = 0.0  # the reference default (ctc.py:26)
     module.forward = types.MethodType(_ctc_forward, module)
     return module
