@@ -130,52 +130,61 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
-      int stage = 0, ph = 0;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
-        for (int n = 0; n < NT; ++n)
-          for (int kb = 0; kb < nkb; ++kb) {
-            ptx::mbar_wait(ptx::smem_u32(&bars->empty[stage]), ph ^ 1);
+    // The whole warp walks the loop (warp-uniform control flow keeps every operand in
+    // uniform registers); one elected lane issues.
+    const bool leader = ptx::elect_one();
+    int stage = 0, ph = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
+      for (int n = 0; n < NT; ++n)
+        for (int kb = 0; kb < nkb; ++kb) {
+          ptx::mbar_wait(ptx::smem_u32(&bars->empty[stage]), ph ^ 1);
+          if (leader) {
             const uint32_t fb = ptx::smem_u32(&bars->full[stage]);
             ptx::mbar_arrive_expect_tx(fb, kWStageBytes);
             ptx::tma_load_2d(sW + stage * kWStageBytes, &w_map, fb, kb * kBlockK, n * kTileN);
-            if (++stage == kStages) {
-              stage = 0;
-              ph ^= 1;
-            }
           }
-    }
+          if (++stage == kStages) {
+            stage = 0;
+            ph ^= 1;
+          }
+        }
     __syncwarp();
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(kTileM, kTileN);
-      int stage = 0, ph = 0, acc = 0, acc_ph = 0, it = 0;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        for (int n = 0; n < NT; ++n) {
-          ptx::mbar_wait(ptx::smem_u32(&bars->tmem_empty[acc]), acc_ph ^ 1);
+    // Warp-uniform loop, one elected lane issues: with the loop inside `if (lane == 0)` the
+    // compiler could not prove the descriptors uniform and wrapped every tcgen05.mma in an
+    // ELECT / BRA.U.ANY waterfall (~85 instructions per 4 MMAs: the issue thread, not the
+    // tensor pipe, paced the kernel -- profiles/README.md).
+    const bool leader = ptx::elect_one();
+    constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(kTileM, kTileN);
+    const uint64_t desc_hi = ptx::make_sw128_kmajor_desc(0);
+    int stage = 0, ph = 0, acc = 0, acc_ph = 0, it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      for (int n = 0; n < NT; ++n) {
+        ptx::mbar_wait(ptx::smem_u32(&bars->tmem_empty[acc]), acc_ph ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem + acc * kTileN;
+        for (int kb = 0; kb < nkb; ++kb) {
+          if (n == 0) ptx::mbar_wait(ptx::smem_u32(&bars->a_ready[kb]), it & 1);
+          ptx::mbar_wait(ptx::smem_u32(&bars->full[stage]), ph);
           ptx::tc_fence_after();
-          const uint32_t d_tmem = tmem + acc * kTileN;
-          for (int kb = 0; kb < nkb; ++kb) {
-            if (n == 0) ptx::mbar_wait(ptx::smem_u32(&bars->a_ready[kb]), it & 1);
-            ptx::mbar_wait(ptx::smem_u32(&bars->full[stage]), ph);
-            ptx::tc_fence_after();
-            const uint64_t da = ptx::make_sw128_kmajor_desc(sA + kb * kABlockBytes);
-            const uint64_t db = ptx::make_sw128_kmajor_desc(sW + stage * kWStageBytes);
+          if (leader) {
+            const uint64_t da = desc_hi | (uint64_t)(((sA + kb * kABlockBytes) & 0x3FFFF) >> 4);
+            const uint64_t db = desc_hi | (uint64_t)(((sW + stage * kWStageBytes) & 0x3FFFF) >> 4);
 #pragma unroll
             for (int k = 0; k < kBlockK / 16; ++k)  // +32 bytes (>>4 = 2) per K=16 step
               ptx::umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
             ptx::umma_commit(ptx::smem_u32(&bars->empty[stage]));
             if (n == NT - 1) ptx::umma_commit(ptx::smem_u32(&bars->a_free[kb]));
-            if (++stage == kStages) {
-              stage = 0;
-              ph ^= 1;
-            }
           }
-          ptx::umma_commit(ptx::smem_u32(&bars->tmem_full[acc]));
-          acc ^= 1;
-          if (acc == 0) acc_ph ^= 1;
+          if (++stage == kStages) {
+            stage = 0;
+            ph ^= 1;
+          }
         }
+        if (leader) ptx::umma_commit(ptx::smem_u32(&bars->tmem_full[acc]));
+        acc ^= 1;
+        if (acc == 0) acc_ph ^= 1;
       }
     }
     __syncwarp();
