@@ -39,9 +39,12 @@ constexpr int kThreads = 512;
 constexpr int kEpiThreads = 256;   // warps 4..11
 constexpr int kBuilderWarp0 = 12;  // warps 12..15
 constexpr int kTmemCols = 512;
-constexpr int kXchgBytes = kTileM * 3 * 4;  // forward statistics handed between column halves
-constexpr int kSmemBytes =
-    kABytes + kStages * kWStageBytes + 1024 /*align*/ + 256 /*barriers*/ + kXchgBytes;
+constexpr int kBarBytes = 256;
+constexpr int kBiasBytes = 2 * kTileN * 4;  // bias slice of the current and of the next N tile
+constexpr int kXchgBytes = kTileM * 4;      // forward statistics handed between column halves
+// A + W ring leave 3 KB of the 227 KB: no slack for re-aligning the base (checked at run time)
+constexpr int kSmemBytes = kABytes + kStages * kWStageBytes + kBarBytes + kBiasBytes + kXchgBytes;
+static_assert(kSmemBytes <= 232448, "shared memory budget");
 
 enum { MODE_FWD = 0, MODE_GRAD = 1 };
 
@@ -75,6 +78,7 @@ struct Barriers {
   uint64_t a_free[kMaxKB];
   uint32_t tmem_base;
 };
+static_assert(sizeof(Barriers) <= kBarBytes, "barrier block overlaps the bias staging area");
 
 __device__ __forceinline__ float tanh_approx(float x) {
   float y;
@@ -89,14 +93,14 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t raw = ptx::smem_u32(smem_raw);
-  const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B operands need 1024-B alignment
-  uint8_t* smem = smem_raw + (base - raw);
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t base = ptx::smem_u32(smem);
+  if (base & 1023u) __trap();  // SWIZZLE_128B operands need 1024-B alignment
   const uint32_t sA = base;
   const uint32_t sW = base + kABytes;
   Barriers* bars = reinterpret_cast<Barriers*>(smem + kABytes + kStages * kWStageBytes);
-  float* xchg = reinterpret_cast<float*>(smem + kABytes + kStages * kWStageBytes + 256);
+  float* bias_s = reinterpret_cast<float*>(smem + kABytes + kStages * kWStageBytes + kBarBytes);
+  float* xchg = bias_s + 2 * kTileN;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int nkb = P.J / kBlockK;
