@@ -135,16 +135,23 @@ int b200_ctc_grad(const void* logits, int dtype, const float* lse, const float* 
  * (wenet/transducer/joint.py:58-69: broadcast add, tanh, ffn_out) fused with the
  * log-softmax statistics / logits-gradient of torchaudio.functional.rnnt_loss.
  * e [B*T, J], p [B*U1, J] fp32 = outputs of enc_ffn / pred_ffn (joint.py:55-56, library
- * GEMMs on the caller's side); w_bf16 [V, J] bf16 = ffn_out.weight; bias_pad
- * [ceil(V/256)*256] fp32 zero padded = ffn_out.bias.  J multiple of 64, <= 512.
+ * GEMMs on the caller's side); w_bf16 [V, J] bf16 = ffn_out.weight; bias_pad [>= V] fp32 =
+ * ffn_out.bias (only the first V entries are read).  J multiple of 64, <= 512.
  * Tensor-core kernel (tcgen05 / TMEM / TMA); max_ctas <= 0 means one CTA per SM.
  */
 
-/* forward: per lattice cell lse over V and the blank / target log-probs [B,T,U1] */
+/* bound[0] (device) = max_v (|W_v|_1 + |b_v|) >= |logit| of any cell, since |tanh| <= 1 */
+int b200_joint_logit_bound(const void* w_bf16, const float* bias, int V, int J, float* bound,
+                           b200_stream_t stream);
+
+/* forward: per lattice cell lse over V and the blank / target log-probs [B,T,U1].
+ * logit_bound: NULL, or the device scalar of b200_joint_logit_bound for THESE weights; when
+ * it is small enough for 2^(bound*log2 e) to stay inside fp32 the log-sum-exp runs without a
+ * running maximum (same result, fewer instructions per logit). */
 int b200_joint_fwd(const float* e, const float* p, const void* w_bf16, const float* bias_pad,
                    const int32_t* targets, const int32_t* logit_len, const int32_t* target_len,
                    int B, int T, int U1, int V, int J, int blank,
-                   float* lse, float* lp_blank, float* lp_emit,
+                   float* lse, float* lp_blank, float* lp_emit, const float* logit_bound,
                    int max_ctas, b200_stream_t stream);
 
 /* backward, one chunk of cells [cell0, cell0+ncells) (cell = (b*T+t)*U1+u): recompute the

@@ -52,9 +52,44 @@ joint_dz_reduce_kernel(const float* __restrict__ dH, const __nv_bfloat16* __rest
   }
 }
 
+// bound[0] = max_v (sum_j |W[v,j]| + |b[v]|) >= |logit| of every lattice cell (|tanh| <= 1):
+// lets the forward joint kernel drop the running maximum of its log-sum-exp.  One warp per
+// vocabulary row; non-negative floats order like their bit patterns.
+__global__ void joint_logit_bound_kernel(const __nv_bfloat16* __restrict__ w,
+                                         const float* __restrict__ bias, int V, int J,
+                                         float* __restrict__ bound) {
+  const int v = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (v >= V) return;
+  const int lane = threadIdx.x & 31;
+  const __nv_bfloat162* row = reinterpret_cast<const __nv_bfloat162*>(w + (long long)v * J);
+  float s = 0.f;
+  for (int j = lane; j < J / 2; j += 32) {
+    const float2 f = __bfloat1622float2(row[j]);
+    s += fabsf(f.x) + fabsf(f.y);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) {
+    s = (s + fabsf(bias[v])) * 1.001f;  // headroom for the summation order
+    if (!(s == s)) s = INFINITY;         // NaN weights: no bound
+    atomicMax(reinterpret_cast<int*>(bound), __float_as_int(s));
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200_joint_logit_bound(const void* w_bf16, const float* bias, int V, int J,
+                                      float* bound, b200_stream_t stream) {
+  B200_CHECK_ARG(w_bf16 && bias && bound, "b200_joint_logit_bound: null pointer");
+  B200_CHECK_ARG(V > 0 && J > 0 && J % 2 == 0, "b200_joint_logit_bound: bad shape V=%d J=%d", V, J);
+  B200_CHECK_CUDA(cudaMemsetAsync(bound, 0, sizeof(float), (cudaStream_t)stream));
+  joint_logit_bound_kernel<<<(V + 7) / 8, 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const __nv_bfloat16*>(w_bf16), bias, V, J, bound);
+  B200_CHECK_LAUNCH("joint_logit_bound_kernel");
+  return B200_OK;
+}
 
 extern "C" int b200_joint_dz_reduce(const float* dH, const void* H, int ldh, int nb, int T, int U1,
                                     int J, float* de, float* dp, b200_stream_t stream) {

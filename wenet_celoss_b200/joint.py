@@ -60,16 +60,26 @@ def _pad_bias(bias: torch.Tensor, V: int) -> torch.Tensor:
     return out
 
 
+def joint_logit_bound(w_bf16, bias_pad, V):
+    """Device scalar max_v(|W_v|_1 + |b_v|): an upper bound of |logit| (|tanh| <= 1)."""
+    bound = torch.empty(1, dtype=torch.float32, device=w_bf16.device)
+    _lib.call("b200_joint_logit_bound", ptr(w_bf16), ptr(bias_pad), i32(V), i32(w_bf16.shape[1]),
+              ptr(bound), _lib.stream_handle(w_bf16.device))
+    return bound
+
+
 def joint_logprobs(e, p, w_bf16, bias_pad, targets, logit_lengths, target_lengths, V, blank,
-                   max_ctas: int = 0):
+                   max_ctas: int = 0, use_bound: bool = True):
     """lse, lp_blank, lp_emit [B,T,U1] from e [B,T,J], p [B,U1,J] (fp32) and W_out (bf16)."""
     B, T, J = e.shape
     U1 = p.shape[1]
     lat = torch.empty(3, B, T, U1, dtype=torch.float32, device=e.device)
     lse, lpb, lpe = lat.unbind(0)
+    bound = joint_logit_bound(w_bf16, bias_pad, V) if use_bound else None
     _lib.call("b200_joint_fwd", ptr(e), ptr(p), ptr(w_bf16), ptr(bias_pad), ptr(targets),
               ptr(logit_lengths), ptr(target_lengths), i32(B), i32(T), i32(U1), i32(V), i32(J),
-              i32(blank), ptr(lse), ptr(lpb), ptr(lpe), i32(max_ctas), _lib.stream_handle(e.device))
+              i32(blank), ptr(lse), ptr(lpb), ptr(lpe), ptr(bound), i32(max_ctas),
+              _lib.stream_handle(e.device))
     return lse, lpb, lpe
 
 
