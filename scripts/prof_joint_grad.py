@@ -15,6 +15,7 @@ tgt = torch.randint(1, V, (B, U), generator=g, dtype=torch.int32).to(dev)
 coef = torch.zeros(B, T, U1, 4, device=dev); coef[..., 0] = -9.0; coef[..., 1] = -3.0; coef[..., 2] = -3.0; coef[..., 3] = 1.0
 per_utt = T * U1; ldg = (V + 15) // 16 * 16; ldh = J + 8
 nb = int(sys.argv[1]) if len(sys.argv) > 1 else 1
+dbg = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 G = torch.empty(nb * per_utt, ldg, dtype=torch.bfloat16, device=dev)
 H = torch.zeros(nb * per_utt, ldh, dtype=torch.bfloat16, device=dev)
 st = _lib.stream_handle(torch.device(dev))
@@ -24,7 +25,7 @@ for _ in range(4):
     e0.record()
     _lib.call("b200_joint_grad_chunk", ptr(e), ptr(p), ptr(w), ptr(bias), ptr(tgt), ptr(coef), i32(B), i32(T),
               i32(U1), i32(V), i32(J), i32(0), ctypes.c_longlong(0), ctypes.c_longlong(nb * per_utt), ptr(G),
-              i32(ldg), ptr(H), i32(ldh), i32(0), st)
+              i32(ldg), ptr(H if not (dbg & 2) else None), i32(ldh), i32(dbg << 16), st)
     e1.record(); e1.synchronize(); ts.append(e0.elapsed_time(e1))
 tiles = -(-nb * per_utt // 128)
-print(f"GRAD chunk nb={nb}: {min(ts):.3f} ms, tiles {tiles}, waves {-(-tiles // 148)}, per wave {min(ts) * 1e3 / -(-tiles // 148):.1f} us")
+print(f"GRAD dbg={dbg} chunk nb={nb}: {min(ts):.3f} ms, tiles {tiles}, waves {-(-tiles // 148)}, per wave {min(ts) * 1e3 / -(-tiles // 148):.1f} us")

@@ -9,20 +9,21 @@
 // here as e [B*T, J] and p [B*U1, J] (fp32).
 //
 // One persistent CTA per SM walks M-tiles of 128 lattice cells (cell = (b*T + t)*U1 + u):
-//   warps 12-15 build the A tile H = tanh(e+p) in bf16, DOUBLE BUFFERED and split along K:
-//               k-blocks 0..3 (k < 256) in shared memory (K-major SWIZZLE_128B, 2 x 64 KB),
-//               k-blocks 4..7 in tensor memory (tcgen05.st, lane = cell row, 2 x 128 columns).
-//               Neither memory can hold two whole 128 x 512 tiles next to the W ring / the
-//               accumulators, together they can: the next tile is built while the current one
-//               is multiplied (with one buffer the tensor pipe idled ~25 % of every tile
-//               waiting for the builders, see profiles/README.md)
+//   warps 12-15 build the NEXT tile's A = tanh(e+p) in bf16 into a shared-memory staging
+//               buffer (K-major SWIZZLE_128B, 8 k-blocks of 16 KB) while the current tile is
+//               being multiplied: their global-load latency is off the critical path
+//   warp  1     at the start of a tile copies the staged A into TENSOR MEMORY (tcgen05.cp,
+//               128 lanes x 256 columns = 128 x 512 bf16) and then issues tcgen05.mma with A
+//               read from tensor memory (M=128, N=128, K=16) into two 128-column accumulators.
+//               A from TMEM matters: an M128 N128 MMA with both operands in shared memory
+//               reads 8 KB per 64 tensor cycles = the whole shared-memory bandwidth of the SM
+//               (measured: 94 instead of 64 cycles per MMA); with A in TMEM only W is read
 //   warp  0     TMA-loads W_out tiles [128 vocab rows x 2 x 64 k] (bf16) into a 3-stage ring
-//   warp  1     issues tcgen05.mma (M=128, N=128, K=16): A from shared memory for k < 256,
-//               from tensor memory above; two TMEM accumulators of 128 columns
 //   warps 4-11  epilogue: two warps per TMEM lane quarter (= two per SM sub-partition, so one
 //               hides the other's TMEM / MUFU latency), each thread owns one cell row and
 //               half of the 128 columns of every N tile, tcgen05.ld 32 columns at a time:
-//     MODE_FWD   online (max, sum-exp) over V, picks the blank and target logits
+//     MODE_FWD   log2-domain sum-exp over V (no running maximum when the host-provided logit
+//                bound allows), picks the blank and target logits
 //                -> lse, lp_blank, lp_emit  (3 floats per cell leave the CTA)
 //     MODE_GRAD  G = scale*(exp(x+c0) - [v==blank]exp(x+cb) - [v==y]exp(x+ce)) in bf16 into a
 //                bounded scratch chunk that feeds the two plain backward GEMMs
@@ -38,28 +39,25 @@ constexpr int kTileN = 128;
 constexpr int kBiasBlock = 256;  // bias is staged (and padded on the host) in blocks of 256 classes
 constexpr int kBlockK = 64;      // bf16 elements per 128-byte swizzle row
 constexpr int kMaxKB = 8;        // J <= 512
-constexpr int kSmemKB = 4;       // k-blocks of A kept in shared memory; the rest in tensor memory
 constexpr int kStages = 3;       // W ring: each stage holds TWO k-blocks (128 x 128 k = 32 KB), so
                                  // one barrier round trip of the issuing warp feeds 8 MMAs (512
                                  // tensor cycles); with 4 MMAs per wait the issue latency showed
 constexpr int kABlockBytes = kTileM * kBlockK * 2;      // 16 KB per k-block
-constexpr int kABufBytes = kSmemKB * kABlockBytes;      // 64 KB per buffer
-constexpr int kABytes = 2 * kABufBytes;                 // 128 KB
+constexpr int kABytes = kMaxKB * kABlockBytes;          // 128 KB staging for the next tile
 constexpr int kWBlockBytes = kTileN * kBlockK * 2;      // 16 KB per k-block
 constexpr int kWStageBytes = 2 * kWBlockBytes;          // 32 KB
 constexpr int kThreads = 512;
 constexpr int kEpiThreads = 256;   // warps 4..11
 constexpr int kBuilderWarp0 = 12;  // warps 12..15
 constexpr int kTmemCols = 512;
-constexpr int kTmemA0 = 2 * kTileN;                      // TMEM columns [256,512): 2 x 128 of A
-constexpr int kTmemABuf = (kMaxKB - kSmemKB) * kBlockK / 2;  // 128 columns (2 bf16 per column)
+constexpr int kTmemA0 = 2 * kTileN;  // TMEM columns [256,512): A, 2 bf16 per 32-bit column
 constexpr int kBarBytes = 512;
 constexpr int kBiasBytes = 2 * kBiasBlock * 4;  // bias block in use and the next one
 constexpr int kXchgBytes = kTileM * 4;          // forward statistics handed between column halves
 // A + W ring leave 3 KB of the 227 KB: no slack for re-aligning the base (checked at run time)
 constexpr int kSmemBytes = kABytes + kStages * kWStageBytes + kBarBytes + kBiasBytes + kXchgBytes;
 static_assert(kSmemBytes <= 232448, "shared memory budget");
-static_assert(kTmemA0 + 2 * kTmemABuf <= kTmemCols, "tensor memory budget");
+static_assert(kTmemA0 + kMaxKB * kBlockK / 2 <= kTmemCols, "tensor memory budget");
 
 enum { MODE_FWD = 0, MODE_GRAD = 1 };
 
@@ -71,6 +69,7 @@ struct Params {
   const int32_t* logit_len;
   const int32_t* target_len;
   int B, T, U1, V, J, blank;
+  int dbg;
   long long cell0, ncells, total_cells;
   // MODE_FWD
   float* lse;
@@ -90,8 +89,9 @@ struct Barriers {
   uint64_t empty[kStages];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
-  uint64_t a_ready[2][kMaxKB / 2];  // per A buffer and pair of k-blocks
-  uint64_t a_free[2][kMaxKB / 2];
+  uint64_t a_ready[kMaxKB / 2];  // staging -> MMA warp, per pair of k-blocks
+  uint64_t a_free[kMaxKB / 2];   // staging copied to TMEM -> builders
+  uint64_t a_done;               // all MMAs of a tile complete: its A in TMEM may be overwritten
   uint32_t tmem_base;
 };
 static_assert(sizeof(Barriers) <= kBarBytes, "barrier block overlaps the bias staging area");
@@ -133,10 +133,11 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
       ptx::mbar_init(ptx::smem_u32(&bars->tmem_full[i]), 1);
       ptx::mbar_init(ptx::smem_u32(&bars->tmem_empty[i]), kEpiThreads);
     }
-    for (int i = 0; i < kMaxKB; ++i) {
-      ptx::mbar_init(ptx::smem_u32(&bars->a_ready[0][i]), 4);
-      ptx::mbar_init(ptx::smem_u32(&bars->a_free[0][i]), 1);
+    for (int i = 0; i < kMaxKB / 2; ++i) {
+      ptx::mbar_init(ptx::smem_u32(&bars->a_ready[i]), 4);
+      ptx::mbar_init(ptx::smem_u32(&bars->a_free[i]), 1);
     }
+    ptx::mbar_init(ptx::smem_u32(&bars->a_done), 1);
     ptx::fence_barrier_init();
     ptx::prefetch_tensormap(&w_map);
   }
@@ -184,82 +185,80 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
     const uint64_t desc_hi = ptx::make_sw128_kmajor_desc(0);
     int stage = 0, ph = 0, acc = 0, acc_ph = 0, it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      const int ab = it & 1;               // A buffer of this tile
-      const uint32_t a_par = (it >> 1) & 1;  // parity of its a_ready phase
+      // the previous tile's MMAs still read A from tensor memory: wait until they are done
+      if (it > 0) ptx::mbar_wait(ptx::smem_u32(&bars->a_done), (it - 1) & 1);
       for (int n = 0; n < NT; ++n) {
         ptx::mbar_wait(ptx::smem_u32(&bars->tmem_empty[acc]), acc_ph ^ 1);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem + acc * kTileN;
         for (int kp = 0; kp < nkp; ++kp) {
-          if (n == 0) ptx::mbar_wait(ptx::smem_u32(&bars->a_ready[ab][kp]), a_par);
-          ptx::mbar_wait(ptx::smem_u32(&bars->full[stage]), ph);
-          ptx::tc_fence_after();
-          if (leader) {
-            const int nk = (2 * kp + 1 < nkb) ? 2 * (kBlockK / 16) : (kBlockK / 16);  // K=16 steps
-            // W: k-block j of the stage at +16 KB (>>4 = 1024), +32 bytes (>>4 = 2) per K=16 step
-            const uint64_t db = desc_hi | (uint64_t)(((sW + stage * kWStageBytes) & 0x3FFFF) >> 4);
-            if (2 * kp < kSmemKB) {
-              const uint64_t da = desc_hi | (uint64_t)(((sA + ab * kABufBytes + 2 * kp * kABlockBytes) &
-                                                        0x3FFFF) >> 4);
+          const int nk = (2 * kp + 1 < nkb) ? 2 * (kBlockK / 16) : (kBlockK / 16);  // K=16 steps
+          const uint32_t ta = tmem + kTmemA0 + kp * kBlockK;  // 2 k-blocks = 64 columns per pair
+          if (n == 0) {
+            // staged A (pair kp) -> tensor memory: 128 lanes x 32 bytes per tcgen05.cp
+            ptx::mbar_wait(ptx::smem_u32(&bars->a_ready[kp]), it & 1);
+            ptx::tc_fence_after();
+            if (leader) {
+              const uint64_t da = desc_hi | (uint64_t)(((sA + 2 * kp * kABlockBytes) & 0x3FFFF) >> 4);
 #pragma unroll
               for (int k = 0; k < 2 * (kBlockK / 16); ++k)
                 if (k < nk)
-                  ptx::umma_bf16(d_tmem, da + (k >> 2) * (kABlockBytes >> 4) + 2 * (k & 3),
-                                 db + (k >> 2) * (kWBlockBytes >> 4) + 2 * (k & 3), idesc, (kp | k) != 0);
-            } else {
-              const uint32_t ta = tmem + kTmemA0 + ab * kTmemABuf + (2 * kp - kSmemKB) * (kBlockK / 2);
-#pragma unroll
-              for (int k = 0; k < 2 * (kBlockK / 16); ++k)  // A: +8 columns per K=16 step
-                if (k < nk)
-                  ptx::umma_bf16_ts(d_tmem, ta + 8 * k, db + (k >> 2) * (kWBlockBytes >> 4) + 2 * (k & 3),
-                                    idesc, 1u);
+                  ptx::tmem_cp_128x256b(ta + 8 * k, da + (k >> 2) * (kABlockBytes >> 4) + 2 * (k & 3));
+              ptx::umma_commit(ptx::smem_u32(&bars->a_free[kp]));
             }
+          }
+          ptx::mbar_wait(ptx::smem_u32(&bars->full[stage]), ph);
+          ptx::tc_fence_after();
+          if (leader) {
+            // W: k-block j of the stage at +16 KB (>>4 = 1024), +32 bytes (>>4 = 2) per K=16 step
+            const uint64_t db = desc_hi | (uint64_t)(((sW + stage * kWStageBytes) & 0x3FFFF) >> 4);
+#pragma unroll
+            for (int k = 0; k < 2 * (kBlockK / 16); ++k)  // A: +8 columns per K=16 step
+              if (k < nk)
+                ptx::umma_bf16_ts(d_tmem, ta + 8 * k, db + (k >> 2) * (kWBlockBytes >> 4) + 2 * (k & 3),
+                                  idesc, (kp | k) != 0);
             ptx::umma_commit(ptx::smem_u32(&bars->empty[stage]));
-            if (n == NT - 1) ptx::umma_commit(ptx::smem_u32(&bars->a_free[ab][kp]));
           }
           if (++stage == kStages) {
             stage = 0;
             ph ^= 1;
           }
         }
-        if (leader) ptx::umma_commit(ptx::smem_u32(&bars->tmem_full[acc]));
+        if (leader) {
+          ptx::umma_commit(ptx::smem_u32(&bars->tmem_full[acc]));
+          if (n == NT - 1) ptx::umma_commit(ptx::smem_u32(&bars->a_done));
+        }
         acc ^= 1;
         if (acc == 0) acc_ph ^= 1;
       }
     }
     __syncwarp();
   } else if (warp >= kBuilderWarp0) {
-    // ===================== A-tile builders: H = tanh(e + p) -> bf16 =====================
-    const int bw = warp - kBuilderWarp0;  // rows bw*32 .. bw*32+31 (= TMEM lane quarter warp % 4)
-    const int rr = lane >> 3;             // shared-memory path: row within a group of 4
-    const int cc = lane & 7;              //   16-byte chunk within the 128-byte swizzle row
-    const uint32_t a_lane = tmem + ((uint32_t)(bw * 32) << 16) + kTmemA0;
+    // ===================== A-tile builders: H = tanh(e + p) -> bf16, swizzled staging =====================
+    const int bw = warp - kBuilderWarp0;  // rows bw*32 .. bw*32+31
+    const int rr = lane >> 3;             // row within a group of 4
+    const int cc = lane & 7;              // 16-byte chunk within the 128-byte swizzle row
     int it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      const int ab = it & 1;
-      const uint32_t f_par = ((it >> 1) & 1) ^ 1;
-      // --- k < 256: eight lanes per row, 16 bytes each, into swizzled shared memory ---
-      {
-        int eoff[8], poff[8], rowl[8];
+      int eoff[8], poff[8], rowl[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int r = bw * 32 + i * 4 + rr;
-          const long long local = (long long)tile * kTileM + r;
-          rowl[i] = local < P.ncells ? (int)local : -1;
-          long long cell = P.cell0 + local;
-          if (cell >= P.total_cells) cell = P.total_cells - 1;
-          const int bt = (int)(cell / P.U1);
-          const int u = (int)(cell - (long long)bt * P.U1);
-          const int b = bt / P.T;
-          eoff[i] = bt * P.J;  // < 2^31: B*T*J and B*U1*J elements are checked on the host
-          poff[i] = (b * P.U1 + u) * P.J;
-        }
-        const int nsm = nkb < kSmemKB ? nkb : kSmemKB;
-        for (int kp = 0; 2 * kp < nsm; ++kp) {
-          ptx::mbar_wait(ptx::smem_u32(&bars->a_free[ab][kp]), f_par);
-          for (int kb = 2 * kp; kb < 2 * kp + 2 && kb < nsm; ++kb) {
+      for (int i = 0; i < 8; ++i) {
+        const int r = bw * 32 + i * 4 + rr;
+        const long long local = (long long)tile * kTileM + r;
+        rowl[i] = local < P.ncells ? (int)local : -1;
+        long long cell = P.cell0 + local;
+        if (cell >= P.total_cells) cell = P.total_cells - 1;
+        const int bt = (int)(cell / P.U1);
+        const int u = (int)(cell - (long long)bt * P.U1);
+        const int b = bt / P.T;
+        eoff[i] = bt * P.J;  // < 2^31: B*T*J and B*U1*J elements are checked on the host
+        poff[i] = (b * P.U1 + u) * P.J;
+      }
+      for (int kp = 0; kp < nkp; ++kp) {
+        ptx::mbar_wait(ptx::smem_u32(&bars->a_free[kp]), (it & 1) ^ 1);
+        for (int kb = 2 * kp; kb < 2 * kp + 2 && kb < nkb; ++kb) {
           const int k0 = kb * kBlockK + cc * 8;
-          uint8_t* ablk = smem + ab * kABufBytes + kb * kABlockBytes;
+          uint8_t* ablk = smem + kb * kABlockBytes;
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const int r = bw * 32 + i * 4 + rr;
@@ -276,53 +275,10 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
             if (MODE == MODE_GRAD && P.H != nullptr && rowl[i] >= 0)
               *reinterpret_cast<uint4*>(P.H + (long long)rowl[i] * P.ldh + k0) = h;
           }
-          }
-          ptx::fence_proxy_async();  // generic-proxy stores -> visible to the tensor core
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bars->a_ready[ab][kp]));
         }
-      }
-      // --- k >= 256: thread = cell row = TMEM lane, 32 k per tcgen05.st ---
-      if (nkb > kSmemKB) {
-        const int row = bw * 32 + lane;
-        const long long local = (long long)tile * kTileM + row;
-        const long long rowg = local < P.ncells ? local : -1;
-        long long cell = P.cell0 + local;
-        if (cell >= P.total_cells) cell = P.total_cells - 1;
-        const long long bt = cell / P.U1;
-        const int u = (int)(cell - bt * P.U1);
-        const int b = (int)(bt / P.T);
-        const float* erow = P.e + bt * P.J;  // shared by the cells of one frame
-        const float* prow = P.p + ((long long)b * P.U1 + u) * P.J;
-        for (int kp = kSmemKB / 2; kp < nkp; ++kp) {
-          ptx::mbar_wait(ptx::smem_u32(&bars->a_free[ab][kp]), f_par);
-          ptx::tc_fence_after();
-          for (int kb = 2 * kp; kb < 2 * kp + 2 && kb < nkb; ++kb) {
-#pragma unroll
-          for (int h2 = 0; h2 < 2; ++h2) {
-            const int k0 = kb * kBlockK + h2 * 32;
-            uint32_t v[16];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const float4 ev = __ldg(reinterpret_cast<const float4*>(erow + k0) + i);
-              const float4 pv = __ldg(reinterpret_cast<const float4*>(prow + k0) + i);
-              v[2 * i] = pack_bf16x2(tanh_approx(ev.x + pv.x), tanh_approx(ev.y + pv.y));
-              v[2 * i + 1] = pack_bf16x2(tanh_approx(ev.z + pv.z), tanh_approx(ev.w + pv.w));
-            }
-            ptx::tmem_st16(a_lane + ab * kTmemABuf + (kb - kSmemKB) * (kBlockK / 2) + h2 * 16, v);
-            if (MODE == MODE_GRAD && P.H != nullptr && rowg >= 0) {
-              uint4* hp = reinterpret_cast<uint4*>(P.H + rowg * P.ldh + k0);
-#pragma unroll
-              for (int i = 0; i < 4; ++i)
-                hp[i] = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-            }
-          }
-          }
-          ptx::tmem_st_wait();
-          ptx::tc_fence_before();
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bars->a_ready[ab][kp]));
-        }
+        ptx::fence_proxy_async();  // generic-proxy stores -> visible to the tensor-core proxy
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bars->a_ready[kp]));
       }
     }
   } else if (warp >= 4) {

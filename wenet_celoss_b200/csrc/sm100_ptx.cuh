@@ -111,6 +111,12 @@ __device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, u
       "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// shared memory -> TMEM, issued by ONE thread: 128 lanes x 256 bits (8 columns) from the
+// matrix described by a shared-memory descriptor (same layouts as an MMA operand); ordered
+// with later tcgen05.mma of the same thread, completion via tcgen05.commit
+__device__ __forceinline__ void tmem_cp_128x256b(uint32_t taddr, uint64_t s_desc) {
+  asm volatile("tcgen05.cp.cta_group::1.128x256b [%0], %1;" ::"r"(taddr), "l"(s_desc) : "memory");
+}
 // registers -> TMEM: thread i of the warp writes 16 consecutive 32-bit columns of lane (base+i)
 __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
   asm volatile(
