@@ -156,7 +156,9 @@ int b200_joint_fwd(const float* e, const float* p, const void* w_bf16, const flo
 
 /* backward, one chunk of cells [cell0, cell0+ncells) (cell = (b*T+t)*U1+u): recompute the
  * logits tile and write G = d loss / d logits (bf16, [ncells, ldg], ldg % 16 == 0) from the
- * coefficients of b200_rnnt_grad_coef; optionally also H = tanh(e+p) in bf16 [ncells, ldh]. */
+ * coefficients of b200_rnnt_grad_coef.  H [ncells, ldh] bf16 (ldh >= J, ldh % 8 == 0) is a
+ * required scratch: columns [0,J) receive tanh(e+p) (the kernel's A operand, also the
+ * activations the dW GEMM needs); columns >= J are left untouched. */
 int b200_joint_grad_chunk(const float* e, const float* p, const void* w_bf16,
                           const float* bias_pad, const int32_t* targets, const float* coef,
                           int B, int T, int U1, int V, int J, int blank,

@@ -39,11 +39,22 @@ constexpr int kTileN = 128;
 constexpr int kBiasBlock = 256;  // bias is staged (and padded on the host) in blocks of 256 classes
 constexpr int kBlockK = 64;      // bf16 elements per 128-byte swizzle row
 constexpr int kMaxKB = 8;        // J <= 512
-constexpr int kStages = 3;       // W ring: each stage holds TWO k-blocks (128 x 128 k = 32 KB), so
+constexpr int kMaxStages = 4;    // W ring: each stage holds TWO k-blocks (128 x 128 k = 32 KB), so
                                  // one barrier round trip of the issuing warp feeds 8 MMAs (512
                                  // tensor cycles); with 4 MMAs per wait the issue latency showed
 constexpr int kABlockBytes = kTileM * kBlockK * 2;      // 16 KB per k-block
-constexpr int kABytes = kMaxKB * kABlockBytes;          // 128 KB staging for the next tile
+constexpr int kASlotBytes = 2 * kABlockBytes;           // one pair of k-blocks
+constexpr int kOperandBytes = 224 * 1024;  // A staging + W ring (+ G staging), per mode:
+//   MODE_FWD : A 4 slots (whole next tile, written by the builder warps) | W ring of 3
+//   MODE_GRAD: A 2 slots (TMA ring fed from the bf16 H scratch) | W ring of 4 | G staging 8 x 4 KB
+//              (the G stores and H loads lengthen the L2 round trip of the W stream: with 3
+//              stages the MMA warp waited 40 % of the time for W)
+template <int MODE> struct Cfg {
+  static constexpr int kASlots = MODE == 0 ? 4 : 2;
+  static constexpr int kStages = MODE == 0 ? 3 : 4;
+  static constexpr int kABytes = kASlots * kASlotBytes;
+  static constexpr int kGStageBytes = MODE == 0 ? 0 : 8 * 4096;
+};
 constexpr int kWBlockBytes = kTileN * kBlockK * 2;      // 16 KB per k-block
 constexpr int kWStageBytes = 2 * kWBlockBytes;          // 32 KB
 constexpr int kThreads = 512;
@@ -55,8 +66,11 @@ constexpr int kBarBytes = 512;
 constexpr int kBiasBytes = 2 * kBiasBlock * 4;  // bias block in use and the next one
 constexpr int kXchgBytes = kTileM * 4;          // forward statistics handed between column halves
 // A + W ring leave 3 KB of the 227 KB: no slack for re-aligning the base (checked at run time)
-constexpr int kSmemBytes = kABytes + kStages * kWStageBytes + kBarBytes + kBiasBytes + kXchgBytes;
+constexpr int kSmemBytes = kOperandBytes + kBarBytes + kBiasBytes + kXchgBytes;
 static_assert(kSmemBytes <= 232448, "shared memory budget");
+static_assert(Cfg<0>::kABytes + Cfg<0>::kStages * (2 * kTileN * kBlockK * 2) + Cfg<0>::kGStageBytes <= kOperandBytes &&
+              Cfg<1>::kABytes + Cfg<1>::kStages * (2 * kTileN * kBlockK * 2) + Cfg<1>::kGStageBytes <= kOperandBytes,
+              "operand area");
 static_assert(kTmemA0 + kMaxKB * kBlockK / 2 <= kTmemCols, "tensor memory budget");
 
 enum { MODE_FWD = 0, MODE_GRAD = 1 };
@@ -69,7 +83,6 @@ struct Params {
   const int32_t* logit_len;
   const int32_t* target_len;
   int B, T, U1, V, J, blank;
-  int dbg;
   long long cell0, ncells, total_cells;
   // MODE_FWD
   float* lse;
@@ -85,12 +98,12 @@ struct Params {
 };
 
 struct Barriers {
-  uint64_t full[kStages];
-  uint64_t empty[kStages];
+  uint64_t full[kMaxStages];
+  uint64_t empty[kMaxStages];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
-  uint64_t a_ready[kMaxKB / 2];  // staging -> MMA warp, per pair of k-blocks
-  uint64_t a_free[kMaxKB / 2];   // staging copied to TMEM -> builders
+  uint64_t a_ready[4];  // A slot filled (builder warps / TMA) -> MMA warp
+  uint64_t a_free[4];   // A slot copied to TMEM -> builders / TMA producer
   uint64_t a_done;               // all MMAs of a tile complete: its A in TMEM may be overwritten
   uint32_t tmem_base;
 };
@@ -108,14 +121,19 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
-joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
+joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap h_map,
+             const __grid_constant__ CUtensorMap g_map, const Params P) {
+  constexpr int kASlots = Cfg<MODE>::kASlots;
+  constexpr int kStages = Cfg<MODE>::kStages;
+  constexpr int kABytes = Cfg<MODE>::kABytes;
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t base = ptx::smem_u32(smem);
   if (base & 1023u) __trap();  // SWIZZLE_128B operands need 1024-B alignment
   const uint32_t sA = base;
   const uint32_t sW = base + kABytes;
-  Barriers* bars = reinterpret_cast<Barriers*>(smem + kABytes + kStages * kWStageBytes);
-  float* bias_s = reinterpret_cast<float*>(smem + kABytes + kStages * kWStageBytes + kBarBytes);
+  uint8_t* g_stage = smem + kABytes + kStages * kWStageBytes;  // MODE_GRAD: 4 KB per epilogue warp
+  Barriers* bars = reinterpret_cast<Barriers*>(smem + kOperandBytes);
+  float* bias_s = reinterpret_cast<float*>(smem + kOperandBytes + kBarBytes);
   float* xchg = bias_s + 2 * kBiasBlock;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -133,13 +151,17 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
       ptx::mbar_init(ptx::smem_u32(&bars->tmem_full[i]), 1);
       ptx::mbar_init(ptx::smem_u32(&bars->tmem_empty[i]), kEpiThreads);
     }
-    for (int i = 0; i < kMaxKB / 2; ++i) {
-      ptx::mbar_init(ptx::smem_u32(&bars->a_ready[i]), 4);
+    for (int i = 0; i < 4; ++i) {
+      ptx::mbar_init(ptx::smem_u32(&bars->a_ready[i]), MODE == MODE_FWD ? 4 : 1);
       ptx::mbar_init(ptx::smem_u32(&bars->a_free[i]), 1);
     }
     ptx::mbar_init(ptx::smem_u32(&bars->a_done), 1);
     ptx::fence_barrier_init();
     ptx::prefetch_tensormap(&w_map);
+    if (MODE == MODE_GRAD) {
+      ptx::prefetch_tensormap(&h_map);
+      ptx::prefetch_tensormap(&g_map);
+    }
   }
   if (warp == 2) {
     ptx::tmem_alloc(ptx::smem_u32(&bars->tmem_base), kTmemCols);
@@ -183,7 +205,7 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
     const bool leader = ptx::elect_one();
     constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(kTileM, kTileN);
     const uint64_t desc_hi = ptx::make_sw128_kmajor_desc(0);
-    int stage = 0, ph = 0, acc = 0, acc_ph = 0, it = 0;
+    int stage = 0, ph = 0, acc = 0, acc_ph = 0, it = 0, aslot = 0, aph = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       // the previous tile's MMAs still read A from tensor memory: wait until they are done
       if (it > 0) ptx::mbar_wait(ptx::smem_u32(&bars->a_done), (it - 1) & 1);
@@ -196,15 +218,19 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
           const uint32_t ta = tmem + kTmemA0 + kp * kBlockK;  // 2 k-blocks = 64 columns per pair
           if (n == 0) {
             // staged A (pair kp) -> tensor memory: 128 lanes x 32 bytes per tcgen05.cp
-            ptx::mbar_wait(ptx::smem_u32(&bars->a_ready[kp]), it & 1);
+            ptx::mbar_wait(ptx::smem_u32(&bars->a_ready[aslot]), aph);
             ptx::tc_fence_after();
             if (leader) {
-              const uint64_t da = desc_hi | (uint64_t)(((sA + 2 * kp * kABlockBytes) & 0x3FFFF) >> 4);
+              const uint64_t da = desc_hi | (uint64_t)(((sA + aslot * kASlotBytes) & 0x3FFFF) >> 4);
 #pragma unroll
               for (int k = 0; k < 2 * (kBlockK / 16); ++k)
                 if (k < nk)
                   ptx::tmem_cp_128x256b(ta + 8 * k, da + (k >> 2) * (kABlockBytes >> 4) + 2 * (k & 3));
-              ptx::umma_commit(ptx::smem_u32(&bars->a_free[kp]));
+              ptx::umma_commit(ptx::smem_u32(&bars->a_free[aslot]));
+            }
+            if (++aslot == kASlots) {
+              aslot = 0;
+              aph ^= 1;
             }
           }
           ptx::mbar_wait(ptx::smem_u32(&bars->full[stage]), ph);
@@ -233,20 +259,39 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
       }
     }
     __syncwarp();
-  } else if (warp >= kBuilderWarp0) {
+  } else if (MODE == MODE_GRAD && warp == 3) {
+    // ===================== A producer (MODE_GRAD): TMA ring fed from the bf16 H scratch =====================
+    const bool leader = ptx::elect_one();
+    int aslot = 0, aph = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
+      for (int kp = 0; kp < nkp; ++kp) {
+        ptx::mbar_wait(ptx::smem_u32(&bars->a_free[aslot]), aph ^ 1);
+        if (leader) {
+          const uint32_t fb = ptx::smem_u32(&bars->a_ready[aslot]);
+          const bool two = 2 * kp + 1 < nkb;
+          ptx::mbar_arrive_expect_tx(fb, two ? kASlotBytes : kABlockBytes);
+          const uint32_t dst = sA + aslot * kASlotBytes;
+          ptx::tma_load_2d(dst, &h_map, fb, 2 * kp * kBlockK, tile * kTileM);
+          if (two) ptx::tma_load_2d(dst + kABlockBytes, &h_map, fb, (2 * kp + 1) * kBlockK, tile * kTileM);
+        }
+        if (++aslot == kASlots) {
+          aslot = 0;
+          aph ^= 1;
+        }
+      }
+    __syncwarp();
+  } else if (MODE == MODE_FWD && warp >= kBuilderWarp0) {
     // ===================== A-tile builders: H = tanh(e + p) -> bf16, swizzled staging =====================
     const int bw = warp - kBuilderWarp0;  // rows bw*32 .. bw*32+31
     const int rr = lane >> 3;             // row within a group of 4
     const int cc = lane & 7;              // 16-byte chunk within the 128-byte swizzle row
-    int it = 0;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      int eoff[8], poff[8], rowl[8];
+    int aslot = 0, aph = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      int eoff[8], poff[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const int r = bw * 32 + i * 4 + rr;
-        const long long local = (long long)tile * kTileM + r;
-        rowl[i] = local < P.ncells ? (int)local : -1;
-        long long cell = P.cell0 + local;
+        long long cell = P.cell0 + (long long)tile * kTileM + r;
         if (cell >= P.total_cells) cell = P.total_cells - 1;
         const int bt = (int)(cell / P.U1);
         const int u = (int)(cell - (long long)bt * P.U1);
@@ -255,10 +300,10 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
         poff[i] = (b * P.U1 + u) * P.J;
       }
       for (int kp = 0; kp < nkp; ++kp) {
-        ptx::mbar_wait(ptx::smem_u32(&bars->a_free[kp]), (it & 1) ^ 1);
+        ptx::mbar_wait(ptx::smem_u32(&bars->a_free[aslot]), aph ^ 1);
         for (int kb = 2 * kp; kb < 2 * kp + 2 && kb < nkb; ++kb) {
           const int k0 = kb * kBlockK + cc * 8;
-          uint8_t* ablk = smem + kb * kABlockBytes;
+          uint8_t* ablk = smem + aslot * kASlotBytes + (kb & 1) * kABlockBytes;
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const int r = bw * 32 + i * 4 + rr;
@@ -272,16 +317,18 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
             h.z = pack_bf16x2(tanh_approx(e1.x + p1.x), tanh_approx(e1.y + p1.y));
             h.w = pack_bf16x2(tanh_approx(e1.z + p1.z), tanh_approx(e1.w + p1.w));
             *reinterpret_cast<uint4*>(ablk + r * 128 + ((cc ^ (r & 7)) << 4)) = h;
-            if (MODE == MODE_GRAD && P.H != nullptr && rowl[i] >= 0)
-              *reinterpret_cast<uint4*>(P.H + (long long)rowl[i] * P.ldh + k0) = h;
           }
         }
         ptx::fence_proxy_async();  // generic-proxy stores -> visible to the tensor-core proxy
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bars->a_ready[kp]));
+        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bars->a_ready[aslot]));
+        if (++aslot == kASlots) {
+          aslot = 0;
+          aph ^= 1;
+        }
       }
     }
-  } else if (warp >= 4) {
+  } else if (warp >= 4 && warp < kBuilderWarp0) {
     // ===================== epilogue =====================
 #include "joint_fused_epilogue.inc"
   }
@@ -291,6 +338,35 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const Params P) {
   if (warp == 2) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem, kTmemCols);
+  }
+}
+
+// H[cell - cell0, 0:J] = bf16(tanh(e[b,t,:] + p[b,u,:])) for one chunk of cells: the A operand of
+// the backward joint kernel (read back through TMA while still in L2) and of the dW GEMM.
+// Same arithmetic as the forward builders (tanh.approx.f32, round-to-nearest bf16).
+__global__ void __launch_bounds__(256)
+joint_h_kernel(const float* __restrict__ e, const float* __restrict__ p, int T, int U1, int J,
+               long long cell0, long long ncells, __nv_bfloat16* __restrict__ H, int ldh) {
+  const int g8 = J >> 3;  // 8-element groups per row
+  const long long total = ncells * g8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long local = i / g8;
+    const int k0 = (int)(i - local * g8) << 3;
+    const long long cell = cell0 + local;
+    const long long bt = cell / U1;
+    const int u = (int)(cell - bt * U1);
+    const long long b = bt / T;
+    const float4* ep = reinterpret_cast<const float4*>(e + bt * J + k0);
+    const float4* pp = reinterpret_cast<const float4*>(p + (b * U1 + u) * J + k0);
+    const float4 e0 = __ldg(ep), e1 = __ldg(ep + 1);
+    const float4 p0 = __ldg(pp), p1 = __ldg(pp + 1);
+    uint4 h;
+    h.x = pack_bf16x2(tanh_approx(e0.x + p0.x), tanh_approx(e0.y + p0.y));
+    h.y = pack_bf16x2(tanh_approx(e0.z + p0.z), tanh_approx(e0.w + p0.w));
+    h.z = pack_bf16x2(tanh_approx(e1.x + p1.x), tanh_approx(e1.y + p1.y));
+    h.w = pack_bf16x2(tanh_approx(e1.z + p1.z), tanh_approx(e1.w + p1.w));
+    *reinterpret_cast<uint4*>(H + local * ldh + k0) = h;
   }
 }
 
