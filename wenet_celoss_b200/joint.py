@@ -32,7 +32,7 @@ from .rnnt import rnnt_grad_coef, rnnt_lattice
 
 _TILE_N = 256
 _TILE_M = 128
-SCRATCH_BYTES = 2 << 30  # bound on the bf16 G scratch of the backward pass
+SCRATCH_BYTES = 4 << 30  # bound on the bf16 G scratch of the backward pass
 
 
 def _chunk_utts(B: int, per_utt: int, ldg: int, sms: int) -> int:
