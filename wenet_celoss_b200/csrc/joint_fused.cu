@@ -8,25 +8,29 @@
 // enc_ffn / pred_ffn (joint.py:55-56) stay library GEMMs in the Python wrapper and arrive
 // here as e [B*T, J] and p [B*U1, J] (fp32).
 //
-// One persistent CTA per SM walks M-tiles of 128 lattice cells (cell = (b*T + t)*U1 + u):
-//   warps 12-15 build the NEXT tile's A = tanh(e+p) in bf16 into a shared-memory staging
-//               buffer (K-major SWIZZLE_128B, 8 k-blocks of 16 KB) while the current tile is
-//               being multiplied: their global-load latency is off the critical path
+// One persistent CTA (640 threads) per SM walks M-tiles of 128 lattice cells
+// (cell = (b*T + t)*U1 + u):
+//   warp  0     TMA-loads W_out tiles [128 vocab rows x 2 x 64 k] (bf16) into a ring
 //   warp  1     at the start of a tile copies the staged A into TENSOR MEMORY (tcgen05.cp,
 //               128 lanes x 256 columns = 128 x 512 bf16) and then issues tcgen05.mma with A
 //               read from tensor memory (M=128, N=128, K=16) into two 128-column accumulators.
 //               A from TMEM matters: an M128 N128 MMA with both operands in shared memory
 //               reads 8 KB per 64 tensor cycles = the whole shared-memory bandwidth of the SM
 //               (measured: 94 instead of 64 cycles per MMA); with A in TMEM only W is read
-//   warp  0     TMA-loads W_out tiles [128 vocab rows x 2 x 64 k] (bf16) into a 3-stage ring
-//   warps 4-11  epilogue: two warps per TMEM lane quarter (= two per SM sub-partition, so one
-//               hides the other's TMEM / MUFU latency), each thread owns one cell row and
-//               half of the 128 columns of every N tile, tcgen05.ld 32 columns at a time:
+//   warp  2     allocates / frees tensor memory
+//   warp  3     MODE_GRAD: TMA-loads A tiles from the bf16 H scratch into a 2-slot ring
+//   warps 4..   epilogue: 2 (MODE_FWD) or 4 (MODE_GRAD) warps per TMEM lane quarter (= per SM
+//               sub-partition); each thread owns one cell row and 64 / 32 of the 128 columns of
+//               every N tile; the accumulator is released as soon as it is in registers.
 //     MODE_FWD   log2-domain sum-exp over V (no running maximum when the host-provided logit
 //                bound allows), picks the blank and target logits
-//                -> lse, lp_blank, lp_emit  (3 floats per cell leave the CTA)
-//     MODE_GRAD  G = scale*(exp(x+c0) - [v==blank]exp(x+cb) - [v==y]exp(x+ce)) in bf16 into a
-//                bounded scratch chunk that feeds the two plain backward GEMMs
+//                -> lse, lp_blank, lp_emit  (3 floats per cell leave the CTA).
+//                Warps 12-15 build the NEXT tile's A = tanh(e+p) (bf16, K-major SWIZZLE_128B
+//                staging, 128 KB) while the current tile is multiplied (folding this into the
+//                epilogue warps was measured slower: 58 vs 54 us per tile)
+//     MODE_GRAD  G = scale*(exp(x+c0) - [v==blank]exp(x+cb) - [v==y]exp(x+ce)) in bf16, staged
+//                per warp in shared memory and written with TMA stores into a bounded scratch
+//                chunk that feeds the two plain backward GEMMs
 // Roofline: tensor pipe; algorithmic flops per launch = 2 * cells * J * V.
 #include "common.cuh"
 #include "sm100_ptx.cuh"
@@ -43,23 +47,28 @@ constexpr int kMaxStages = 4;    // W ring: each stage holds TWO k-blocks (128 x
                                  // one barrier round trip of the issuing warp feeds 8 MMAs (512
                                  // tensor cycles); with 4 MMAs per wait the issue latency showed
 constexpr int kABlockBytes = kTileM * kBlockK * 2;      // 16 KB per k-block
+constexpr int kEpiWarp0 = 4;  // warps 0..3: TMA (W), MMA, TMEM alloc, TMA (A, MODE_GRAD)
 constexpr int kASlotBytes = 2 * kABlockBytes;           // one pair of k-blocks
 constexpr int kOperandBytes = 224 * 1024;  // A staging + W ring (+ G staging), per mode:
 //   MODE_FWD : A 4 slots (whole next tile, written by the builder warps) | W ring of 3
 //   MODE_GRAD: A 2 slots (TMA ring fed from the bf16 H scratch) | W ring of 4 | G staging 8 x 4 KB
 //              (the G stores and H loads lengthen the L2 round trip of the W stream: with 3
 //              stages the MMA warp waited 40 % of the time for W)
+//   MODE_FWD : 512 threads: 8 epilogue warps (64 columns each) + 4 A-builder warps
+//   MODE_GRAD: 640 threads: 16 epilogue warps (32 columns each; its epilogue is the longer one:
+//              FADD + bf16 packing + staging stores on top of FFMA / MUFU)
 template <int MODE> struct Cfg {
+  static constexpr int kEpiWarps = MODE == 0 ? 8 : 16;
+  static constexpr int kEpiThreads = kEpiWarps * 32;
+  static constexpr int kBuilderWarp0 = kEpiWarp0 + kEpiWarps;  // MODE_FWD: 4 builder warps
+  static constexpr int kThreads = MODE == 0 ? 512 : 640;
   static constexpr int kASlots = MODE == 0 ? 4 : 2;
   static constexpr int kStages = MODE == 0 ? 3 : 4;
   static constexpr int kABytes = kASlots * kASlotBytes;
-  static constexpr int kGStageBytes = MODE == 0 ? 0 : 8 * 4096;
+  static constexpr int kGStageBytes = MODE == 0 ? 0 : 16 * 2048;
 };
 constexpr int kWBlockBytes = kTileN * kBlockK * 2;      // 16 KB per k-block
 constexpr int kWStageBytes = 2 * kWBlockBytes;          // 32 KB
-constexpr int kThreads = 512;
-constexpr int kEpiThreads = 256;   // warps 4..11
-constexpr int kBuilderWarp0 = 12;  // warps 12..15
 constexpr int kTmemCols = 512;
 constexpr int kTmemA0 = 2 * kTileN;  // TMEM columns [256,512): A, 2 bf16 per 32-bit column
 constexpr int kBarBytes = 512;
@@ -120,18 +129,21 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(Cfg<MODE>::kThreads, 1)
 joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ CUtensorMap h_map,
              const __grid_constant__ CUtensorMap g_map, const Params P) {
   constexpr int kASlots = Cfg<MODE>::kASlots;
   constexpr int kStages = Cfg<MODE>::kStages;
+  constexpr int kEpiWarps = Cfg<MODE>::kEpiWarps;
+  constexpr int kEpiThreads = Cfg<MODE>::kEpiThreads;
+  constexpr int kBuilderWarp0 = Cfg<MODE>::kBuilderWarp0;
   constexpr int kABytes = Cfg<MODE>::kABytes;
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t base = ptx::smem_u32(smem);
   if (base & 1023u) __trap();  // SWIZZLE_128B operands need 1024-B alignment
   const uint32_t sA = base;
   const uint32_t sW = base + kABytes;
-  uint8_t* g_stage = smem + kABytes + kStages * kWStageBytes;  // MODE_GRAD: 4 KB per epilogue warp
+  uint8_t* g_stage = smem + kABytes + kStages * kWStageBytes;  // MODE_GRAD: 2 KB per epilogue warp
   Barriers* bars = reinterpret_cast<Barriers*>(smem + kOperandBytes);
   float* bias_s = reinterpret_cast<float*>(smem + kOperandBytes + kBarBytes);
   float* xchg = bias_s + 2 * kBiasBlock;
@@ -177,6 +189,9 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
     // The whole warp walks the loop (warp-uniform control flow keeps every operand in
     // uniform registers); one elected lane issues.
     const bool leader = ptx::elect_one();
+    // W_out (5 MB) is re-read by every tile of every SM: keep it in L2 while the G / H streams
+    // of MODE_GRAD pass through (15 % of the W sectors missed L2 without the hint)
+    const uint64_t w_policy = ptx::l2_policy_evict_last();
     int stage = 0, ph = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
       for (int n = 0; n < NT; ++n)
@@ -187,8 +202,10 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
             const bool two = 2 * kp + 1 < nkb;
             ptx::mbar_arrive_expect_tx(fb, two ? kWStageBytes : kWBlockBytes);
             const uint32_t dst = sW + stage * kWStageBytes;
-            ptx::tma_load_2d(dst, &w_map, fb, 2 * kp * kBlockK, n * kTileN);
-            if (two) ptx::tma_load_2d(dst + kWBlockBytes, &w_map, fb, (2 * kp + 1) * kBlockK, n * kTileN);
+            ptx::tma_load_2d_hint(dst, &w_map, fb, 2 * kp * kBlockK, n * kTileN, w_policy);
+            if (two)
+              ptx::tma_load_2d_hint(dst + kWBlockBytes, &w_map, fb, (2 * kp + 1) * kBlockK, n * kTileN,
+                                    w_policy);
           }
           if (++stage == kStages) {
             stage = 0;
@@ -218,15 +235,17 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
           const uint32_t ta = tmem + kTmemA0 + kp * kBlockK;  // 2 k-blocks = 64 columns per pair
           if (n == 0) {
             // staged A (pair kp) -> tensor memory: 128 lanes x 32 bytes per tcgen05.cp
-            ptx::mbar_wait(ptx::smem_u32(&bars->a_ready[aslot]), aph);
+            // MODE_FWD: slot = pair index (the staging holds a whole tile); MODE_GRAD: ring
+            const int as = MODE == MODE_FWD ? kp : aslot;
+            ptx::mbar_wait(ptx::smem_u32(&bars->a_ready[as]), MODE == MODE_FWD ? (it & 1) : aph);
             ptx::tc_fence_after();
             if (leader) {
-              const uint64_t da = desc_hi | (uint64_t)(((sA + aslot * kASlotBytes) & 0x3FFFF) >> 4);
+              const uint64_t da = desc_hi | (uint64_t)(((sA + as * kASlotBytes) & 0x3FFFF) >> 4);
 #pragma unroll
               for (int k = 0; k < 2 * (kBlockK / 16); ++k)
                 if (k < nk)
                   ptx::tmem_cp_128x256b(ta + 8 * k, da + (k >> 2) * (kABlockBytes >> 4) + 2 * (k & 3));
-              ptx::umma_commit(ptx::smem_u32(&bars->a_free[aslot]));
+              ptx::umma_commit(ptx::smem_u32(&bars->a_free[as]));
             }
             if (++aslot == kASlots) {
               aslot = 0;
@@ -262,6 +281,7 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
   } else if (MODE == MODE_GRAD && warp == 3) {
     // ===================== A producer (MODE_GRAD): TMA ring fed from the bf16 H scratch =====================
     const bool leader = ptx::elect_one();
+    const uint64_t h_policy = ptx::l2_policy_evict_first();  // each H tile is read once here
     int aslot = 0, aph = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
       for (int kp = 0; kp < nkp; ++kp) {
@@ -271,8 +291,10 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
           const bool two = 2 * kp + 1 < nkb;
           ptx::mbar_arrive_expect_tx(fb, two ? kASlotBytes : kABlockBytes);
           const uint32_t dst = sA + aslot * kASlotBytes;
-          ptx::tma_load_2d(dst, &h_map, fb, 2 * kp * kBlockK, tile * kTileM);
-          if (two) ptx::tma_load_2d(dst + kABlockBytes, &h_map, fb, (2 * kp + 1) * kBlockK, tile * kTileM);
+          ptx::tma_load_2d_hint(dst, &h_map, fb, 2 * kp * kBlockK, tile * kTileM, h_policy);
+          if (two)
+            ptx::tma_load_2d_hint(dst + kABlockBytes, &h_map, fb, (2 * kp + 1) * kBlockK, tile * kTileM,
+                                  h_policy);
         }
         if (++aslot == kASlots) {
           aslot = 0;
@@ -285,8 +307,8 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
     const int bw = warp - kBuilderWarp0;  // rows bw*32 .. bw*32+31
     const int rr = lane >> 3;             // row within a group of 4
     const int cc = lane & 7;              // 16-byte chunk within the 128-byte swizzle row
-    int aslot = 0, aph = 0;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    int it = 0;  // slot = pair index kp (the staging holds a whole tile), phase = tile parity
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       int eoff[8], poff[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -300,10 +322,10 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
         poff[i] = (b * P.U1 + u) * P.J;
       }
       for (int kp = 0; kp < nkp; ++kp) {
-        ptx::mbar_wait(ptx::smem_u32(&bars->a_free[aslot]), aph ^ 1);
+        ptx::mbar_wait(ptx::smem_u32(&bars->a_free[kp]), (it & 1) ^ 1);
         for (int kb = 2 * kp; kb < 2 * kp + 2 && kb < nkb; ++kb) {
           const int k0 = kb * kBlockK + cc * 8;
-          uint8_t* ablk = smem + aslot * kASlotBytes + (kb & 1) * kABlockBytes;
+          uint8_t* ablk = smem + kb * kABlockBytes;
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const int r = bw * 32 + i * 4 + rr;
@@ -321,14 +343,10 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
         }
         ptx::fence_proxy_async();  // generic-proxy stores -> visible to the tensor-core proxy
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bars->a_ready[aslot]));
-        if (++aslot == kASlots) {
-          aslot = 0;
-          aph ^= 1;
-        }
+        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bars->a_ready[kp]));
       }
     }
-  } else if (warp >= 4 && warp < kBuilderWarp0) {
+  } else if (warp >= kEpiWarp0 && warp < kBuilderWarp0) {
     // ===================== epilogue =====================
 #include "joint_fused_epilogue.inc"
   }
