@@ -15,6 +15,8 @@
 // All arithmetic is fp32 FMA (no tensor cores, no bf16): the outputs are integers and
 // must match the reference's argmax.  enc_ffn(enc_out) is one library GEMM done by the
 // caller; projection and pred_ffn are pre-composed on the host (fp64) into W_c, b_c.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -54,7 +56,7 @@ struct State {
   int32_t* part_idx; // [B][n_tiles]
   int32_t* act_list;   // [2][B]
   int32_t* need_list;  // [2][B]
-  int32_t* counters;   // [2][2]: {n_act, n_need} per parity
+  int32_t* counters;   // [2][2]: {n_act, n_need} per parity; [4] = rounds run (persistent kernel)
 };
 
 __global__ void init_kernel(State S, int blank, int L, int H) {
@@ -304,6 +306,8 @@ __global__ void __launch_bounds__(1024) update_kernel(Model M, State S, int roun
     }
   }
 }
+
+#include "greedy_persistent.inc"
 
 }  // namespace gs
 }  // namespace b200
