@@ -408,7 +408,7 @@ class RnntFusedWorkload:
         def k_grad():
             _lib.call("b200_joint_grad_chunk", ptr(e), ptr(p), ptr(w), ptr(bias), ptr(self.targets),
                       ptr(box["coef"]), i32(B), i32(T), i32(U1), i32(V), i32(J), i32(0), _i64(0),
-                      _i64(per_utt), ptr(G), i32(ldg), ptr(H), i32(ldh), i32(0), st)
+                      _i64(per_utt), ptr(G), i32(ldg), ptr(H), i32(ldh), ptr(None), i32(0), st)
 
         out = {}
         k_fwd(); k_lat()

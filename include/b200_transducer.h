@@ -158,12 +158,14 @@ int b200_joint_fwd(const float* e, const float* p, const void* w_bf16, const flo
  * logits tile and write G = d loss / d logits (bf16, [ncells, ldg], ldg % 16 == 0) from the
  * coefficients of b200_rnnt_grad_coef.  H [ncells, ldh] bf16 (ldh >= J, ldh % 8 == 0) is a
  * required scratch: columns [0,J) receive tanh(e+p) (the kernel's A operand, also the
- * activations the dW GEMM needs); columns >= J are left untouched. */
+ * activations the dW GEMM needs); columns >= J are left untouched.
+ * db_part: NULL, or fp32 [16][ceil(V/128)*128] (zeroed by the caller before the first chunk):
+ * receives partial column sums of G, i.e. d b_out = sum over the 16 rows, first V entries. */
 int b200_joint_grad_chunk(const float* e, const float* p, const void* w_bf16,
                           const float* bias_pad, const int32_t* targets, const float* coef,
                           int B, int T, int U1, int V, int J, int blank,
                           long long cell0, long long ncells,
-                          void* G, int ldg, void* H, int ldh,
+                          void* G, int ldg, void* H, int ldh, float* db_part,
                           int max_ctas, b200_stream_t stream);
 
 /* backward tail: dZ = dH * (1 - H^2), d e[b,t,:] = sum_u dZ, d p[b,u,:] += sum_t dZ

@@ -25,7 +25,7 @@ for _ in range(4):
     e0.record()
     _lib.call("b200_joint_grad_chunk", ptr(e), ptr(p), ptr(w), ptr(bias), ptr(tgt), ptr(coef), i32(B), i32(T),
               i32(U1), i32(V), i32(J), i32(0), ctypes.c_longlong(0), ctypes.c_longlong(nb * per_utt), ptr(G),
-              i32(ldg), ptr(H), i32(ldh), i32(0), st)
+              i32(ldg), ptr(H), i32(ldh), ptr(None), i32(0), st)
     e1.record(); e1.synchronize(); ts.append(e0.elapsed_time(e1))
 tiles = -(-nb * per_utt // 128)
 print(f"GRAD dbg={dbg} chunk nb={nb}: {min(ts):.3f} ms, tiles {tiles}, waves {-(-tiles // 148)}, per wave {min(ts) * 1e3 / -(-tiles // 148):.1f} us")

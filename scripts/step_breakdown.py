@@ -31,23 +31,24 @@ def step():
     dy = torch.full((B,), 1.0 / B, device=dev)
     with Ph('coef'):
         coef = rnnt_grad_coef(lse, alpha, beta, diag_off, dy, tgt, tl, ul, 0)
-    per_utt = T * U1; ldg = (V + 15) // 16 * 16; ldh = J + 8
+    per_utt = T * U1; ldg = (V + 15) // 16 * 16; ldh = J
     with Ph('alloc/fill'):
         G = torch.empty(nb * per_utt, ldg, dtype=torch.bfloat16, device=dev)
-        H = torch.zeros(nb * per_utt, ldh, dtype=torch.bfloat16, device=dev); H[:, J] = 1.0
-        dW = torch.zeros(V, ldh, dtype=torch.float32, device=dev)
+        H = torch.empty(nb * per_utt, ldh, dtype=torch.bfloat16, device=dev)
+        dbp = torch.zeros(16, (V + 127) // 128 * 128, device=dev)
+        dWt = torch.zeros(J, ldg, dtype=torch.float32, device=dev)
         de = torch.empty(B, T, J, device=dev); dp = torch.zeros(B, U1, J, device=dev)
     for b0 in range(0, B, nb):
         b1 = min(B, b0 + nb); n = (b1 - b0) * per_utt
         with Ph('grad joint (+H)'):
             _lib.call("b200_joint_grad_chunk", ptr(e), ptr(p), ptr(w), ptr(bias), ptr(tgt), ptr(coef), i32(B), i32(T),
                       i32(U1), i32(V), i32(J), i32(0), jm._i64(b0 * per_utt), jm._i64(n), ptr(G), i32(ldg), ptr(H),
-                      i32(ldh), i32(0), st)
+                      i32(ldh), ptr(dbp), i32(0), st)
         Gv = G[:n, :V]
         with Ph('dH gemm'):
             dH = torch.mm(Gv, w, out_dtype=torch.float32)
         with Ph('dW gemm'):
-            dW += torch.mm(Gv.t(), H[:n], out_dtype=torch.float32)
+            dWt += torch.mm(H[:n].t(), G[:n], out_dtype=torch.float32)
         with Ph('dz reduce'):
             _lib.call("b200_joint_dz_reduce", ptr(dH), ptr(H), i32(ldh), i32(b1 - b0), i32(T), i32(U1), i32(J),
                       ptr(de[b0:b1]), ptr(dp[b0:b1]), st)

@@ -102,8 +102,10 @@ struct Params {
   const float4* coef;
   __nv_bfloat16* G;  // [ncells, ldg]
   int ldg;
-  __nv_bfloat16* H;  // optional [ncells, ldh]: the bf16 activations, for the dW GEMM
+  __nv_bfloat16* H;  // [ncells, ldh]: the bf16 activations (A operand, and for the dW GEMM)
   int ldh;
+  float* db_part;    // optional [16][ld_db]: partial column sums of G (= d b_out), accumulated
+  int ld_db;
 };
 
 struct Barriers {

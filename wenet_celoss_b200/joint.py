@@ -118,13 +118,16 @@ class _FusedJointLossFn(torch.autograd.Function):
                                   target_lengths, blank)
             per_utt = T * U1
             ldg = (V + 15) // 16 * 16  # 32-byte rows: the epilogue stores 32 bytes per thread
-            ldh = J + 8
+            ldh = J
             sms = torch.cuda.get_device_properties(dev).multi_processor_count
             nb = _chunk_utts(B, per_utt, ldg, sms)
             G = torch.empty(nb * per_utt, ldg, dtype=torch.bfloat16, device=dev)
-            H = torch.zeros(nb * per_utt, ldh, dtype=torch.bfloat16, device=dev)
-            H[:, J] = 1.0  # ones column: d b_out falls out of the dW GEMM
-            dW_aug = torch.zeros(V, ldh, dtype=torch.float32, device=dev)
+            H = torch.empty(nb * per_utt, ldh, dtype=torch.bfloat16, device=dev)
+            # d b_out = column sums of G: accumulated by the joint kernel's epilogue into 16
+            # partial rows (an augmented ones column made the dW GEMM 520 wide: 25 % slower)
+            db_part = torch.zeros(16, (V + _TILE_M - 1) // _TILE_M * _TILE_M, dtype=torch.float32,
+                                  device=dev)
+            dWt = torch.zeros(J, ldg, dtype=torch.float32, device=dev)  # d W_out^T, padded columns
             de = torch.empty(B, T, J, dtype=torch.float32, device=dev)
             dp = torch.zeros(B, U1, J, dtype=torch.float32, device=dev)
             for b0 in range(0, B, nb):
@@ -133,15 +136,14 @@ class _FusedJointLossFn(torch.autograd.Function):
                 _lib.call("b200_joint_grad_chunk", ptr(e32), ptr(p32), ptr(w_bf16), ptr(bias_pad),
                           ptr(targets), ptr(coef), i32(B), i32(T), i32(U1), i32(V), i32(J),
                           i32(blank), _i64(b0 * per_utt), _i64(n), ptr(G), i32(ldg), ptr(H), i32(ldh),
-                          i32(0), st)
-                Gv = G[:n, :V]
-                dH = torch.mm(Gv, w_bf16, out_dtype=torch.float32)        # [n, J]
-                dW_aug += torch.mm(Gv.t(), H[:n], out_dtype=torch.float32)  # [V, J+8]
+                          ptr(db_part), i32(0), st)
+                dH = torch.mm(G[:n, :V], w_bf16, out_dtype=torch.float32)  # [n, J]
+                dWt += torch.mm(H[:n].t(), G[:n], out_dtype=torch.float32)  # [J, ldg]
                 _lib.call("b200_joint_dz_reduce", ptr(dH), ptr(H), i32(ldh), i32(b1 - b0), i32(T),
                           i32(U1), i32(J), ptr(de[b0:b1]), ptr(dp[b0:b1]), st)
         dt_e, dt_p, dt_w, dt_b = ctx.in_dtypes
-        return (de.to(dt_e), dp.to(dt_p), dW_aug[:, :J].to(dt_w), dW_aug[:, J].to(dt_b), None, None,
-                None, None)
+        return (de.to(dt_e), dp.to(dt_p), dWt[:, :V].t().to(dt_w), db_part.sum(0)[:V].to(dt_b), None,
+                None, None, None)
 
 
 def _check_joint_module(joint) -> None:
