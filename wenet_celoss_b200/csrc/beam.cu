@@ -92,144 +92,7 @@ __global__ void init_rows_kernel(State S) {
   if (S.lens[b] > 0) S.row_list[atomicAdd(&S.n_rows[0], 1)] = b * S.beam;
 }
 
-// ---- LSTM layer over the live rows (one warp per hidden unit x 8 rows) ----
-__global__ void __launch_bounds__(256) lstm_kernel(Model M, State S, int layer, int frame) {
-  const int set = frame & 1;
-  // the other parity's row counter was last read one frame ago: reset it for this frame's update
-  if (layer == 0 && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) S.n_rows[set ^ 1] = 0;
-  const int n = S.n_rows[set];
-  const int g0 = blockIdx.y * 8;
-  if (g0 >= n) return;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int j = blockIdx.x * 8 + warp;
-  const int H = M.H, In = layer == 0 ? M.Emb : H;
-  if (j >= H) return;
-  float bsum[4];
-#pragma unroll
-  for (int g = 0; g < 4; ++g) bsum[g] = M.b_ih[layer][g * H + j] + M.b_hh[layer][g * H + j];
-  const float* wi = M.w_ih[layer] + (size_t)j * In;
-  const float* wh = M.w_hh[layer] + (size_t)j * H;
-  const int* list = S.row_list + set * S.n_rows_max;
-  const size_t lay = (size_t)S.n_rows_max * H;
-  for (int q = g0; q < min(n, g0 + 8); ++q) {
-    const int row = list[q];
-    const float* hin = S.cache_h + ((size_t)set * M.L + layer) * lay + (size_t)row * H;
-    const float* cin = S.cache_c + ((size_t)set * M.L + layer) * lay + (size_t)row * H;
-    const int len = S.hyp_len[set * S.n_rows_max + row];
-    const int tok = S.hyp[((size_t)set * S.n_rows_max + row) * S.max_len + len - 1];
-    const float* x = layer == 0 ? M.embed + (size_t)tok * In
-                                : S.new_h + (size_t)(layer - 1) * lay + (size_t)row * H;
-    float a[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int i = lane; i < In; i += 32) {
-      const float xv = x[i];
-#pragma unroll
-      for (int g = 0; g < 4; ++g) a[g] = fmaf(__ldg(wi + (size_t)g * H * In + i), xv, a[g]);
-    }
-    for (int i = lane; i < H; i += 32) {
-      const float hv = hin[i];
-#pragma unroll
-      for (int g = 0; g < 4; ++g) a[g] = fmaf(__ldg(wh + (size_t)g * H * H + i), hv, a[g]);
-    }
-#pragma unroll
-    for (int g = 0; g < 4; ++g) a[g] = warp_sum(a[g]) + bsum[g];
-    if (lane == 0) {
-      const float ig = sigm(a[0]), fg = sigm(a[1]), gg = tanhf(a[2]), og = sigm(a[3]);
-      const float cn = fg * cin[j] + ig * gg;
-      S.new_c[(size_t)layer * lay + (size_t)row * H + j] = cn;
-      S.new_h[(size_t)layer * lay + (size_t)row * H + j] = og * tanhf(cn);
-    }
-  }
-}
-
-__global__ void __launch_bounds__(256) pred_z_kernel(Model M, State S, int frame) {
-  const int set = frame & 1;
-  const int n = S.n_rows[set];
-  const int g0 = blockIdx.y * 8;
-  if (g0 >= n) return;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int j = blockIdx.x * 8 + warp;
-  if (j >= M.J) return;
-  const int H = M.H;
-  const float* w = M.w_c + (size_t)j * H;
-  const float bc = M.b_c[j];
-  const int* list = S.row_list + set * S.n_rows_max;
-  const size_t lay = (size_t)S.n_rows_max * H;
-  for (int q = g0; q < min(n, g0 + 8); ++q) {
-    const int row = list[q];
-    const float* h = S.new_h + (size_t)(M.L - 1) * lay + (size_t)row * H;
-    float a = 0.f;
-    for (int i = lane; i < H; i += 32) a = fmaf(__ldg(w + i), h[i], a);
-    a = warp_sum(a) + bc;
-    if (lane == 0) {
-      const int b = row / S.beam;
-      const float e = S.enc_proj[((size_t)b * S.T + frame) * M.J + j];
-      S.z[(size_t)row * M.J + j] = tanhf(e + a);
-    }
-  }
-}
-
-// ---- logits[row, v] for a tile of 32 vocabulary rows x all live rows ----
-constexpr int kVT = 32, kUG = 16, kPad = 4;
-
-__global__ void __launch_bounds__(128) logits_kernel(Model M, State S, int frame) {
-  extern __shared__ float sm[];
-  const int set = frame & 1;
-  const int n = S.n_rows[set];
-  if (n == 0) return;
-  const int J = M.J, ld = J + kPad;
-  float* sw = sm;
-  float* sz = sm + kVT * ld;
-  const int v0 = blockIdx.x * kVT;
-  const int tid = threadIdx.x;
-  for (int i = tid; i < kVT * (J / 4); i += blockDim.x) {
-    const int r = i / (J / 4), k4 = i - r * (J / 4);
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (v0 + r < M.V) v = *reinterpret_cast<const float4*>(M.w_out + (size_t)(v0 + r) * J + k4 * 4);
-    *reinterpret_cast<float4*>(sw + r * ld + k4 * 4) = v;
-  }
-  const int u2 = tid & 7, rs = tid >> 3;
-  const float b0 = (v0 + rs < M.V) ? M.b_out[v0 + rs] : 0.f;
-  const float b1 = (v0 + rs + 16 < M.V) ? M.b_out[v0 + rs + 16] : 0.f;
-  const int* list = S.row_list + set * S.n_rows_max;
-  for (int g0 = 0; g0 < n; g0 += kUG) {
-    __syncthreads();
-    for (int i = tid; i < kUG * (J / 4); i += blockDim.x) {
-      const int uu = i / (J / 4), k4 = i - uu * (J / 4);
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (g0 + uu < n) v = *reinterpret_cast<const float4*>(S.z + (size_t)list[g0 + uu] * J + k4 * 4);
-      *reinterpret_cast<float4*>(sz + uu * ld + k4 * 4) = v;
-    }
-    __syncthreads();
-    float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f;
-    const float* w0 = sw + rs * ld;
-    const float* w1 = sw + (rs + 16) * ld;
-    const float* z0 = sz + (2 * u2) * ld;
-    const float* z1 = sz + (2 * u2 + 1) * ld;
-#pragma unroll 4
-    for (int k = 0; k < J; k += 4) {
-      const float4 wa = *reinterpret_cast<const float4*>(w0 + k);
-      const float4 wb = *reinterpret_cast<const float4*>(w1 + k);
-      const float4 za = *reinterpret_cast<const float4*>(z0 + k);
-      const float4 zb = *reinterpret_cast<const float4*>(z1 + k);
-      a00 = fmaf(wa.x, za.x, a00); a00 = fmaf(wa.y, za.y, a00); a00 = fmaf(wa.z, za.z, a00); a00 = fmaf(wa.w, za.w, a00);
-      a01 = fmaf(wa.x, zb.x, a01); a01 = fmaf(wa.y, zb.y, a01); a01 = fmaf(wa.z, zb.z, a01); a01 = fmaf(wa.w, zb.w, a01);
-      a10 = fmaf(wb.x, za.x, a10); a10 = fmaf(wb.y, za.y, a10); a10 = fmaf(wb.z, za.z, a10); a10 = fmaf(wb.w, za.w, a10);
-      a11 = fmaf(wb.x, zb.x, a11); a11 = fmaf(wb.y, zb.y, a11); a11 = fmaf(wb.z, zb.z, a11); a11 = fmaf(wb.w, zb.w, a11);
-    }
-    const int ra = g0 + 2 * u2, rb = ra + 1;
-    if (ra < n) {
-      float* o = S.logits + (size_t)list[ra] * M.V + v0;
-      if (v0 + rs < M.V) o[rs] = a00 + b0;
-      if (v0 + rs + 16 < M.V) o[rs + 16] = a10 + b1;
-    }
-    if (rb < n) {
-      float* o = S.logits + (size_t)list[rb] * M.V + v0;
-      if (v0 + rs < M.V) o[rs] = a01 + b0;
-      if (v0 + rs + 16 < M.V) o[rs + 16] = a11 + b1;
-    }
-  }
-}
-
+#include "beam_gemm.inc"
 #include "beam_select.inc"
 
 }  // namespace bs
