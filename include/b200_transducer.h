@@ -174,6 +174,13 @@ int b200_joint_grad_chunk(const float* e, const float* p, const void* w_bf16,
 int b200_joint_dz_reduce(const float* dH, const void* H, int ldh, int nb, int T, int U1, int J,
                          float* de, float* dp, b200_stream_t stream);
 
+/* weight gradient of ffn_out for one chunk: dW [V, J] fp32 += G^T H (autograd of
+ * joint.py:68-69), G [n, ldg] bf16 and H [n, ldh] bf16 as written by b200_joint_grad_chunk.
+ * 2-CTA tcgen05 kernel (cta_group::2, M = 256, both operands MN-major through TMA); J must
+ * be a multiple of 128 in [128, 512]; dW must be zeroed before the first chunk. */
+int b200_joint_dw(const void* G, int ldg, const void* H, int ldh, long long n, int V, int J,
+                  float* dW, int max_ctas, b200_stream_t stream);
+
 /* ---- Batched RNN-T greedy search ------------------------------------------
  * replaces the Python loop of wenet/transducer/search/greedy_search.py:34-176 (core
  * algorithm: "greedy_search copy.py":6-63): per lattice step predictor.forward_step

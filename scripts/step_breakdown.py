@@ -36,7 +36,7 @@ def step():
         G = torch.empty(nb * per_utt, ldg, dtype=torch.bfloat16, device=dev)
         H = torch.empty(nb * per_utt, ldh, dtype=torch.bfloat16, device=dev)
         dbp = torch.zeros(16, (V + 127) // 128 * 128, device=dev)
-        dWt = torch.zeros(J, ldg, dtype=torch.float32, device=dev)
+        dW = torch.zeros(V, J, dtype=torch.float32, device=dev)
         de = torch.empty(B, T, J, device=dev); dp = torch.zeros(B, U1, J, device=dev)
     for b0 in range(0, B, nb):
         b1 = min(B, b0 + nb); n = (b1 - b0) * per_utt
@@ -48,11 +48,12 @@ def step():
         with Ph('dH gemm'):
             dH = torch.mm(Gv, w, out_dtype=torch.float32)
         with Ph('dW gemm'):
-            dWt += torch.mm(H[:n].t(), G[:n], out_dtype=torch.float32)
+            jm.joint_dw(G, H, n, V, J, dW)
         with Ph('dz reduce'):
             _lib.call("b200_joint_dz_reduce", ptr(dH), ptr(H), i32(ldh), i32(b1 - b0), i32(T), i32(U1), i32(J),
                       ptr(de[b0:b1]), ptr(dp[b0:b1]), st)
-for it in range(3):
+iters = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+for it in range(iters):
     acc.clear()
     t0 = torch.cuda.Event(True); t1 = torch.cuda.Event(True)
     t0.record(); step(); t1.record(); torch.cuda.synchronize()

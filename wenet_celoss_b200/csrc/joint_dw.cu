@@ -1,0 +1,400 @@
+// dW_out += G^T H : the weight-gradient GEMM of the fused joint backward
+// (autograd of ffn_out in wenet/transducer/joint.py:68-69, reached from
+// wenet/transducer/transducer.py:132-147), as a 2-CTA tcgen05 kernel.
+//
+//   G [n, ldg] bf16 = d loss / d logits of a chunk of n lattice cells (joint_kernel<GRAD>)
+//   H [n, ldh] bf16 = tanh(e + p) of the same cells
+//   dW [V, J]  fp32 += sum over cells of G[c, v] * H[c, j]
+//
+// The contraction runs over CELLS (K = n, up to 1.6 M at cfg3) and the output is tiny
+// (V x J), so both operands are "MN-major" for the tensor core: rows of G / H are K slices.
+// TMA brings [64 cells x 64 v] and [64 cells x 64 j] boxes (SWIZZLE_128B) straight from the
+// row-major scratch; the shared-memory descriptors describe them as MN-major operands
+// (LBO = distance between 64-wide MN groups, SBO = distance between 8-row K groups).
+//
+// One CTA pair (cluster of 2, cta_group::2) owns a [256 v x J] output tile: M = 256 (128 rows of
+// G^T per CTA), N = J as up to two accumulators of 256 columns - all 512 TMEM columns of both
+// SMs - so every byte staged in shared memory feeds 2*256*J/(128 + J/2) flop: 0.0059 B/flop at
+// J = 512, against 0.0117 for a 128 x 256 single-CTA tile.  Work = (V tile, K split) units dealt
+// round-robin to the pairs, V tile fastest, so the pairs that run at the same time read the
+// SAME cells of H (L2 hits) and G is read exactly once.  Accumulators are flushed with
+// 16-byte atomics at the end of a unit (3 units per pair per launch).
+#include <cuda.h>
+
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace b200 {
+namespace dw {
+
+constexpr int kBlockK = 64;                 // cells per pipeline stage
+constexpr int kStages = 4;
+constexpr int kTileV = 256;                 // V rows per CTA pair
+constexpr int kBoxBytes = 64 * kBlockK * 2;  // one SW128 box: 64 (mn) x 64 (k) bf16 = 8 KB
+constexpr int kThreads = 192;               // warp 0 TMA, warp 1 MMA + TMEM, warps 2-5 epilogue
+constexpr int kMaxJ = 512;
+
+struct Params {
+  int V, J;
+  long long n;        // cells
+  int kblocks;        // ceil(n / 64)
+  int nvt;            // V tiles of 256
+  int nsplit;         // K splits
+  float* dW;          // [V, J] fp32, accumulated
+};
+
+__host__ __device__ constexpr int stage_bytes(int J) { return (2 + J / 128) * kBoxBytes; }
+
+// MN-major SWIZZLE_128B operand made of 8 KB boxes [64 k rows x 128 bytes]:
+// LBO = bytes between consecutive 64-element MN groups, SBO = bytes between 8-row K groups.
+__device__ __forceinline__ uint64_t make_sw128_mnmajor_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(kBoxBytes >> 4) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// kind::f16, bf16 x bf16 -> f32, both operands MN-major (bits 15, 16)
+__host__ __device__ constexpr uint32_t make_idesc_mn(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_id_x() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t nclusters_x() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%nclusterid.x;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::
+                   : "memory");
+}
+// address of the same shared-memory variable in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr)
+               : "memory");
+}
+// TMA load of one box into THIS CTA's shared memory; completion bytes go to the mbarrier at
+// cluster address `bar` (the leader CTA's) - the pair's MMA consumes both CTAs' stages
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* m, uint32_t bar,
+                                                 int c0, int c1, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      ".L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst),
+      "l"(m), "r"(bar), "r"(c0), "r"(c1), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem),
+               "r"(ncols)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish_pair() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols)
+               : "memory");
+}
+// D[tmem, both CTAs] (+)= A[smem of both CTAs] * B[smem of both CTAs]; issued by the leader CTA
+__device__ __forceinline__ void umma_bf16_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+                                               uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on the mbarrier at this shared-memory offset in BOTH CTAs once all MMAs issued so far
+// have completed
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 "
+      "[%0], %1;" ::"r"(bar),
+      "h"((uint16_t)3)
+      : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+    joint_dw_kernel(const __grid_constant__ CUtensorMap gmap, const __grid_constant__ CUtensorMap hmap,
+                    const Params P) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bars[2 * kStages + 2];
+  __shared__ uint32_t tmem_holder;
+
+  const uint32_t rank = cluster_ctarank();
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int J = P.J;
+  const int sbytes = stage_bytes(J);
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar0 = ptx::smem_u32(bars);
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (kStages + s); };
+  const uint32_t acc_full = bar0 + 8u * (2 * kStages);
+  const uint32_t acc_empty = bar0 + 8u * (2 * kStages + 1);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      ptx::mbar_init(full_bar(s), 1);
+      ptx::mbar_init(empty_bar(s), 1);
+    }
+    ptx::mbar_init(acc_full, 1);
+    ptx::mbar_init(acc_empty, 8);  // 4 epilogue warps in each CTA of the pair
+    ptx::fence_barrier_init();
+    ptx::prefetch_tensormap(&gmap);
+    ptx::prefetch_tensormap(&hmap);
+  }
+  if (warp == 1) {
+    tmem_alloc_pair(ptx::smem_u32(&tmem_holder), 512);
+    tmem_relinquish_pair();
+  }
+  ptx::tc_fence_before();
+  cluster_sync_all();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = tmem_holder;
+
+  const int nunits = P.nvt * P.nsplit;
+  const int pair = (int)cluster_id_x();
+  const int npairs = (int)nclusters_x();
+  const int nacc = (J + 255) / 256;
+
+  if (warp == 0) {
+    // ---------------- TMA producer (both CTAs; each loads its own half of the operands)
+    const uint32_t leader_full0 = map_to_cta(full_bar(0), 0);
+    const uint64_t pol_stream = ptx::l2_policy_evict_first();
+    const uint64_t pol_keep = ptx::l2_policy_evict_last();
+    long long it = 0;
+    for (int u = pair; u < nunits; u += npairs) {
+      const int vt = u % P.nvt, ks = u / P.nvt;
+      const int kb0 = (int)((long long)P.kblocks * ks / P.nsplit);
+      const int kb1 = (int)((long long)P.kblocks * (ks + 1) / P.nsplit);
+      const int v0 = vt * kTileV + (int)rank * 128;
+      for (int kb = kb0; kb < kb1; ++kb, ++it) {
+        const int s = (int)(it % kStages);
+        const uint32_t ph = (uint32_t)((it / kStages) & 1);
+        ptx::mbar_wait(empty_bar(s), ph ^ 1u);
+        if (ptx::elect_one()) {
+          if (rank == 0) ptx::mbar_arrive_expect_tx(full_bar(s), 2u * (uint32_t)sbytes);
+          const uint32_t bar = leader_full0 + 8u * s;
+          const uint32_t dst = smem_base + (uint32_t)s * sbytes;
+          const int c = kb * kBlockK;
+          // A: G^T rows v0 .. v0+127 (two boxes of 64 v); read exactly once: evict first
+          tma_load_2d_pair(dst, &gmap, bar, v0, c, pol_stream);
+          tma_load_2d_pair(dst + kBoxBytes, &gmap, bar, v0 + 64, c, pol_stream);
+          // B: this CTA's half of each accumulator's J range; shared by all V tiles: keep in L2
+          uint32_t bdst = dst + 2 * kBoxBytes;
+          for (int a = 0; a < nacc; ++a) {
+            const int Na = min(256, J - 256 * a);
+            const int j0 = 256 * a + (int)rank * (Na / 2);
+            for (int i = 0; i < Na / 128; ++i, bdst += kBoxBytes)
+              tma_load_2d_pair(bdst, &hmap, bar, j0 + 64 * i, c, pol_keep);
+          }
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------- MMA issuer (leader CTA only)
+    if (rank == 0) {
+      long long it = 0;
+      int nu = 0;
+      for (int u = pair; u < nunits; u += npairs) {
+        const int ks = u / P.nvt;
+        const int kb0 = (int)((long long)P.kblocks * ks / P.nsplit);
+        const int kb1 = (int)((long long)P.kblocks * (ks + 1) / P.nsplit);
+        if (kb1 <= kb0) continue;  // (the epilogue skips empty units the same way)
+        // accumulators drained by both CTAs' epilogues?
+        ptx::mbar_wait(acc_empty, (uint32_t)((nu & 1) ^ 1));
+        ++nu;
+        ptx::tc_fence_after();
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+          const int s = (int)(it % kStages);
+          const uint32_t ph = (uint32_t)((it / kStages) & 1);
+          ptx::mbar_wait(full_bar(s), ph);
+          ptx::tc_fence_after();
+          if (ptx::elect_one()) {
+            const uint32_t sa = smem_base + (uint32_t)s * sbytes;
+#pragma unroll
+            for (int k = 0; k < kBlockK / 16; ++k) {
+              const uint64_t adesc = make_sw128_mnmajor_desc(sa + k * 2048);
+              uint32_t sb = sa + 2 * kBoxBytes;
+              for (int a = 0; a < nacc; ++a) {
+                const int Na = min(256, J - 256 * a);
+                const uint64_t bdesc = make_sw128_mnmajor_desc(sb + k * 2048);
+                umma_bf16_pair(tmem_base + 256u * a, adesc, bdesc, make_idesc_mn(256, Na),
+                               (kb > kb0 || k > 0) ? 1u : 0u);
+                sb += (Na / 128) * kBoxBytes;
+              }
+            }
+            umma_commit_pair(empty_bar(s));
+            if (kb == kb1 - 1) umma_commit_pair(acc_full);
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else {
+    // ---------------- epilogue (both CTAs): TMEM -> registers -> 16-byte atomics on dW
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    int nu = 0;
+    for (int u = pair; u < nunits; u += npairs) {
+      const int vt = u % P.nvt, ks = u / P.nvt;
+      const int kb0 = (int)((long long)P.kblocks * ks / P.nsplit);
+      const int kb1 = (int)((long long)P.kblocks * (ks + 1) / P.nsplit);
+      if (kb1 <= kb0) continue;
+      ptx::mbar_wait(acc_full, (uint32_t)(nu & 1));
+      ++nu;
+      ptx::tc_fence_after();
+      const int v = vt * kTileV + (int)rank * 128 + q * 32 + lane;
+      float* row = P.dW + (long long)v * J;
+      for (int c0 = 0; c0 < J; c0 += 32) {
+        uint32_t r[32];
+        ptx::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+        ptx::tmem_ld_wait();
+        if (v < P.V) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 4)
+            atomicAdd(reinterpret_cast<float4*>(row + c0 + i),
+                      make_float4(__uint_as_float(r[i]), __uint_as_float(r[i + 1]),
+                                  __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3])));
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(map_to_cta(acc_empty, 0));
+    }
+  }
+
+  // teardown: both CTAs done with TMEM and with each other's shared memory / barriers
+  ptx::tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) tmem_dealloc_pair(tmem_base, 512);
+}
+
+}  // namespace dw
+}  // namespace b200
+
+using namespace b200;
+
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn dw_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// [rows, cols] bf16 with a row pitch; box = 64 columns x 64 rows, SWIZZLE_128B; columns / rows
+// outside the tensor read as zero (they then add nothing to dW)
+int make_dw_map(CUtensorMap* map, const void* ptr, long long rows, int cols, long long pitch_bytes) {
+  EncodeTiledFn fn = dw_encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled entry point not available");
+    return B200_ERR_CUDA;
+  }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)pitch_bytes};
+  cuuint32_t box[2] = {64, (cuuint32_t)dw::kBlockK};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box,
+                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return B200_ERR_CUDA;
+  }
+  return B200_OK;
+}
+
+}  // namespace
+
+extern "C" int b200_joint_dw(const void* G, int ldg, const void* H, int ldh, long long n, int V, int J,
+                             float* dW, int max_ctas, b200_stream_t stream) {
+  B200_CHECK_ARG(G && H && dW, "b200_joint_dw: null pointer");
+  B200_CHECK_ARG(n > 0 && V > 0, "b200_joint_dw: bad shape n=%lld V=%d", n, V);
+  B200_CHECK_ARG(J >= 128 && J <= dw::kMaxJ && J % 128 == 0,
+                 "b200_joint_dw: join dim J=%d must be a multiple of 128 in [128, 512]", J);
+  B200_CHECK_ARG(ldg >= V && ldg % 8 == 0 && ((uintptr_t)G & 15) == 0,
+                 "b200_joint_dw: ldg=%d must be >= V and a multiple of 8, G 16-byte aligned", ldg);
+  B200_CHECK_ARG(ldh >= J && ldh % 8 == 0 && ((uintptr_t)H & 15) == 0,
+                 "b200_joint_dw: ldh=%d must be >= J and a multiple of 8, H 16-byte aligned", ldh);
+  B200_CHECK_ARG(((uintptr_t)dW & 15) == 0, "b200_joint_dw: dW must be 16-byte aligned");
+  B200_CHECK_ARG((n + dw::kBlockK - 1) / dw::kBlockK < (1ll << 31), "b200_joint_dw: n too large");
+  CUtensorMap gmap, hmap;
+  if (int rc = make_dw_map(&gmap, G, n, V, (long long)ldg * 2)) return rc;
+  if (int rc = make_dw_map(&hmap, H, n, J, (long long)ldh * 2)) return rc;
+  int sms = 0, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (sms <= 0) sms = 148;
+  int ctas = sms & ~1;
+  if (max_ctas > 0 && max_ctas < ctas) ctas = max_ctas & ~1;
+  if (ctas < 2) ctas = 2;
+  const int npairs = ctas / 2;
+  dw::Params P{};
+  P.V = V;
+  P.J = J;
+  P.n = n;
+  P.kblocks = (int)((n + dw::kBlockK - 1) / dw::kBlockK);
+  P.nvt = (V + dw::kTileV - 1) / dw::kTileV;
+  // K splits: fill `rounds` rounds of the pairs as evenly as possible (V tile fastest), units of
+  // at least 64 k-blocks so the accumulator flush stays below 2 % of a unit
+  int best = 1;
+  {
+    const int max_split = P.kblocks / 64 > 1 ? P.kblocks / 64 : 1;
+    double best_eff = 0.0;
+    for (int s = 1; s <= max_split && s <= 4 * npairs; ++s) {
+      const int units = P.nvt * s;
+      const int rounds = (units + npairs - 1) / npairs;
+      const double eff = (double)units / ((double)rounds * npairs);
+      if (eff > best_eff + 0.02) {
+        best_eff = eff;
+        best = s;
+      }
+    }
+  }
+  P.nsplit = best;
+  P.dW = dW;
+  const int smem = dw::kStages * dw::stage_bytes(J) + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(dw::joint_dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         dw::kStages * dw::stage_bytes(dw::kMaxJ) + 1024));
+    attr_set = true;
+  }
+  int grid = 2 * npairs;
+  if (P.nvt * P.nsplit < npairs) grid = 2 * P.nvt * P.nsplit;
+  dw::joint_dw_kernel<<<grid, dw::kThreads, smem, (cudaStream_t)stream>>>(gmap, hmap, P);
+  B200_CHECK_LAUNCH("joint_dw_kernel");
+  return B200_OK;
+}

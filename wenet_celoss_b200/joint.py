@@ -16,7 +16,8 @@ Forward : enc_ffn / pred_ffn (library GEMMs, joint.py:55-56) -> tcgen05 joint ke
           streaming log-softmax epilogue (lse, lp_blank, lp_emit per cell) -> lattice kernel.
 Backward: per chunk of whole utterances, the same tcgen05 mainloop recomputes the logits
           tile and its epilogue writes G = d loss / d logits (bf16) into a bounded scratch;
-          dH = G W and dW = G^T [H | 1] are plain library GEMMs on that scratch; the
+          dW = G^T H is the 2-CTA tcgen05 kernel of csrc/joint_dw.cu (both operands MN-major,
+          split over cells), dH = G W a plain library GEMM on that scratch; the
           tanh' / sum-over-u / sum-over-t reduction gives d e and d p.
 Operands of the big GEMMs are bf16 (fp32 accumulate); tolerance vs the fp32 reference is
 rtol 1e-2 (north_star's bf16 bar).
@@ -32,18 +33,18 @@ from .rnnt import rnnt_grad_coef, rnnt_lattice
 
 _TILE_N = 256
 _TILE_M = 128
-SCRATCH_BYTES = 4 << 30  # bound on the bf16 G scratch of the backward pass
+SCRATCH_BYTES = 20 << 30  # bound on the bf16 G scratch of the backward pass (cfg3: 16.2 GB, one chunk)
 
 
 def _chunk_utts(B: int, per_utt: int, ldg: int, sms: int) -> int:
     """Utterances per backward chunk: whole utterances, G scratch <= SCRATCH_BYTES, and as
     few idle SMs in the last wave of 128-cell tiles as possible."""
     cap = max(1, min(B, SCRATCH_BYTES // (per_utt * ldg * 2)))
-    best, best_eff = 1, 0.0
-    for nb in range(1, cap + 1):
+    best, best_eff = cap, 0.0
+    for nb in range(cap, 0, -1):  # the largest chunk, unless a smaller one wastes 2 % fewer SM slots
         tiles = -(-nb * per_utt // _TILE_M)
         eff = tiles / (sms * -(-tiles // sms))
-        if eff > best_eff + 1e-3:
+        if eff > best_eff + 0.02:
             best, best_eff = nb, eff
     return best
 
@@ -81,6 +82,13 @@ def joint_logprobs(e, p, w_bf16, bias_pad, targets, logit_lengths, target_length
               i32(blank), ptr(lse), ptr(lpb), ptr(lpe), ptr(bound), i32(max_ctas),
               _lib.stream_handle(e.device))
     return lse, lpb, lpe
+
+
+def joint_dw(G, H, n, V, J, dW, max_ctas: int = 0):
+    """dW [V, J] fp32 += G[:n, :V]^T H[:n, :J] (bf16 operands) through the 2-CTA tcgen05 kernel."""
+    _lib.call("b200_joint_dw", ptr(G), i32(G.stride(0)), ptr(H), i32(H.stride(0)), _i64(n), i32(V),
+              i32(J), ptr(dW), i32(max_ctas), _lib.stream_handle(G.device))
+    return dW
 
 
 class _FusedJointLossFn(torch.autograd.Function):
@@ -127,7 +135,8 @@ class _FusedJointLossFn(torch.autograd.Function):
             # partial rows (an augmented ones column made the dW GEMM 520 wide: 25 % slower)
             db_part = torch.zeros(16, (V + _TILE_M - 1) // _TILE_M * _TILE_M, dtype=torch.float32,
                                   device=dev)
-            dWt = torch.zeros(J, ldg, dtype=torch.float32, device=dev)  # d W_out^T, padded columns
+            own_dw = J % 128 == 0  # csrc/joint_dw.cu; other join dims: library GEMM
+            dW = torch.zeros(V, J, dtype=torch.float32, device=dev)
             de = torch.empty(B, T, J, dtype=torch.float32, device=dev)
             dp = torch.zeros(B, U1, J, dtype=torch.float32, device=dev)
             for b0 in range(0, B, nb):
@@ -138,11 +147,14 @@ class _FusedJointLossFn(torch.autograd.Function):
                           i32(blank), _i64(b0 * per_utt), _i64(n), ptr(G), i32(ldg), ptr(H), i32(ldh),
                           ptr(db_part), i32(0), st)
                 dH = torch.mm(G[:n, :V], w_bf16, out_dtype=torch.float32)  # [n, J]
-                dWt += torch.mm(H[:n].t(), G[:n], out_dtype=torch.float32)  # [J, ldg]
+                if own_dw:
+                    joint_dw(G, H, n, V, J, dW)
+                else:
+                    dW += torch.mm(G[:n, :V].t(), H[:n], out_dtype=torch.float32)
                 _lib.call("b200_joint_dz_reduce", ptr(dH), ptr(H), i32(ldh), i32(b1 - b0), i32(T),
                           i32(U1), i32(J), ptr(de[b0:b1]), ptr(dp[b0:b1]), st)
         dt_e, dt_p, dt_w, dt_b = ctx.in_dtypes
-        return (de.to(dt_e), dp.to(dt_p), dWt[:, :V].t().to(dt_w), db_part.sum(0)[:V].to(dt_b), None,
+        return (de.to(dt_e), dp.to(dt_p), dW.to(dt_w), db_part.sum(0)[:V].to(dt_b), None,
                 None, None, None)
 
 
