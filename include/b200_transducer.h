@@ -218,6 +218,22 @@ int b200_rnnt_beam(const float* enc_proj, const float* ctc_lp, const int32_t* le
                    int32_t* out_hyp, int32_t* out_len, double* out_score, int32_t* out_n,
                    void* workspace, size_t ws_bytes, b200_stream_t stream);
 
+/* ---- Batched CTC prefix beam search ------------------------------------------
+ * replaces the Python loop of ASRModel._ctc_prefix_beam_search
+ * (wenet/transformer/asr_model.py:326-409; C++ twin runtime/core/decoder/
+ * ctc_prefix_beam_search.cc:107-200), reached from transducer_attention_rescoring
+ * (wenet/transducer/transducer.py:447-456).  logp [B,T,V] fp32 = CTC.log_softmax
+ * (ctc.py:66-74); per frame: top-k (k = beam), blank / repeat / extend updates of
+ * (pb, pnb) in fp64 with log_add (common.py:268-276), stable sort by log_add(pb,pnb),
+ * keep beam.  One CTA per utterance, prefixes in a trie inside the workspace.
+ * Outputs: out_tokens [B,beam,T] int32 (first out_len entries valid), out_len [B,beam]
+ * (-1 = no hypothesis), out_score [B,beam] fp64, out_n [B]. */
+size_t b200_ctc_prefix_beam_workspace_bytes(int B, int T, int beam);
+int b200_ctc_prefix_beam(const float* logp, const int32_t* lens, int B, int T, int V,
+                         int beam, int blank, int32_t* out_tokens, int32_t* out_len,
+                         double* out_score, int32_t* out_n, void* workspace,
+                         size_t ws_bytes, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -275,3 +275,36 @@ def beam_search_best(model, enc_out, **kw) -> Tuple[List[int], float]:
     """(hyp without the seed blank, score) as Transducer.beam_search returns (transducer.py:377)."""
     beam = prefix_beam_search(model, enc_out, **kw)
     return beam[0].hyp[1:], beam[0].score
+
+
+def ctc_prefix_beam_search(ctc_probs: torch.Tensor, beam_size: int, blank: int = 0):
+    """CTC prefix beam search over the log-probs of one utterance ``[T,V]`` (restates
+    wenet/transformer/asr_model.py:370-408; blank is hard-wired to 0 there).  Returns
+    ``[(prefix tuple, log_add(pb, pnb)), ...]`` best first."""
+    from collections import defaultdict
+    ninf = -float("inf")
+    cur = [(tuple(), (0.0, ninf))]
+    for t in range(ctc_probs.size(0)):
+        logp = ctc_probs[t]
+        nxt = defaultdict(lambda: (ninf, ninf))
+        _, top_ix = logp.topk(beam_size)
+        for s in top_ix.tolist():
+            ps = logp[s].item()
+            for prefix, (pb, pnb) in cur:
+                last = prefix[-1] if prefix else None
+                if s == blank:
+                    n_pb, n_pnb = nxt[prefix]
+                    nxt[prefix] = (log_add([n_pb, pb + ps, pnb + ps]), n_pnb)
+                elif s == last:
+                    n_pb, n_pnb = nxt[prefix]
+                    nxt[prefix] = (n_pb, log_add([n_pnb, pnb + ps]))
+                    ext = prefix + (s,)
+                    n_pb, n_pnb = nxt[ext]
+                    nxt[ext] = (n_pb, log_add([n_pnb, pb + ps]))
+                else:
+                    ext = prefix + (s,)
+                    n_pb, n_pnb = nxt[ext]
+                    nxt[ext] = (n_pb, log_add([n_pnb, pb + ps, pnb + ps]))
+        ranked = sorted(nxt.items(), key=lambda kv: log_add(list(kv[1])), reverse=True)  # stable
+        cur = ranked[:beam_size]
+    return [(prefix, log_add([pb, pnb])) for prefix, (pb, pnb) in cur]

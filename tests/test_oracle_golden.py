@@ -134,3 +134,29 @@ def test_log_add_and_add_blank():
     assert abs(orc.log_add([0.0, 0.0]) - math.log(2)) < 1e-15
     ys = torch.tensor([[1, 2, 3], [4, -1, -1]])
     assert orc.add_blank(ys, 0, -1).tolist() == [[0, 1, 2, 3], [0, 4, 0, 0]]
+
+
+# ---- CTC prefix beam search ---------------------------------------------------------------
+# Known-answer test of the reference itself: runtime/core/test/ctc_prefix_beam_search_test.cc:30-61
+# (3 frames x 3 classes, beam 3; prefix scores 0.2185 / 0.1550 / 0.1525).
+KAT_PROBS = [[0.25, 0.40, 0.35], [0.40, 0.35, 0.25], [0.10, 0.50, 0.40]]
+KAT_HYPS = [(2, 1), (1, 2), (1,)]
+KAT_SCORES = [0.2185, 0.1550, 0.1525]
+
+
+def test_ctc_prefix_beam_search_reference_known_answer():
+    hyps = orc.ctc_prefix_beam_search(torch.log(torch.tensor(KAT_PROBS)), 3)
+    assert [h[0] for h in hyps] == KAT_HYPS
+    np.testing.assert_allclose(np.exp([h[1] for h in hyps]), KAT_SCORES, rtol=1e-6)
+
+
+def test_ctc_prefix_beam_search_matches_reference(golden):
+    d = golden("ctc_search")
+    for name in d["names"]:
+        logits = torch.from_numpy(d[f"{name}.logits"])
+        beam = int(d[f"{name}.beam"])
+        hyps = orc.ctc_prefix_beam_search(torch.log_softmax(logits.unsqueeze(0), dim=2)[0], beam)
+        assert len(hyps) == int(d[f"{name}.n"])
+        for k, (prefix, score) in enumerate(hyps):
+            assert list(prefix) == d[f"{name}.tokens"][k][:d[f"{name}.lens"][k]].tolist(), (name, k)
+            np.testing.assert_allclose(score, d[f"{name}.scores"][k], rtol=1e-12)

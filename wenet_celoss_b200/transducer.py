@@ -140,6 +140,10 @@ def patch_transducer(model: torch.nn.Module) -> torch.nn.Module:
             raise TypeError(f"patch_transducer expects a Transducer-like module (missing .{attr})")
     if getattr(model, "ctc", None) is not None:
         patch_ctc(model.ctc)
+        if hasattr(model, "_forward_encoder"):  # ASRModel's CTC prefix beam search (asr_model.py:326-443)
+            from . import ctc_search
+            model._ctc_prefix_beam_search = types.MethodType(ctc_search._ctc_prefix_beam_search, model)
+            model.ctc_prefix_beam_search = types.MethodType(ctc_search.ctc_prefix_beam_search, model)
     model.forward = types.MethodType(transducer_forward, model)
     model._cal_transducer_score = types.MethodType(transducer_score, model)
     model.greedy_search = types.MethodType(transducer_greedy_search, model)
