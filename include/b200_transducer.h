@@ -234,6 +234,18 @@ int b200_ctc_prefix_beam(const float* logp, const int32_t* lens, int B, int T, i
                          double* out_score, int32_t* out_n, void* workspace,
                          size_t ws_bytes, b200_stream_t stream);
 
+/* ---- Batched CTC forced alignment -----------------------------------------------
+ * replaces forced_align (wenet/utils/ctc_util.py:27-83, driven by wenet/bin/alignment.py):
+ * Viterbi over the blank-interleaved labels, fp32 max/add only (bit-identical alignments,
+ * the reference's negative-index wrap of state 0 included).  logp [B,T,V] fp32 log-probs,
+ * ys_pad [B,Lmax] int64, hlens / ys_lens [B] (ys_lens >= 1); alignment [B,T] int32 = token
+ * per frame, -1 beyond hlens.  workspace: back-pointers [B,T,2*Lmax+1] int16. */
+size_t b200_ctc_forced_align_workspace_bytes(int B, int T, int Lmax);
+int b200_ctc_forced_align(const float* logp, const int64_t* ys_pad, const int32_t* hlens,
+                          const int32_t* ys_lens, int B, int T, int V, int Lmax, int blank,
+                          int32_t* alignment, void* workspace, size_t ws_bytes,
+                          b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -85,6 +85,25 @@ def main():
         names.append(name)
         print(f"{name}: T={T} V={logits.size(1)} beam={beam} best={hyps[0][0][:8]}... score={hyps[0][1]:.6f}")
     blob["names"] = np.array(names)
+    # ---- forced alignment: the real forced_align (wenet/utils/ctc_util.py:27-83)
+    from wenet.utils.ctc_util import forced_align as ref_align
+    g = torch.Generator().manual_seed(123)
+    anames = []
+    for name, T, V, y in [("plain", 30, 20, [3, 7, 7, 2, 9]), ("tight", 12, 15, [4, 4, 5, 6, 6, 1]),
+                          ("single", 9, 8, [5]), ("infeasible", 5, 10, [1, 2, 3, 4]),
+                          ("long", 120, 40, [int(v) for v in torch.randint(1, 40, (30,), generator=g)]),
+                          ("one_frame", 1, 6, [2, 3])]:
+        lp = torch.log_softmax(torch.randn(T, V, generator=g) * 2.0, dim=1)
+        yt = torch.tensor(y, dtype=torch.int64)
+        want = [int(v) for v in ref_align(lp, yt, 0)]
+        mine = orc.forced_align(lp, yt, 0)
+        assert want == mine, (name, want, mine)
+        blob[f"align.{name}.logp"] = lp.numpy()
+        blob[f"align.{name}.y"] = yt.numpy()
+        blob[f"align.{name}.alignment"] = np.array(want, dtype=np.int64)
+        anames.append(name)
+        print(f"align {name}: T={T} L={len(y)} -> {want[:16]}")
+    blob["align_names"] = np.array(anames)
     GOLD.mkdir(parents=True, exist_ok=True)
     np.savez_compressed(GOLD / "ctc_search.npz", **blob)
     print("written", GOLD / "ctc_search.npz", (GOLD / "ctc_search.npz").stat().st_size, "bytes")

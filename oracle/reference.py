@@ -308,3 +308,34 @@ def ctc_prefix_beam_search(ctc_probs: torch.Tensor, beam_size: int, blank: int =
         ranked = sorted(nxt.items(), key=lambda kv: log_add(list(kv[1])), reverse=True)  # stable
         cur = ranked[:beam_size]
     return [(prefix, log_add([pb, pnb])) for prefix, (pb, pnb) in cur]
+
+
+def forced_align(ctc_probs: torch.Tensor, y: torch.Tensor, blank_id: int = 0) -> List[int]:
+    """CTC forced alignment of one utterance (restates wenet/utils/ctc_util.py:27-83 with numpy
+    rows instead of per-cell tensors; fp32 max/add; Python's negative-index wrap of state 0 kept)."""
+    import numpy as np
+    lp = ctc_probs.detach().cpu().numpy().astype(np.float32)
+    T = lp.shape[0]
+    lab = [blank_id]
+    for tok in y.tolist():
+        lab += [int(tok), blank_id]
+    S = len(lab)
+    alpha = np.full((T, S), -np.inf, dtype=np.float32)
+    path = np.full((T, S), -1, dtype=np.int64)
+    alpha[0, 0] = lp[0, lab[0]]
+    alpha[0, 1] = lp[0, lab[1]]
+    for t in range(1, T):
+        for s in range(S):
+            prev = [s, s - 1]
+            if not (lab[s] == blank_id or s < 2 or lab[s] == lab[s - 2]):
+                prev.append(s - 2)
+            cand = np.array([alpha[t - 1, q] for q in prev], dtype=np.float32)  # q = -1 wraps
+            k = int(np.argmax(cand))  # first maximum
+            alpha[t, s] = cand[k] + lp[t, lab[s]]
+            path[t, s] = prev[k]
+    st = [S - 1, S - 2][int(np.argmax(np.array([alpha[-1, S - 1], alpha[-1, S - 2]])))]
+    seq = [0] * T
+    seq[-1] = st
+    for t in range(T - 2, -1, -1):
+        seq[t] = int(path[t + 1, seq[t + 1]])
+    return [lab[q] for q in seq]

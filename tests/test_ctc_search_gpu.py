@@ -73,3 +73,29 @@ def test_model_level_entry_points():
     assert [h[0] for h in hyps] == [h[0] for h in want]
     best = ctc_search.ctc_prefix_beam_search(Model(), x.to(DEV), torch.tensor([25]), 5)
     assert best[0] == want[0][0]
+
+
+def test_forced_align_golden(golden):
+    """alignments of the real forced_align (ctc_util.py:27-83), bit-identical (fp32 max/add)."""
+    from wenet_celoss_b200.ctc_search import forced_align
+    d = golden("ctc_search")
+    for name in d["align_names"]:
+        got = forced_align(torch.from_numpy(d[f"align.{name}.logp"]).to(DEV),
+                           torch.from_numpy(d[f"align.{name}.y"]), 0)
+        assert got == d[f"align.{name}.alignment"].tolist(), name
+
+
+def test_forced_align_ragged_batch():
+    from wenet_celoss_b200.ctc_search import forced_align_batch
+    g = torch.Generator().manual_seed(77)
+    B, T, V, Lmax = 6, 90, 300, 20
+    lp = torch.log_softmax(torch.randn(B, T, V, generator=g) * 2.0, dim=2)
+    hl = torch.randint(45, T + 1, (B,), generator=g)
+    yl = torch.randint(1, Lmax + 1, (B,), generator=g)
+    ys = torch.randint(1, V, (B, Lmax), generator=g)
+    ys[1, 1] = ys[1, 0]  # a repeated label
+    yl[1] = max(int(yl[1]), 2)
+    got = forced_align_batch(lp.to(DEV), ys, hl, yl, 0)
+    for b in range(B):
+        want = orc.forced_align(lp[b, :int(hl[b])], ys[b, :int(yl[b])], 0)
+        assert got[b] == want, b

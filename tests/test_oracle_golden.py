@@ -160,3 +160,11 @@ def test_ctc_prefix_beam_search_matches_reference(golden):
         for k, (prefix, score) in enumerate(hyps):
             assert list(prefix) == d[f"{name}.tokens"][k][:d[f"{name}.lens"][k]].tolist(), (name, k)
             np.testing.assert_allclose(score, d[f"{name}.scores"][k], rtol=1e-12)
+
+
+def test_forced_align_matches_reference(golden):
+    d = golden("ctc_search")
+    for name in d["align_names"]:
+        got = orc.forced_align(torch.from_numpy(d[f"align.{name}.logp"]),
+                               torch.from_numpy(d[f"align.{name}.y"]), 0)
+        assert got == d[f"align.{name}.alignment"].tolist(), name

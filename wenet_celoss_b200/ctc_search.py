@@ -83,3 +83,40 @@ def ctc_prefix_beam_search(self, speech: torch.Tensor, speech_lengths: torch.Ten
     hyps, _ = _ctc_prefix_beam_search(self, speech, speech_lengths, beam_size, decoding_chunk_size,
                                       num_decoding_left_chunks, simulate_streaming)
     return hyps[0]
+
+
+@torch.no_grad()
+def forced_align_batch(ctc_probs: torch.Tensor, ys_pad: torch.Tensor, hlens: torch.Tensor,
+                       ys_lens: torch.Tensor, blank_id: int = 0) -> List[List[int]]:
+    """CTC forced alignment of a batch: ``ctc_probs [B,T,V]`` log-probs, ``ys_pad [B,Lmax]``
+    labels (padding ignored), ``hlens`` / ``ys_lens [B]``.  Returns per utterance the aligned token
+    of every frame (ctc_util.py:27-83 per utterance)."""
+    _lib.require_cuda(ctc_probs, "ctc_probs")
+    dev = ctc_probs.device
+    B, T, V = ctc_probs.shape
+    Lmax = ys_pad.size(1)
+    with torch.cuda.device(dev):
+        lp = ctc_probs.float().contiguous()
+        ys = ys_pad.to(device=dev, dtype=torch.int64).contiguous()
+        hl = hlens.reshape(-1).to(device=dev, dtype=torch.int32).clamp(max=T).contiguous()
+        yl = ys_lens.reshape(-1).to(device=dev, dtype=torch.int32).contiguous()
+        if int(yl.min()) < 1:
+            raise RuntimeError("forced_align needs at least one label per utterance")
+        out = torch.empty(B, T, dtype=torch.int32, device=dev)
+        L_ = _lib.lib()
+        L_.b200_ctc_forced_align_workspace_bytes.restype = ctypes.c_size_t
+        ws_bytes = L_.b200_ctc_forced_align_workspace_bytes(B, T, Lmax)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        _lib.call("b200_ctc_forced_align", ptr(lp), ptr(ys), ptr(hl), ptr(yl), i32(B), i32(T), i32(V),
+                  i32(Lmax), i32(blank_id), ptr(out), ptr(ws), ctypes.c_size_t(ws_bytes),
+                  _lib.stream_handle(dev))
+        rows = out.cpu().tolist()
+        n = hl.cpu().tolist()
+    return [rows[b][:n[b]] for b in range(B)]
+
+
+def forced_align(ctc_probs: torch.Tensor, y: torch.Tensor, blank_id: int = 0) -> list:
+    """Drop-in for ``forced_align(ctc_probs [T,D], y [L], blank_id)`` (ctc_util.py:27-83)."""
+    T = ctc_probs.size(0)
+    return forced_align_batch(ctc_probs.unsqueeze(0), y.reshape(1, -1), torch.tensor([T]),
+                              torch.tensor([y.numel()]), blank_id)[0]
