@@ -543,6 +543,32 @@ def extra_rows(cfg, dev, pk):
                   "workload": "cfg5: CTC.forward+backward B=64 T=1000 V=5000 L<=100 fp32; 'ms' includes "
                               "the fp32 ctc_lo library GEMMs, 'loss_only' is ctc_loss(logits) fwd+bwd "
                               "(3*B*T*V*4 algorithmic bytes)"}
+    # SURVEY 8(f) rows 2 and 4 on the cfg5 shape: CTC prefix beam search (beam 10) and forced alignment
+    from wenet_celoss_b200.ctc_search import ctc_prefix_beam_search_batch, forced_align_batch
+    with torch.no_grad():
+        lp5 = torch.log_softmax(logits.detach(), dim=2)
+    ms_b, hyps5 = timed(lambda: ctc_prefix_beam_search_batch(lp5, hl, 10), reps=2)
+    out["ctc_prefix_beam10"] = {
+        "value": B5 / (ms_b * 1e-3), "unit": "utt/s", "ms": ms_b, "frames_per_s": B5 * T5 / (ms_b * 1e-3),
+        "workload": "cfg5 shape: B=64 T=1000 V=5000 CTC prefix beam search, beam=10, log-probs resident; "
+                    "one CTA per utterance, T dependent frames (bound: per-frame latency chain)"}
+    ys_a = ys.clamp(min=1)
+    ms_a, _ = timed(lambda: forced_align_batch(lp5, ys_a, hl, yl), reps=3)
+    out["ctc_forced_align"] = {
+        "value": B5 / (ms_a * 1e-3), "unit": "utt/s", "ms": ms_a,
+        "workload": "cfg5 shape: B=64 T=1000 V=5000 L in [50,100] Viterbi alignment, log-probs resident"}
+    try:  # reference algorithm on the host for one short utterance (oracle = checker, bounded sample)
+        import time as _t
+        from oracle import reference as orc
+        lp_h = lp5[0, :100].cpu()
+        t0 = _t.perf_counter(); orc.ctc_prefix_beam_search(lp_h, 10); dt = _t.perf_counter() - t0
+        out["ctc_prefix_beam10"]["cpu_port_utts_per_sec"] = 1.0 / (dt * T5 / 100)
+        out["ctc_prefix_beam10"]["cpu_port_sample"] = "1 utterance x 100 of 1000 frames, python port, 1 core, scaled"
+        t0 = _t.perf_counter(); orc.forced_align(lp_h, ys_a[0, :10].cpu(), 0); dt = _t.perf_counter() - t0
+        out["ctc_forced_align"]["cpu_port_utts_per_sec"] = 1.0 / (dt * (T5 / 100) * (75 / 10))
+        out["ctc_forced_align"]["cpu_port_sample"] = "1 utterance x 100 frames x 10 labels, python port, 1 core, scaled by T and L"
+    except Exception as exc:  # noqa: BLE001
+        out["ctc_prefix_beam10"]["cpu_port_error"] = repr(exc)
     return out
 
 

@@ -28,8 +28,10 @@ namespace b200 {
 namespace cb {
 
 constexpr int kMaxBeam = 16;
-constexpr int kThreads = 256;
+constexpr int kThreads = 256;      // top-k kernel
+constexpr int kBeamThreads = 288;  // >= kMaxBeam * (kMaxBeam + 1) = 272 entries
 constexpr int kMaxEnt = kMaxBeam * (kMaxBeam + 1);
+static_assert(kMaxEnt <= 288, "one thread per entry");
 
 __device__ __forceinline__ bool better(float v, int i, float w, int k) {
   return v > w || (v == w && i < k);
@@ -58,15 +60,65 @@ struct Params {
   int B, T, V, beam, blank;
   int32_t* parent;      // [B][T*beam+1] trie: node 0 = empty prefix
   int32_t* tok;         // [B][T*beam+1]
+  float* topv;          // [B][T][beam] per-frame top-k log-probs (sorted)
+  int32_t* topi;        // [B][T][beam]
   int32_t* out_node;    // [B][beam] final node of each hypothesis, best first
   double* out_score;    // [B][beam] log_add(pb, pnb)
   int32_t* out_n;       // [B]
 };
 
-__global__ void __launch_bounds__(kThreads) ctc_prefix_beam_kernel(const Params P) {
+// ---- kernel 1: top-k of every frame, all B*T rows in parallel (one CTA per row).  The frames are
+// independent; only the prefix bookkeeping below is a T-step chain.
+__global__ void __launch_bounds__(kThreads) ctc_topk_kernel(const Params P) {
   extern __shared__ float sx[];  // [V]
   __shared__ float s_red[2][kThreads / 32];
   __shared__ int s_idx[2][kThreads / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int NW = kThreads / 32;
+  const int row = blockIdx.x;
+  const int b = row / P.T, t = row - b * P.T;
+  if (t >= P.lens[b]) return;
+  const int V = P.V, K = P.beam;
+  // sorted descending, lower index wins ties
+  const float* x = P.logp + (size_t)row * V;
+  float bv = -INFINITY;
+  int bi = 0x7fffffff;
+#pragma unroll 4
+  for (int v = tid; v < V; v += kThreads) {
+    const float xv = x[v];
+    sx[v] = xv;
+    argmax_pair(bv, bi, xv, v);
+  }
+  for (int k = 0; k < K; ++k) {
+    float wv = bv;
+    int wi = bi;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+      argmax_pair(wv, wi, __shfl_xor_sync(0xffffffffu, wv, o), __shfl_xor_sync(0xffffffffu, wi, o));
+    if (lane == 0) {
+      s_red[k & 1][warp] = wv;
+      s_idx[k & 1][warp] = wi;
+    }
+    __syncthreads();
+    wv = s_red[k & 1][0];
+    wi = s_idx[k & 1][0];
+#pragma unroll
+    for (int w = 1; w < NW; ++w) argmax_pair(wv, wi, s_red[k & 1][w], s_idx[k & 1][w]);
+    if (tid == 0) {
+      P.topv[(size_t)row * K + k] = wv;
+      P.topi[(size_t)row * K + k] = wi;
+    }
+    if (wi == bi && wi != 0x7fffffff) {
+      sx[wi] = __int_as_float(0x7fc00000);  // NaN never compares "better"
+      bv = -INFINITY;
+      bi = 0x7fffffff;
+      for (int v = tid; v < V; v += kThreads) argmax_pair(bv, bi, sx[v], v);
+    }
+  }
+}
+
+// ---- kernel 2: one CTA per utterance walks the frames
+__global__ void __launch_bounds__(kBeamThreads) ctc_prefix_beam_kernel(const Params P) {
   __shared__ float s_topv[kMaxBeam];
   __shared__ int s_topi[kMaxBeam];
   // current beam
@@ -77,17 +129,17 @@ __global__ void __launch_bounds__(kThreads) ctc_prefix_beam_kernel(const Params 
   __shared__ double e_pb[kMaxEnt], e_pnb[kMaxEnt], e_key[kMaxEnt];
   __shared__ int e_order[kMaxEnt];  // insertion order in the reference's dict, -1 = absent
   __shared__ int sel[kMaxBeam];
-  __shared__ int s_nsel;
 
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  constexpr int NW = kThreads / 32;
+  const int tid = threadIdx.x;
   const int b = blockIdx.x;
-  const int V = P.V, K = P.beam;
+  const int K = P.beam;
   const int Tb = min(P.lens[b], P.T);
   const size_t pool = (size_t)P.T * K + 1;
   int32_t* parent = P.parent + (size_t)b * pool;
   int32_t* tokens = P.tok + (size_t)b * pool;
-  int n_nodes = 1;  // tracked by thread 0 only
+  const float* topv = P.topv + (size_t)b * P.T * K;
+  const int32_t* topi = P.topi + (size_t)b * P.T * K;
+  int n_nodes = 1;  // tracked by warp 0 (uniform across its lanes)
   if (tid == 0) {
     parent[0] = -1;
     tokens[0] = -1;
@@ -98,50 +150,25 @@ __global__ void __launch_bounds__(kThreads) ctc_prefix_beam_kernel(const Params 
     c_pnb[0] = -INFINITY;
     s_n = 1;
   }
+  if (tid < K && Tb > 0) {
+    s_topv[tid] = topv[tid];
+    s_topi[tid] = topi[tid];
+  }
   __syncthreads();
 
   for (int t = 0; t < Tb; ++t) {
-    // ---- 1. top-k of this frame's log-probs (sorted descending, lower index wins ties)
-    const float* x = P.logp + ((size_t)b * P.T + t) * V;
-    float bv = -INFINITY;
-    int bi = 0x7fffffff;
-#pragma unroll 4
-    for (int v = tid; v < V; v += kThreads) {
-      const float xv = x[v];
-      sx[v] = xv;
-      argmax_pair(bv, bi, xv, v);
+    // next frame's top-k: in flight while this frame is processed
+    float nv = 0.f;
+    int ni = 0;
+    if (tid < K && t + 1 < Tb) {
+      nv = topv[(size_t)(t + 1) * K + tid];
+      ni = topi[(size_t)(t + 1) * K + tid];
     }
-    for (int k = 0; k < K; ++k) {
-      float wv = bv;
-      int wi = bi;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1)
-        argmax_pair(wv, wi, __shfl_xor_sync(0xffffffffu, wv, o), __shfl_xor_sync(0xffffffffu, wi, o));
-      if (lane == 0) {
-        s_red[k & 1][warp] = wv;
-        s_idx[k & 1][warp] = wi;
-      }
-      __syncthreads();
-      wv = s_red[k & 1][0];
-      wi = s_idx[k & 1][0];
-#pragma unroll
-      for (int w = 1; w < NW; ++w) argmax_pair(wv, wi, s_red[k & 1][w], s_idx[k & 1][w]);
-      if (tid == 0) {
-        s_topv[k] = wv;
-        s_topi[k] = wi;
-      }
-      if (wi == bi && wi != 0x7fffffff) {
-        sx[wi] = __int_as_float(0x7fc00000);  // NaN never compares "better"
-        bv = -INFINITY;
-        bi = 0x7fffffff;
-        for (int v = tid; v < V; v += kThreads) argmax_pair(bv, bi, sx[v], v);
-      }
-    }
-    __syncthreads();
     const int N = s_n;
     const int nent = N * (K + 1);
     // ---- 2. entries of `next`
-    for (int e = tid; e < nent; e += kThreads) {
+    if (tid < nent) {
+      const int e = tid;
       const int j = e / (K + 1), slot = e - j * (K + 1);
       double pb = -INFINITY, pnb = -INFINITY;
       int order = -1;
@@ -202,64 +229,59 @@ __global__ void __launch_bounds__(kThreads) ctc_prefix_beam_kernel(const Params 
       e_order[e] = order;
       e_key[e] = log_add2(pb, pnb);
     }
-    __syncthreads();
+    const int cnt = __syncthreads_count(tid < nent && e_order[tid] >= 0);
     // ---- 3. stable sort by key (descending), ties by insertion order; keep K
-    if (warp == 0) {
-      int cnt = 0;
-      for (int e = lane; e < nent; e += 32) {
-        if (e_order[e] < 0) continue;
-        ++cnt;
-        const double v = e_key[e];
-        const int o = e_order[e];
-        int rank = 0;
-        for (int d = 0; d < nent; ++d)
-          if (e_order[d] >= 0 && (e_key[d] > v || (e_key[d] == v && e_order[d] < o))) ++rank;
-        if (rank < K) sel[rank] = e;
-      }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-      if (lane == 0) s_nsel = cnt < K ? cnt : K;
+    if (tid < nent && e_order[tid] >= 0) {
+      const double v = e_key[tid];
+      const int o = e_order[tid];
+      int rank = 0;
+      for (int d = 0; d < nent; ++d)
+        if (e_order[d] >= 0 && (e_key[d] > v || (e_key[d] == v && e_order[d] < o))) ++rank;
+      if (rank < K) sel[rank] = tid;
     }
     __syncthreads();
-    // ---- 4. new beam (thread r builds hypothesis r; thread 0 hands out trie nodes)
-    const int Nn = s_nsel;
-    int my_node = -1, my_last = -1, my_par = -1;
-    double my_pb = 0.0, my_pnb = 0.0;
-    if (tid < Nn) {
-      const int e = sel[tid];
-      const int j = e / (K + 1), slot = e - j * (K + 1);
-      my_pb = e_pb[e];
-      my_pnb = e_pnb[e];
-      if (slot == 0) {
-        my_node = c_node[j];
-        my_last = c_last[j];
-        my_par = c_par[j];
-      } else {
-        my_last = s_topi[slot - 1];
-        my_par = c_node[j];
+    // ---- 4. new beam: lane r of warp 0 builds hypothesis r, new trie nodes by ballot
+    if (tid < 32) {
+      const int Nn = cnt < K ? cnt : K;
+      int my_node = -1, my_last = -1, my_par = -1;
+      double my_pb = 0.0, my_pnb = 0.0;
+      bool ext = false;
+      if (tid < Nn) {
+        const int e = sel[tid];
+        const int j = e / (K + 1), slot = e - j * (K + 1);
+        my_pb = e_pb[e];
+        my_pnb = e_pnb[e];
+        if (slot == 0) {
+          my_node = c_node[j];
+          my_last = c_last[j];
+          my_par = c_par[j];
+        } else {
+          ext = true;
+          my_last = s_topi[slot - 1];
+          my_par = c_node[j];
+        }
       }
-    }
-    __syncthreads();
-    if (tid == 0) {
-      for (int r = 0; r < Nn; ++r) {
-        const int e = sel[r];
-        if (e % (K + 1) != 0) sel[r] = -(n_nodes++) - 1;  // new node id, encoded negative
-      }
-    }
-    __syncthreads();
-    if (tid < Nn) {
-      if (my_node < 0) {
-        my_node = -sel[tid] - 1;
+      const unsigned m = __ballot_sync(0xffffffffu, ext);
+      if (ext) {
+        my_node = n_nodes + __popc(m & ((1u << tid) - 1u));
         parent[my_node] = my_par;
         tokens[my_node] = my_last;
       }
-      c_node[tid] = my_node;
-      c_last[tid] = my_last;
-      c_par[tid] = my_par;
-      c_pb[tid] = my_pb;
-      c_pnb[tid] = my_pnb;
+      n_nodes += __popc(m);
+      __syncwarp();  // every lane has read the old beam
+      if (tid < Nn) {
+        c_node[tid] = my_node;
+        c_last[tid] = my_last;
+        c_par[tid] = my_par;
+        c_pb[tid] = my_pb;
+        c_pnb[tid] = my_pnb;
+      }
+      if (tid == 0) s_n = Nn;
+      if (tid < K) {
+        s_topv[tid] = nv;
+        s_topi[tid] = ni;
+      }
     }
-    if (tid == 0) s_n = Nn;
     __syncthreads();
   }
   const int N = s_n;
@@ -303,7 +325,8 @@ using namespace b200;
 
 extern "C" size_t b200_ctc_prefix_beam_workspace_bytes(int B, int T, int beam) {
   const size_t pool = (size_t)T * beam + 1;
-  return 2 * (size_t)B * pool * sizeof(int32_t) + (size_t)B * beam * sizeof(int32_t);
+  return 2 * (size_t)B * pool * sizeof(int32_t) + (size_t)B * beam * sizeof(int32_t) +
+         2 * (size_t)B * T * beam * sizeof(int32_t);
 }
 
 extern "C" int b200_ctc_prefix_beam(const float* logp, const int32_t* lens, int B, int T, int V,
@@ -335,14 +358,18 @@ extern "C" int b200_ctc_prefix_beam(const float* logp, const int32_t* lens, int 
   P.parent = reinterpret_cast<int32_t*>(workspace);
   P.tok = P.parent + (size_t)B * pool;
   P.out_node = P.tok + (size_t)B * pool;
+  P.topi = P.out_node + (size_t)B * beam;
+  P.topv = reinterpret_cast<float*>(P.topi + (size_t)B * T * beam);
   P.out_score = out_score;
   P.out_n = out_n;
   cudaStream_t st = (cudaStream_t)stream;
   const size_t smem = (size_t)V * sizeof(float);
   if (smem > 48 * 1024)
-    B200_CHECK_CUDA(cudaFuncSetAttribute(cb::ctc_prefix_beam_kernel,
+    B200_CHECK_CUDA(cudaFuncSetAttribute(cb::ctc_topk_kernel,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  cb::ctc_prefix_beam_kernel<<<B, cb::kThreads, smem, st>>>(P);
+  cb::ctc_topk_kernel<<<B * T, cb::kThreads, smem, st>>>(P);
+  B200_CHECK_LAUNCH("ctc_topk_kernel");
+  cb::ctc_prefix_beam_kernel<<<B, cb::kBeamThreads, 0, st>>>(P);
   B200_CHECK_LAUNCH("ctc_prefix_beam_kernel");
   const int n = B * beam;
   cb::ctc_beam_backtrack_kernel<<<(n + 127) / 128, 128, 0, st>>>(P, out_tokens, out_len);
