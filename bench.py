@@ -410,12 +410,21 @@ class RnntFusedWorkload:
                       ptr(box["coef"]), i32(B), i32(T), i32(U1), i32(V), i32(J), i32(0), _i64(0),
                       _i64(per_utt), ptr(G), i32(ldg), ptr(H), i32(ldh), ptr(None), i32(0), st)
 
+        from wenet_celoss_b200.joint import joint_dw
+        G8 = torch.zeros(8 * per_utt, ldg, dtype=torch.bfloat16, device=self.dev)
+        H8 = torch.zeros(8 * per_utt, J, dtype=torch.bfloat16, device=self.dev)
+        dW8 = torch.zeros(V, J, device=self.dev)
+
+        def k_dw():
+            joint_dw(G8, H8, 8 * per_utt, V, J, dW8)
+
         out = {}
         k_fwd(); k_lat()
         alpha, beta, costs, doff = box["ab"]
         box["coef"] = rnnt_grad_coef(box["lat"][0], alpha, beta, doff, dy, self.targets, self.tl, self.ul, 0)
         for name, fn in (("joint_kernel<FWD> (all cells)", k_fwd), ("rnnt_lattice_kernel", k_lat),
-                         ("joint_kernel<GRAD> (1 utterance chunk)", k_grad)):
+                         ("joint_kernel<GRAD> (1 utterance chunk)", k_grad),
+                         ("joint_dw_kernel (8 utterance chunk)", k_dw)):
             ts = []
             for _ in range(iters + 1):
                 e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
@@ -435,12 +444,21 @@ class RnntFusedWorkload:
         achieved = flops_fwd / (t_fwd * 1e-3) / 1e12
         flops_chunk = 2.0 * cfg["T"] * (cfg["U"] + 1) * cfg["J"] * cfg["V"]
         ach_g = flops_chunk / (kb["joint_kernel<GRAD> (1 utterance chunk)"] * 1e-3) / 1e12
+        ach_dw = 8 * flops_chunk / (kb["joint_dw_kernel (8 utterance chunk)"] * 1e-3) / 1e12
         counted = 6.0 * self.cells * cfg["J"] * cfg["V"]
+        traffic = None
+        try:  # per-launch DRAM bytes of this kernel from the committed ncu --set full capture
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles",
+                                   "r01_traffic.json")) as fh:
+                traffic = json.load(fh)["joint_kernel<FWD>"]["bytes"]
+        except (OSError, KeyError, ValueError):
+            pass
         return {"bound": "tensor", "kernel": "joint_kernel<FWD>", "achieved": achieved,
-                "peak": pk["bf16"], "unit": "TFLOP/s", "frac": achieved / pk["bf16"], "traffic": None,
+                "peak": pk["bf16"], "unit": "TFLOP/s", "frac": achieved / pk["bf16"], "traffic": traffic,
                 "peak_source": pk["source"] + " (burst: kernel timed alone)",
                 "algorithmic_flops_per_launch": flops_fwd, "kernel_ms": kb,
-                "other": {"joint_kernel<GRAD>": {"achieved": ach_g, "frac": ach_g / pk["bf16"]}},
+                "other": {"joint_kernel<GRAD>": {"achieved": ach_g, "frac": ach_g / pk["bf16"]},
+                          "joint_dw_kernel": {"achieved": ach_dw, "frac": ach_dw / pk["bf16"]}},
                 "step_frac_of_tensor_roofline":
                     counted / (ms_step * 1e-3) / 1e12 / pk["bf16_sustained"],
                 "step_counted_flops": counted}
