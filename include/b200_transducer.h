@@ -200,6 +200,26 @@ int b200_rnnt_greedy(const float* enc_proj, const int32_t* lens, int B, int T,
                      int32_t* tokens, int32_t* n_tok, int max_tokens,
                      void* workspace, size_t ws_bytes, int* rounds_out, b200_stream_t stream);
 
+/* greedy search with the fork's hot-word predictor bias applied at every predictor step
+ * (wenet/transducer/search/greedy_search.py:92-144 with context_filter_state='off':
+ * ContextBias.forward_predictor_bias, wenet/transformer/context_bias.py:375-381, over the EMPTY
+ * context).  All pointers are device pointers to fp32 row-major weights of the reference modules:
+ * predictor.projection [P,H]; predictor_bias.linear_q [P,P]; k / v = linear_k / linear_v applied
+ * to the Nc context vectors [Nc,P]; linear_out [P,P]; predictor_bias_bias_norm; predictor_bias_combine
+ * [P,2P]; predictor_bias_out_norm; joint.pred_ffn [J,P]. */
+typedef struct {
+  const float *proj_w, *proj_b, *wq, *bq, *k, *v, *wo, *bo, *ln1_g, *ln1_b, *wc, *bc, *ln2_g, *ln2_b,
+      *wf, *bf;
+  int P, Nc, heads;
+  float ln_eps;
+} b200_pred_bias_t;
+int b200_rnnt_greedy_bias(const float* enc_proj, const int32_t* lens, int B, int T,
+                          const float* embed, const float* const* lstm, const float* w_out,
+                          const float* b_out, int V, int Emb, int H, int L, int J, int blank,
+                          int n_steps, const b200_pred_bias_t* bias, int32_t* tokens,
+                          int32_t* n_tok, int max_tokens, void* workspace, size_t ws_bytes,
+                          int* rounds_out, b200_stream_t stream);
+
 /* ---- Batched RNN-T prefix beam search ---------------------------------------
  * replaces PrefixBeamSearch.prefix_beam_search (wenet/transducer/search/
  * prefix_beam_search.py:42-148) for a batch: per frame predictor step + joint + log_softmax

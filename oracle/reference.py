@@ -339,3 +339,63 @@ def forced_align(ctc_probs: torch.Tensor, y: torch.Tensor, blank_id: int = 0) ->
     for t in range(T - 2, -1, -1):
         seq[t] = int(path[t + 1, seq[t + 1]])
     return [lab[q] for q in seq]
+
+
+def predictor_bias(cb, ctx: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """ContextBias.forward_predictor_bias (wenet/transformer/context_bias.py:375-381) restated
+    with functional ops: ``x [1,1,P]`` predictor output, ``ctx [1,Nc,P]`` phrase vectors; ``cb``
+    only supplies the parameters (predictor_bias.{linear_q,linear_k,linear_v,linear_out},
+    predictor_bias_bias_norm, predictor_bias_combine, predictor_bias_out_norm)."""
+    import torch.nn.functional as F
+    mha = cb.predictor_bias
+    nh = int(mha.h)
+    P = x.size(-1)
+    dk = P // nh
+    q = F.linear(x, mha.linear_q.weight, mha.linear_q.bias).view(1, -1, nh, dk).transpose(1, 2)
+    k = F.linear(ctx, mha.linear_k.weight, mha.linear_k.bias).view(1, -1, nh, dk).transpose(1, 2)
+    v = F.linear(ctx, mha.linear_v.weight, mha.linear_v.bias).view(1, -1, nh, dk).transpose(1, 2)
+    att = torch.softmax(q @ k.transpose(-2, -1) / math.sqrt(dk), dim=-1)   # attention.py:48-120
+    a = (att @ v).transpose(1, 2).reshape(1, -1, P)
+    a = F.linear(a, mha.linear_out.weight, mha.linear_out.bias)
+    n1, n2 = cb.predictor_bias_bias_norm, cb.predictor_bias_out_norm
+    a = F.layer_norm(a, (P,), n1.weight, n1.bias, n1.eps)
+    y = F.linear(torch.cat([x, a], dim=-1), cb.predictor_bias_combine.weight, cb.predictor_bias_combine.bias)
+    return F.layer_norm(y, (P,), n2.weight, n2.bias, n2.eps)
+
+
+@torch.no_grad()
+def greedy_search_hotword(model, enc_biased: torch.Tensor, enc_len: int, bias_hidden_empty: torch.Tensor,
+                          n_steps: int = 64) -> List[int]:
+    """The fork's greedy search with ``context_filter_state='off'``
+    (wenet/transducer/search/greedy_search.py:62-165): ``enc_biased`` is the encoder stream after
+    forward_encoder_bias with the given phrase list (:69), every predictor output passes through
+    forward_predictor_bias with the EMPTY phrase list (:140-144) before the joint."""
+    dev = enc_biased.device
+    blank = model.blank
+    pad = torch.zeros(1, 1, device=dev)
+    token = torch.tensor([[blank]], device=dev)
+    state = model.predictor.init_state(1, device=dev)
+    pending_state = state
+    pred_step = None
+    need_predictor = True
+    emitted_here = 0
+    t = 0
+    hyp: List[int] = []
+    while t < int(enc_len):
+        if need_predictor:
+            raw, pending_state = model.predictor.forward_step(token, pad, state)
+            pred_step = predictor_bias(model.context_bias, bias_hidden_empty, raw)
+        logp = joint_logits(enc_biased[:, t:t + 1, :], pred_step, model.joint).log_softmax(dim=-1)
+        k = int(logp.reshape(-1).argmax())
+        if k != blank:
+            hyp.append(k)
+            need_predictor = True
+            emitted_here += 1
+            token = torch.tensor([[k]], device=dev)
+            state = pending_state
+        if k == blank or emitted_here >= n_steps:
+            if k == blank:
+                need_predictor = False
+            t += 1
+            emitted_here = 0
+    return hyp

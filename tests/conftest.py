@@ -48,3 +48,52 @@ def load_oracle_model(d, prefix="w."):
     assert not missing.unexpected_keys, missing
     m.eval()
     return m
+
+
+class _Mha(torch.nn.Module):
+    """parameter container with the reference MultiHeadedAttention's names (attention.py:35-46)."""
+
+    def __init__(self, n_head, n_feat):
+        super().__init__()
+        self.h, self.d_k = n_head, n_feat // n_head
+        self.linear_q = torch.nn.Linear(n_feat, n_feat)
+        self.linear_k = torch.nn.Linear(n_feat, n_feat)
+        self.linear_v = torch.nn.Linear(n_feat, n_feat)
+        self.linear_out = torch.nn.Linear(n_feat, n_feat)
+
+
+class HotwordBiasStandIn(torch.nn.Module):
+    """The slice of ContextBias (context_bias.py:159-399) the greedy path reads, filled from a
+    golden fixture: predictor-bias parameters under the reference's attribute names;
+    forward_bias_hidden returns the stored phrase vectors (given / empty list) and
+    forward_encoder_bias the stored biased encoder stream (the phrase extractor and the encoder-side
+    attention are library modules outside the hot path)."""
+
+    def __init__(self, d):
+        super().__init__()
+        P = int(d["dims"][1])
+        self.predictor_bias = _Mha(int(d["heads"]), P)
+        self.predictor_bias_bias_norm = torch.nn.LayerNorm(P)
+        self.predictor_bias_combine = torch.nn.Linear(2 * P, P)
+        self.predictor_bias_out_norm = torch.nn.LayerNorm(P)
+        sd = {k[3:]: torch.from_numpy(d[k]) for k in d.files
+              if k.startswith("cb.predictor_bias")}
+        self.load_state_dict(sd, strict=True)
+        self.register_buffer("bias_hidden", torch.from_numpy(d["bias_hidden"]))
+        self.register_buffer("bias_hidden_empty", torch.from_numpy(d["bias_hidden_empty"]))
+        self.register_buffer("enc", torch.from_numpy(d["enc"]))
+        self.register_buffer("enc_biased", torch.from_numpy(d["enc_biased"]))
+
+    def forward_bias_hidden(self, context_list, context_lengths):
+        return self.bias_hidden_empty if context_list.numel() == 1 else self.bias_hidden
+
+    def forward_encoder_bias(self, bias_hidden, encoder_out):
+        assert bias_hidden is self.bias_hidden and torch.equal(encoder_out, self.enc)
+        return self.enc_biased, None
+
+
+def load_hotword_model(d):
+    m = load_oracle_model(d)
+    m.context_bias = HotwordBiasStandIn(d)
+    m.eval()
+    return m

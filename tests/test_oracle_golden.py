@@ -168,3 +168,17 @@ def test_forced_align_matches_reference(golden):
         got = orc.forced_align(torch.from_numpy(d[f"align.{name}.logp"]),
                                torch.from_numpy(d[f"align.{name}.y"]), 0)
         assert got == d[f"align.{name}.alignment"].tolist(), name
+
+
+def test_hotword_greedy_matches_reference(golden):
+    """fork greedy search with a real ContextBias, context_filter_state='off'
+    (greedy_search.py:34-176): the oracle's restatement of forward_predictor_bias inside the loop."""
+    from conftest import load_hotword_model
+    d = golden("hotword_greedy")
+    m = load_hotword_model(d)
+    cb = m.context_bias
+    for b in range(d["enc"].shape[0]):
+        n = int(d["lens"][b])
+        got = orc.greedy_search_hotword(m, cb.enc_biased[b:b + 1, :n], n, cb.bias_hidden_empty,
+                                        n_steps=int(d["n_steps"]))
+        assert got == [int(x) for x in d["hyps"][b] if x >= 0], b

@@ -104,3 +104,23 @@ def test_beam_full_dims_vs_oracle():
     beam, enc_out = bs.prefix_beam_search(enc[0:1].to(DEV), torch.tensor([T]), beam_size=10)
     want = orc.prefix_beam_search(m, enc[0:1], beam_size=10)
     assert beam[0].hyp == want[0].hyp and enc_out.shape == (1, T, 256)
+
+
+def test_hotword_greedy_golden(golden):
+    """greedy search with the fork's hot-word streams (real ContextBias, filter 'off'): token lists
+    of the reference's basic_greedy_search (greedy_search.py:34-176), whole batch in one call."""
+    from conftest import load_hotword_model
+    from wenet_celoss_b200 import greedy_search_batch
+    d = golden("hotword_greedy")
+    m = load_hotword_model(d).to(DEV)
+    enc = torch.from_numpy(d["enc"]).to(DEV)
+    lens = torch.from_numpy(d["lens"]).to(DEV)
+    ctx = torch.from_numpy(d["context_list"]).to(DEV)
+    ctx_len = torch.from_numpy(d["context_lengths"]).to(DEV)
+    hyps = greedy_search_batch(m, enc, lens, n_steps=int(d["n_steps"]), context_list=ctx,
+                               context_lengths=ctx_len)
+    for b in range(enc.size(0)):
+        assert hyps[b] == _unpad(d["hyps"][b]), b
+    # without the predictor bias the same model decodes differently: the device path is exercised
+    plain = greedy_search_batch(m, m.context_bias.enc_biased, lens, n_steps=int(d["n_steps"]), hotword=False)
+    assert plain != hyps

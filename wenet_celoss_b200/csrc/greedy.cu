@@ -35,6 +35,7 @@ struct Model {
   const float* w_out;                 // [V, J]
   const float* b_out;                 // [V]
   int V, Emb, H, L, J, blank;
+  int has_bias;                       // pp comes from pred_bias_kernel (hot-word predictor bias)
 };
 
 struct State {
@@ -154,7 +155,7 @@ __global__ void __launch_bounds__(256) pred_z_kernel(Model M, State S, int round
   for (int q = g0; q < min(n_act, g0 + 8); ++q) {
     const int b = list[q];
     float pp;
-    if (S.need[b]) {
+    if (S.need[b] && !M.has_bias) {
       const int p = S.par[b] ^ 1;  // state written by the LSTM kernels of this round
       const float* h = S.h + ((size_t)p * M.L + M.L - 1) * lay + (size_t)b * H;
       float a = 0.f;
@@ -308,6 +309,7 @@ __global__ void __launch_bounds__(1024) update_kernel(Model M, State S, int roun
 }
 
 #include "greedy_persistent.inc"
+#include "greedy_bias.inc"
 
 }  // namespace gs
 }  // namespace b200

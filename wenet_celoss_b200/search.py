@@ -9,8 +9,10 @@ encoder_out_lens [B])`` returns B token lists.  ``model`` is anything exposing w
 reference functions read: ``model.predictor`` (``embed``, ``rnn`` = nn.LSTM, ``projection``),
 ``model.joint`` (``enc_ffn``, ``pred_ffn``, ``ffn_out``) and ``model.blank``.
 
-The hot-word gate / "go-back" of the fork (greedy_search.py:100-144) is out of scope
-(SURVEY.md §8f rank 1); ``context_filter_state='on'`` raises.
+With a real ``ContextBias`` on the model the fork's hot-word streams are applied as
+``context_filter_state='off'`` does (greedy_search.py:62-70,140-144: encoder stream biased once,
+every predictor output biased with the empty context inside the device loop).  The gate /
+"go-back" of ``context_filter_state='on'`` (greedy_search.py:100-131) is not implemented and raises.
 """
 from __future__ import annotations
 
@@ -60,16 +62,83 @@ def _enc_proj(model, encoder_out: torch.Tensor) -> torch.Tensor:
         torch.backends.cuda.matmul.allow_tf32 = prev
 
 
+class _PredBias(ctypes.Structure):
+    """b200_pred_bias_t (include/b200_transducer.h)."""
+    _fields_ = ([(n, ctypes.c_void_p) for n in
+                 ("proj_w", "proj_b", "wq", "bq", "k", "v", "wo", "bo", "ln1_g", "ln1_b", "wc", "bc",
+                  "ln2_g", "ln2_b", "wf", "bf")] +
+                [("P", ctypes.c_int), ("Nc", ctypes.c_int), ("heads", ctypes.c_int),
+                 ("ln_eps", ctypes.c_float)])
+
+
+def _has_hotword_bias(model) -> bool:
+    cb = getattr(model, "context_bias", None)
+    return cb is not None and hasattr(cb, "predictor_bias") and hasattr(cb, "predictor_bias_combine")
+
+
+def _hotword_setup(model, encoder_out, context_list, context_lengths):
+    """What greedy_search.py:62-70 does before its loop: phrase vectors of the given and of the
+    EMPTY context list, encoder stream biased with the given one; plus K / V of the empty context for
+    the per-step predictor bias (fixed for the whole call)."""
+    cb = model.context_bias
+    dev = encoder_out.device
+    if context_list is None:
+        context_list = torch.IntTensor([0])       # the reference's defaults (greedy_search.py:38-39)
+    if context_lengths is None:
+        context_lengths = torch.IntTensor([0])
+    context_list, context_lengths = context_list.to(dev), context_lengths.to(dev)
+    bias_hidden = cb.forward_bias_hidden(context_list, context_lengths)
+    empty = torch.zeros((1, 1), dtype=torch.int, device=dev)
+    bias_hidden_empty = cb.forward_bias_hidden(empty, context_lengths[0].unsqueeze(0))
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        encoder_out, _ = cb.forward_encoder_bias(bias_hidden, encoder_out)
+        mha = cb.predictor_bias
+        ctx = bias_hidden_empty[0].float()
+        f32 = lambda t: t.detach().to(torch.float32).contiguous()
+        keep = dict(k=f32(mha.linear_k(ctx)), v=f32(mha.linear_v(ctx)))
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    pred, joint = model.predictor, model.joint
+    named = dict(proj_w=pred.projection.weight, proj_b=pred.projection.bias,
+                 wq=mha.linear_q.weight, bq=mha.linear_q.bias, wo=mha.linear_out.weight,
+                 bo=mha.linear_out.bias, ln1_g=cb.predictor_bias_bias_norm.weight,
+                 ln1_b=cb.predictor_bias_bias_norm.bias, wc=cb.predictor_bias_combine.weight,
+                 bc=cb.predictor_bias_combine.bias, ln2_g=cb.predictor_bias_out_norm.weight,
+                 ln2_b=cb.predictor_bias_out_norm.bias, wf=joint.pred_ffn.weight, bf=joint.pred_ffn.bias)
+    keep.update({n: f32(t) for n, t in named.items()})
+    P = pred.projection.out_features
+    if keep["wc"].shape != (P, 2 * P) or keep["wq"].shape != (P, P):
+        raise NotImplementedError("predictor bias expects embedding_size == predictor output size")
+    desc = _PredBias(**{n: keep[n].data_ptr() for n in keep}, P=P, Nc=keep["k"].shape[0],
+                     heads=int(mha.h), ln_eps=float(cb.predictor_bias_bias_norm.eps))
+    return encoder_out, desc, keep
+
+
 @torch.no_grad()
 def greedy_search_batch(model, encoder_out: torch.Tensor, encoder_out_lens: torch.Tensor,
-                        n_steps: int = 64, return_rounds: bool = False):
-    """Greedy RNN-T decode of a batch: encoder_out [B,T,E] -> B lists of token ids."""
+                        n_steps: int = 64, return_rounds: bool = False, context_list=None,
+                        context_lengths=None, hotword: bool = None):
+    """Greedy RNN-T decode of a batch: encoder_out [B,T,E] -> B lists of token ids.
+
+    When the model carries a real ``ContextBias`` (``model.context_bias.predictor_bias``) the
+    fork's hot-word streams are applied as greedy_search.py:62-144 does with
+    ``context_filter_state='off'``: the encoder stream is biased with ``context_list`` once, every
+    predictor output with the empty context inside the device loop (``hotword=False`` turns it off)."""
     _lib.require_cuda(encoder_out, "encoder_out")
     if encoder_out.dim() != 3:
         raise RuntimeError("encoder_out must be 3-D (batch, time, dim)")
     dev = encoder_out.device
     B, T, _ = encoder_out.shape
     m = _model_tensors(model)
+    if hotword is None:
+        hotword = _has_hotword_bias(model)
+    bias_desc = None
+    if hotword:
+        with torch.cuda.device(dev):
+            encoder_out, bias_desc, _keep_alive = _hotword_setup(model, encoder_out, context_list,
+                                                                 context_lengths)
     with torch.cuda.device(dev):
         lens = encoder_out_lens.reshape(-1).to(device=dev, dtype=torch.int32).clamp(max=T).contiguous()
         if lens.numel() != B:
@@ -84,11 +153,18 @@ def greedy_search_batch(model, encoder_out: torch.Tensor, encoder_out_lens: torc
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         ptrs = (ctypes.c_void_p * (4 * m["L"]))(*[t.data_ptr() for t in m["lstm"]])
         rounds = ctypes.c_int(0)
-        _lib.call("b200_rnnt_greedy", ptr(enc_proj), ptr(lens), i32(B), i32(T), ptr(m["embed"]), ptrs,
-                  ptr(m["w_c"]), ptr(m["b_c"]), ptr(m["w_out"]), ptr(m["b_out"]), i32(m["V"]),
-                  i32(m["Emb"]), i32(m["H"]), i32(m["L"]), i32(m["J"]), i32(int(model.blank)),
-                  i32(n_steps), ptr(tokens), ptr(n_tok), i32(max_tokens), ptr(ws),
-                  ctypes.c_size_t(ws_bytes), ctypes.byref(rounds), _lib.stream_handle(dev))
+        if bias_desc is None:
+            _lib.call("b200_rnnt_greedy", ptr(enc_proj), ptr(lens), i32(B), i32(T), ptr(m["embed"]), ptrs,
+                      ptr(m["w_c"]), ptr(m["b_c"]), ptr(m["w_out"]), ptr(m["b_out"]), i32(m["V"]),
+                      i32(m["Emb"]), i32(m["H"]), i32(m["L"]), i32(m["J"]), i32(int(model.blank)),
+                      i32(n_steps), ptr(tokens), ptr(n_tok), i32(max_tokens), ptr(ws),
+                      ctypes.c_size_t(ws_bytes), ctypes.byref(rounds), _lib.stream_handle(dev))
+        else:
+            _lib.call("b200_rnnt_greedy_bias", ptr(enc_proj), ptr(lens), i32(B), i32(T), ptr(m["embed"]),
+                      ptrs, ptr(m["w_out"]), ptr(m["b_out"]), i32(m["V"]), i32(m["Emb"]), i32(m["H"]),
+                      i32(m["L"]), i32(m["J"]), i32(int(model.blank)), i32(n_steps),
+                      ctypes.byref(bias_desc), ptr(tokens), ptr(n_tok), i32(max_tokens), ptr(ws),
+                      ctypes.c_size_t(ws_bytes), ctypes.byref(rounds), _lib.stream_handle(dev))
         n_host = n_tok.cpu().tolist()  # one D2H copy of the results at the end
         width = max(n_host) if n_host else 0
         tok_host = tokens[:, :max(width, 1)].cpu().tolist()
@@ -105,7 +181,8 @@ def basic_greedy_search(model, encoder_out: torch.Tensor, encoder_out_lens, cont
     if encoder_out.size(0) != 1:
         raise RuntimeError("basic_greedy_search takes one utterance; use greedy_search_batch")
     lens = torch.as_tensor(encoder_out_lens).reshape(-1)[:1]
-    return [greedy_search_batch(model, encoder_out, lens, n_steps=n_steps)[0]]
+    return [greedy_search_batch(model, encoder_out, lens, n_steps=n_steps, context_list=context_list,
+                                context_lengths=context_lengths)[0]]
 
 
 # --------------------------------------------------------------------------- prefix beam search

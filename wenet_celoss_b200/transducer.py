@@ -112,11 +112,11 @@ def transducer_greedy_search(self, speech: torch.Tensor, speech_lengths: torch.T
     encoder_out, encoder_mask = self.encoder(speech, speech_lengths, decoding_chunk_size,
                                              num_decoding_left_chunks)
     encoder_out_lens = encoder_mask.squeeze(1).sum(1)
-    if getattr(self, "context_bias", None) is not None and _unused.get("context_list") is not None:
-        bias_hidden = self.context_bias.forward_bias_hidden(_unused["context_list"],
-                                                            _unused.get("context_lengths"))
-        encoder_out, _ = self.context_bias.forward_encoder_bias(bias_hidden, encoder_out)
-    return greedy_search_batch(self, encoder_out, encoder_out_lens, n_steps=n_steps)
+    if _unused.get("context_filter_state", "off") == "on":
+        raise NotImplementedError("hot-word gated decoding (greedy_search.py:100-131) is not implemented")
+    return greedy_search_batch(self, encoder_out, encoder_out_lens, n_steps=n_steps,
+                               context_list=_unused.get("context_list"),
+                               context_lengths=_unused.get("context_lengths"))
 
 
 @torch.no_grad()
