@@ -266,6 +266,17 @@ int b200_ctc_forced_align(const float* logp, const int64_t* ys_pad, const int32_
                           int32_t* alignment, void* workspace, size_t ws_bytes,
                           b200_stream_t stream);
 
+/* ---- Hot-word cross-entropy loss ------------------------------------------------
+ * replaces self.hw_criterion = nn.CrossEntropyLoss() (wenet/transducer/transducer.py:66) as
+ * applied at :170-200: logits [B, C, U] fp32 (class dimension 1), labels [B, U] int64, mean over
+ * the positions with label != ignore_index.  loss / count: device scalars.  bwd: grad [B, C, U] =
+ * dy / count * (softmax - onehot), zero at ignored positions. */
+int b200_ce_loss_fwd(const float* logits, const int64_t* labels, int B, int C, int U,
+                     long long ignore_index, float* loss, float* count, b200_stream_t stream);
+int b200_ce_loss_bwd(const float* logits, const int64_t* labels, int B, int C, int U,
+                     long long ignore_index, const float* dy, const float* count, float* grad,
+                     b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -399,3 +399,24 @@ def greedy_search_hotword(model, enc_biased: torch.Tensor, enc_len: int, bias_hi
             t += 1
             emitted_here = 0
     return hyp
+
+
+def hw_ce_loss(hw_output, labels, ignore_index: int = -100):
+    """nn.CrossEntropyLoss() as Transducer.forward applies it to the hot-word head
+    (wenet/transducer/transducer.py:66,181,189,199): ``hw_output [B,C,U]`` (class dim 1), ``labels
+    [B,U]``; mean over labels != ignore_index.  numpy fp64; returns (loss, d loss / d hw_output)."""
+    import numpy as np
+    x = np.asarray(hw_output, dtype=np.float64)
+    y = np.asarray(labels)
+    m = x.max(axis=1, keepdims=True)
+    lse = m + np.log(np.exp(x - m).sum(axis=1, keepdims=True))
+    logp = x - lse                                   # [B,C,U]
+    valid = y != ignore_index
+    n = int(valid.sum())
+    ysafe = np.where(valid, y, 0)
+    picked = np.take_along_axis(logp, ysafe[:, None, :], axis=1)[:, 0, :]
+    loss = float(-(picked * valid).sum() / n) if n else float("nan")
+    onehot = np.zeros_like(x)
+    np.put_along_axis(onehot, ysafe[:, None, :], 1.0, axis=1)
+    grad = (np.exp(logp) - onehot) * valid[:, None, :] / max(n, 1)
+    return loss, grad.astype(np.float32)

@@ -182,3 +182,13 @@ def test_hotword_greedy_matches_reference(golden):
         got = orc.greedy_search_hotword(m, cb.enc_biased[b:b + 1, :n], n, cb.bias_hidden_empty,
                                         n_steps=int(d["n_steps"]))
         assert got == [int(x) for x in d["hyps"][b] if x >= 0], b
+
+
+def test_hw_ce_loss_matches_reference(golden):
+    """what the real Transducer.forward handed to self.hw_criterion (transducer.py:170-200), three
+    loss modes: the numpy fp64 restatement reproduces loss and gradient."""
+    d = golden("hw_loss")
+    for mode in d["modes"]:
+        loss, grad = orc.hw_ce_loss(d[f"{mode}.hw_output"], d[f"{mode}.labels"])
+        np.testing.assert_allclose(loss, float(d[f"{mode}.hw_loss"]), rtol=1e-6)
+        np.testing.assert_allclose(grad, d[f"{mode}.grad"], atol=1e-7)

@@ -18,10 +18,11 @@ there is no CPU or PyTorch fallback.
 from ._lib import B200Error, launch_count, lib  # noqa: F401
 from .ctc import CTC, ctc_loss, patch_ctc  # noqa: F401
 from .ctc_search import ctc_prefix_beam_search_batch  # noqa: F401
+from .hw_loss import hw_ce_loss  # noqa: F401
 from .joint import fused_joint_rnnt_loss, joint_logprobs  # noqa: F401
 from .search import (PrefixBeamSearch, Sequence, basic_greedy_search,  # noqa: F401
                      greedy_search_batch, prefix_beam_search_batch)
 from .transducer import add_blank, patch_transducer, rnnt_targets  # noqa: F401
 from .rnnt import rnnt_grad_coef, rnnt_lattice, rnnt_loss  # noqa: F401
 
-__all__ = ["patch_transducer", "add_blank", "rnnt_targets", "prefix_beam_search_batch", "PrefixBeamSearch", "Sequence", "greedy_search_batch", "basic_greedy_search", "fused_joint_rnnt_loss", "CTC", "ctc_loss", "patch_ctc", "ctc_prefix_beam_search_batch", "rnnt_loss", "rnnt_lattice", "rnnt_grad_coef", "B200Error", "lib", "launch_count"]
+__all__ = ["patch_transducer", "add_blank", "rnnt_targets", "prefix_beam_search_batch", "PrefixBeamSearch", "Sequence", "greedy_search_batch", "basic_greedy_search", "fused_joint_rnnt_loss", "CTC", "ctc_loss", "patch_ctc", "hw_ce_loss", "ctc_prefix_beam_search_batch", "rnnt_loss", "rnnt_lattice", "rnnt_grad_coef", "B200Error", "lib", "launch_count"]

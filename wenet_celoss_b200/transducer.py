@@ -13,8 +13,9 @@ on the hot path to their sm_100a versions and leaves everything else untouched:
 
 Out of scope and kept as in the reference object: encoder, attention decoder
 (``_calc_att_loss``), context biasing (called exactly where the reference calls it, so an
-identity or a real ``ContextBias`` both work) and the hot-word CE loss (``hw_weight`` must be
-0: SURVEY.md §8f rank 1).
+identity or a real ``ContextBias`` both work).  The hot-word CE loss (``hw_weight != 0``,
+transducer.py:170-262) runs through ``hw_loss.hw_ce_loss`` (csrc/ce_loss.cu) on the outputs of the
+model's own ``ContextBias.forward_hw_pred*`` heads.
 """
 from __future__ import annotations
 
@@ -24,6 +25,7 @@ from typing import Dict, Optional
 import torch
 
 from .ctc import patch_ctc
+from .hw_loss import hw_loss_from_streams
 from .joint import fused_joint_rnnt_loss
 from .search import greedy_search_batch, prefix_beam_search_batch
 
@@ -58,18 +60,18 @@ def transducer_forward(self, speech: torch.Tensor, speech_lengths: torch.Tensor,
     assert text_lengths.dim() == 1, text_lengths.shape
     assert (speech.shape[0] == speech_lengths.shape[0] == text.shape[0] == text_lengths.shape[0]), (
         speech.shape, speech_lengths.shape, text.shape, text_lengths.shape)
-    if getattr(self, "hw_weight", 0.0) not in (0, 0.0):
-        raise NotImplementedError("hw_loss (transducer.py:170-262) is out of scope: set hw_weight=0")
     ignore_id = getattr(self, "ignore_id", IGNORE_ID)
     bias_hidden = _bias(self, "forward_bias_hidden", context_list, context_lengths)
     encoder_out, encoder_mask = self.encoder(speech, speech_lengths)
     encoder_out_lens = encoder_mask.squeeze(1).sum(1)
+    encoder_out_bias = predictor_out_bias = None
     if getattr(self, "context_bias", None) is not None:
-        encoder_out, _ = self.context_bias.forward_encoder_bias(bias_hidden, encoder_out)
+        encoder_out, encoder_out_bias = self.context_bias.forward_encoder_bias(bias_hidden, encoder_out)
     ys_in_pad = add_blank(text, self.blank, ignore_id)
     predictor_out = self.predictor(ys_in_pad)
     if getattr(self, "context_bias", None) is not None:
-        predictor_out, _ = self.context_bias.forward_predictor_bias(bias_hidden, predictor_out)
+        predictor_out, predictor_out_bias = self.context_bias.forward_predictor_bias(bias_hidden,
+                                                                                  predictor_out)
     rnnt_text, enc_lens32, text_lens32 = rnnt_targets(text, text_lengths, encoder_out_lens, ignore_id)
     loss = fused_joint_rnnt_loss(self.joint, encoder_out, predictor_out, rnnt_text, enc_lens32,
                                  text_lens32, blank=self.blank, reduction="mean")
@@ -85,8 +87,15 @@ def transducer_forward(self, speech: torch.Tensor, speech_lengths: torch.Tensor,
         loss = loss + self.ctc_weight * loss_ctc.sum()
     if loss_att is not None:
         loss = loss + self.attention_decoder_weight * loss_att.sum()
+    hw_loss: Optional[torch.Tensor] = None
+    if getattr(self, "hw_weight", 0.0) != 0.0:  # transducer.py:170-262
+        if getattr(self, "context_bias", None) is None or hw_label is None:
+            raise RuntimeError("hw_weight != 0 needs model.context_bias and hw_label")
+        hw_loss = hw_loss_from_streams(self, bias_hidden, predictor_out, encoder_out_bias,
+                                       predictor_out_bias, hw_label, add_blank)
+        loss = loss + self.hw_weight * hw_loss
     return {"loss": loss, "loss_att": loss_att, "loss_ctc": loss_ctc, "loss_rnnt": loss_rnnt,
-            "hw_loss": None}
+            "hw_loss": hw_loss}
 
 
 @torch.no_grad()
