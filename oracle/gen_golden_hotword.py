@@ -86,6 +86,22 @@ def main():
         assert want == mine, (b, want, mine)
         hyps_all.append(want)
         print(f"utt {b}: T={int(lens[b])} -> {len(want)} tokens {want[:10]}")
+    # loss_mode 'both': basic_greedy_search_both (greedy_search.py:297-430), filter 'off': the predictor
+    # bias attends to the GIVEN phrase list (:357)
+    from wenet.transducer.search.greedy_search import basic_greedy_search_both as fork_greedy_both
+    hyps_both = []
+    for b in range(Bs):
+        e1 = encs[b:b + 1, :int(lens[b])]
+        with torch.no_grad(), contextlib.redirect_stdout(io.StringIO()):
+            out = fork_greedy_both(model, e1, lens[b], context_list, context_lengths, n_steps=n_steps,
+                                   context_filter_state="off",
+                                   context_decoder_labels_padded=torch.IntTensor([[0]]))
+        want = out[0][0]
+        mine = orc.greedy_search_hotword(model, enc_biased[b:b + 1, :int(lens[b])], int(lens[b]),
+                                         bias_hidden, n_steps=n_steps)
+        assert want == mine, ("both", b, want, mine)
+        hyps_both.append(want)
+    print("both-mode hyps differ from pred-mode:", hyps_both != hyps_all)
     assert any(hyps_all), "degenerate fixture: nothing emitted"
     # the same model WITHOUT predictor bias must decode differently somewhere (the path matters)
     plain = [orc.greedy_search(model, enc_biased[b:b + 1, :int(lens[b])], int(lens[b]), n_steps=n_steps)
@@ -95,7 +111,11 @@ def main():
     arr = np.full((Bs, width), -1, dtype=np.int64)
     for b, h in enumerate(hyps_all):
         arr[b, :len(h)] = h
-    blob = dict(dims=np.array([V, E, E, J, H, L]), enc=encs.numpy(), enc_biased=enc_biased.numpy(),
+    wb = max(1, max(len(h) for h in hyps_both))
+    arr_both = np.full((Bs, wb), -1, dtype=np.int64)
+    for b, h in enumerate(hyps_both):
+        arr_both[b, :len(h)] = h
+    blob = dict(hyps_both=arr_both, dims=np.array([V, E, E, J, H, L]), enc=encs.numpy(), enc_biased=enc_biased.numpy(),
                 lens=lens.numpy(), hyps=arr, n_steps=np.int64(n_steps), heads=np.int64(4),
                 bias_hidden=bias_hidden.numpy(), bias_hidden_empty=bias_hidden_empty.numpy(),
                 context_list=context_list.numpy(), context_lengths=context_lengths.numpy())

@@ -182,6 +182,10 @@ def test_hotword_greedy_matches_reference(golden):
         got = orc.greedy_search_hotword(m, cb.enc_biased[b:b + 1, :n], n, cb.bias_hidden_empty,
                                         n_steps=int(d["n_steps"]))
         assert got == [int(x) for x in d["hyps"][b] if x >= 0], b
+        # basic_greedy_search_both (loss_mode 'both', greedy_search.py:297-430): given phrase list
+        got = orc.greedy_search_hotword(m, cb.enc_biased[b:b + 1, :n], n, cb.bias_hidden,
+                                        n_steps=int(d["n_steps"]))
+        assert got == [int(x) for x in d["hyps_both"][b] if x >= 0], ("both", b)
 
 
 def test_hw_ce_loss_matches_reference(golden):

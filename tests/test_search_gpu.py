@@ -121,6 +121,12 @@ def test_hotword_greedy_golden(golden):
                                context_lengths=ctx_len)
     for b in range(enc.size(0)):
         assert hyps[b] == _unpad(d["hyps"][b]), b
+    # loss_mode 'both' -> basic_greedy_search_both: the predictor bias attends to the given list
+    m.loss_mode = "both"
+    hyps_both = greedy_search_batch(m, enc, lens, n_steps=int(d["n_steps"]), context_list=ctx,
+                                    context_lengths=ctx_len)
+    for b in range(enc.size(0)):
+        assert hyps_both[b] == _unpad(d["hyps_both"][b]), ("both", b)
     # without the predictor bias the same model decodes differently: the device path is exercised
     plain = greedy_search_batch(m, m.context_bias.enc_biased, lens, n_steps=int(d["n_steps"]), hotword=False)
     assert plain != hyps

@@ -78,8 +78,10 @@ def _has_hotword_bias(model) -> bool:
 
 def _hotword_setup(model, encoder_out, context_list, context_lengths):
     """What greedy_search.py:62-70 does before its loop: phrase vectors of the given and of the
-    EMPTY context list, encoder stream biased with the given one; plus K / V of the empty context for
-    the per-step predictor bias (fixed for the whole call)."""
+    EMPTY context list, encoder stream biased with the given one; plus K / V of the context the
+    per-step predictor bias attends to (fixed for the whole call): the EMPTY list in
+    ``basic_greedy_search`` (loss_mode 'pred', :140-144), the GIVEN list in
+    ``basic_greedy_search_both`` (every other loss_mode, :357, transducer.py:559-597)."""
     cb = model.context_bias
     dev = encoder_out.device
     if context_list is None:
@@ -95,7 +97,8 @@ def _hotword_setup(model, encoder_out, context_list, context_lengths):
     try:
         encoder_out, _ = cb.forward_encoder_bias(bias_hidden, encoder_out)
         mha = cb.predictor_bias
-        ctx = bias_hidden_empty[0].float()
+        given = getattr(model, "loss_mode", "pred") != "pred"
+        ctx = (bias_hidden if given else bias_hidden_empty)[0].float()
         f32 = lambda t: t.detach().to(torch.float32).contiguous()
         keep = dict(k=f32(mha.linear_k(ctx)), v=f32(mha.linear_v(ctx)))
     finally:
