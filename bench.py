@@ -240,6 +240,10 @@ class RnntLogitsWorkload:
 
 
 # --------------------------------------------------------------------------- reference arm
+FUSED_DESC = ("rnnt_fused: joint (enc_ffn, pred_ffn, tanh, ffn_out) + RNN-T loss fwd+bwd, logits "
+              "never materialised, B=32 T=500 U=100 V=5000 J=512 per GPU (cfg3), bf16 MMA operands")
+
+
 def reference_step(cfg, T_s, threads, seed=0):
     """One fwd+bwd of the reference path (oracle port: torch joint + torchaudio CPU
     rnnt_loss, wenet/transducer/transducer.py:132-147) on one utterance truncated to
@@ -287,7 +291,8 @@ def run_reference(args, cfg):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": "rnnt_joint_loss_fwd_bwd B=32 T=500 U=100 V=5000 (cfg3)", **cfg},
+        "config": {"workload": FUSED_DESC, "global_batch": cfg["B"], **cfg, "ragged": False,
+                   "parallelism": "cpu (rank 0 only; reference = torch joint + torchaudio rnnt_loss, fp32)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -464,8 +469,7 @@ class RnntFusedWorkload:
                 "step_counted_flops": counted}
 
     def describe(self):
-        return ("rnnt_fused: joint (enc_ffn, pred_ffn, tanh, ffn_out) + RNN-T loss fwd+bwd, logits "
-                "never materialised, B=32 T=500 U=100 V=5000 J=512 per GPU (cfg3), bf16 MMA operands",
+        return (FUSED_DESC,
                 "L2 flushed by the step itself: each step streams >16 GB of gradient scratch")
 
 

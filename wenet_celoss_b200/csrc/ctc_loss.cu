@@ -42,20 +42,37 @@ ctc_logprobs_kernel(const T* __restrict__ logits, const long long* __restrict__ 
   const int b = int(rowi / Tm), t = int(rowi - (long long)b * Tm);
   if (t >= hlens[b]) return;
   const T* row = logits + rowi * V;
-  const float l = warp_row_lse<T>(row, V, lane);
-  if (lane == 0) lse[rowi] = l;
   const int S = 2 * ys_lens[b] + 1;
   const int Smax = 2 * Lmax + 1;
   const long long* ys = ys_pad + (long long)b * Lmax;
-  float* out = lp_ext + rowi * Smax;
-  const float lpb = Elem<T>::to_float(row[blank]) - l;
-  for (int s = lane; s < S; s += 32) {
-    float v = lpb;
-    if (s & 1) {
-      int c = (int)ys[s >> 1];
-      v = (c >= 0 && c < V) ? Elem<T>::to_float(row[c]) - l : -INFINITY;
+  // The label gather goes FIRST: issued before the row is streamed, its 64-byte DRAM fetches are
+  // reused by the stream a few microseconds later (L2 hits).  Gathering after the stream re-fetched
+  // ~100 x 64 B per row from DRAM (ncu: 1.73 GB read for 1.28 GB of logits).
+  constexpr int kPre = 8;  // label states per lane held in registers: S <= 512 (odd states only)
+  float xg[kPre];
+#pragma unroll
+  for (int i = 0; i < kPre; ++i) {
+    const int s = 1 + 2 * (lane + 32 * i);
+    xg[i] = -INFINITY;
+    if (s < S) {
+      const int c = (int)ys[s >> 1];
+      if (c >= 0 && c < V) xg[i] = Elem<T>::to_float(row[c]);
     }
-    out[s] = v;
+  }
+  const float xb = Elem<T>::to_float(row[blank]);
+  const float l = warp_row_lse<T>(row, V, lane);
+  if (lane == 0) lse[rowi] = l;
+  float* out = lp_ext + rowi * Smax;
+  const float lpb = xb - l;
+  for (int s = 2 * lane; s < S; s += 64) out[s] = lpb;  // blank states
+#pragma unroll
+  for (int i = 0; i < kPre; ++i) {
+    const int s = 1 + 2 * (lane + 32 * i);
+    if (s < S) out[s] = xg[i] - l;
+  }
+  for (int s = 1 + 2 * (lane + 32 * kPre); s < S; s += 64) {  // longer label sequences
+    const int c = (int)ys[s >> 1];
+    out[s] = (c >= 0 && c < V) ? Elem<T>::to_float(row[c]) - l : -INFINITY;
   }
 }
 
@@ -284,6 +301,20 @@ ctc_grad_kernel(const T* __restrict__ logits, const float* __restrict__ lse,
   const float* be = beta + rowi * Smax;
   const float* lp = lp_ext + rowi * Smax;
   const int32_t* ld = leader + (long long)b * Smax;
+  // logits at the label classes, gathered BEFORE the row is streamed (see ctc_logprobs_kernel)
+  const long long* ys = ys_pad + (long long)b * Lmax;
+  constexpr int kPre = 8;
+  float xg[kPre];
+#pragma unroll
+  for (int i = 0; i < kPre; ++i) {
+    const int s = 1 + 2 * (lane + 32 * i);
+    xg[i] = 0.f;
+    if (s < S && ld[s] == s) {
+      const int c = (int)ys[s >> 1];
+      if (c >= 0 && c < V) xg[i] = Elem<T>::to_float(row[c]);
+    }
+  }
+  const float xblank = Elem<T>::to_float(row[blank]);
   for (int s = lane; s < S; s += 32) occ[s] = 0.f;
   __syncwarp();
   float occ_blank = 0.f;
@@ -298,16 +329,20 @@ ctc_grad_kernel(const T* __restrict__ logits, const float* __restrict__ lse,
   occ_blank = warp_sum(occ_blank);
   warp_row_softmax_store<T>(row, grow, V, lane, false, -l * kLog2e, sc, -1.f);
   __syncwarp();  // streaming stores and occ[] atomics are ordered before the fix-ups
-  if (lane == 0) {
-    float x = Elem<T>::to_float(row[blank]);
-    grow[blank] = Elem<T>::from_float(sc * (expf(x - l) - occ_blank));
-  }
-  const long long* ys = ys_pad + (long long)b * Lmax;
-  for (int s = 1 + 2 * lane; s < S; s += 64) {
-    if (ld[s] != s) continue;  // only the first state of each distinct label writes
-    int c = (int)ys[s >> 1];
+  if (lane == 0) grow[blank] = Elem<T>::from_float(sc * (expf(xblank - l) - occ_blank));
+#pragma unroll
+  for (int i = 0; i < kPre; ++i) {
+    const int s = 1 + 2 * (lane + 32 * i);
+    if (s >= S || ld[s] != s) continue;  // only the first state of each distinct label writes
+    const int c = (int)ys[s >> 1];
     if (c < 0 || c >= V || c == blank) continue;
-    float x = Elem<T>::to_float(row[c]);
+    grow[c] = Elem<T>::from_float(sc * (expf(xg[i] - l) - occ[s]));
+  }
+  for (int s = 1 + 2 * (lane + 32 * kPre); s < S; s += 64) {  // longer label sequences
+    if (ld[s] != s) continue;
+    const int c = (int)ys[s >> 1];
+    if (c < 0 || c >= V || c == blank) continue;
+    const float x = Elem<T>::to_float(row[c]);
     grow[c] = Elem<T>::from_float(sc * (expf(x - l) - occ[s]));
   }
 }

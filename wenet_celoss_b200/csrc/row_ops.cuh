@@ -14,12 +14,20 @@ __device__ __forceinline__ float warp_row_lse(const T* __restrict__ row, int V, 
   constexpr int K = Elem<T>::kPerVec;
   RowSegs<T> rs(row, V);
   float m = kNegBig, s = 0.f;
+  // software pipeline: the loads of block i+1 are in flight while block i is reduced
+  uint4 v[kUnroll], nv[kUnroll];
+#pragma unroll
+  for (int j = 0; j < kUnroll; ++j) {
+    int idx = j * 32 + lane;
+    if (idx < rs.nseg) nv[j] = ldg_stream16(rs.seg0 + idx);
+  }
   for (int base = 0; base < rs.nseg; base += 32 * kUnroll) {
-    uint4 v[kUnroll];
+#pragma unroll
+    for (int j = 0; j < kUnroll; ++j) v[j] = nv[j];
 #pragma unroll
     for (int j = 0; j < kUnroll; ++j) {
-      int idx = base + j * 32 + lane;
-      if (idx < rs.nseg) v[j] = ldg_stream16(rs.seg0 + idx);
+      int idx = base + 32 * kUnroll + j * 32 + lane;
+      if (idx < rs.nseg) nv[j] = ldg_stream16(rs.seg0 + idx);
     }
     float f[kUnroll][K];
     float lmax = kNegBig;
@@ -69,13 +77,22 @@ __device__ __forceinline__ void warp_row_softmax_store(const T* __restrict__ row
   constexpr int K = Elem<T>::kPerVec;
   RowSegs<T> rs(row, V);
   uint4* oseg0 = reinterpret_cast<uint4*>(reinterpret_cast<uintptr_t>(out) & ~uintptr_t(15));
+  uint4 v[kUnroll], nv[kUnroll];
+  if (!dead) {
+#pragma unroll
+    for (int j = 0; j < kUnroll; ++j) {
+      int idx = j * 32 + lane;
+      if (idx < rs.nseg) nv[j] = ldg_stream16(rs.seg0 + idx);
+    }
+  }
   for (int base = 0; base < rs.nseg; base += 32 * kUnroll) {
-    uint4 v[kUnroll];
-    if (!dead) {
+    if (!dead) {  // software pipeline: next block's loads in flight while this one is written
+#pragma unroll
+      for (int j = 0; j < kUnroll; ++j) v[j] = nv[j];
 #pragma unroll
       for (int j = 0; j < kUnroll; ++j) {
-        int idx = base + j * 32 + lane;
-        if (idx < rs.nseg) v[j] = ldg_stream16(rs.seg0 + idx);
+        int idx = base + 32 * kUnroll + j * 32 + lane;
+        if (idx < rs.nseg) nv[j] = ldg_stream16(rs.seg0 + idx);
       }
     }
 #pragma unroll
