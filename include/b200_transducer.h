@@ -220,6 +220,34 @@ int b200_rnnt_greedy_bias(const float* enc_proj, const int32_t* lens, int B, int
                           int32_t* n_tok, int max_tokens, void* workspace, size_t ws_bytes,
                           int* rounds_out, b200_stream_t stream);
 
+/* greedy search with the fork's hot-word GATE and "go-back" - context_filter_state='on', the
+ * default of Transducer.greedy_search (wenet/transducer/transducer.py:525) and of
+ * wenet/bin/recognize.py:139-141; loop at wenet/transducer/search/greedy_search.py:88-165.
+ * Per predictor call: gate = argmax ContextBias.forward_hw_pred (wenet/transformer/
+ * context_bias.py:382-387) of the predictor output biased with the GIVEN phrase list; decision 0
+ * (predictor stream biased with the given list, joint over the encoder stream biased with the
+ * EMPTY list), decision 1 (the other way round: bias->k / bias->v hold the EMPTY list), or a
+ * go-back (:116-131) that drops the last decision and token, rewinds the frame index and re-runs
+ * the previous predictor call with decisions forced to 1.  `enc_proj` = enc_ffn of the encoder
+ * stream biased with the given list, gate->enc_proj_empty = the same over the empty list.
+ * K / V tensors are linear_k / linear_v of the respective attention applied to the phrase
+ * vectors [Nc,P]; hw_output_layer is [n_labels,P] (unified_hw_odim == P).  Outputs as
+ * b200_rnnt_greedy plus decisions [B,max_dec] / n_dec [B] = the reference's `result` list. */
+typedef struct {
+  const float* enc_proj_empty;
+  const float *k_given, *v_given;
+  const float *hq_w, *hq_b, *hk, *hv, *ho_w, *ho_b, *hln_g, *hln_b, *hout_w, *hout_b;
+  int Nc_given, hw_heads, n_labels;
+} b200_gate_t;
+size_t b200_greedy_gated_workspace_bytes(int B, int V, int H, int L, int J);
+int b200_rnnt_greedy_gated(const float* enc_proj, const int32_t* lens, int B, int T,
+                           const float* embed, const float* const* lstm, const float* w_out,
+                           const float* b_out, int V, int Emb, int H, int L, int J, int blank,
+                           int n_steps, const b200_pred_bias_t* bias, const b200_gate_t* gate,
+                           int32_t* tokens, int32_t* n_tok, int max_tokens, int32_t* decisions,
+                           int32_t* n_dec, int max_dec, void* workspace, size_t ws_bytes,
+                           int* rounds_out, b200_stream_t stream);
+
 /* ---- Batched RNN-T prefix beam search ---------------------------------------
  * replaces PrefixBeamSearch.prefix_beam_search (wenet/transducer/search/
  * prefix_beam_search.py:42-148) for a batch: per frame predictor step + joint + log_softmax

@@ -401,6 +401,119 @@ def greedy_search_hotword(model, enc_biased: torch.Tensor, enc_len: int, bias_hi
     return hyp
 
 
+def hw_pred_gate(cb, ctx: torch.Tensor, y: torch.Tensor) -> int:
+    """ContextBias.forward_hw_pred (wenet/transformer/context_bias.py:382-387) + ``topk(1)`` index
+    (greedy_search.py:103-110): multi-head attention ``hw_bias`` of the BIASED predictor output
+    ``y [1,1,D]`` over the phrase vectors ``ctx [1,Nc,D]``, ``hw_bias_norm``, ``hw_output_layer``;
+    returns the arg-max label (the gate).  Needs unified_hw_odim == embedding size, as in
+    conf/encoder_bias_conformer_rnnt_4_head_bi_1_layer_pred.yaml:40,51."""
+    import torch.nn.functional as F
+    mha = cb.hw_bias
+    nh = int(mha.h)
+    D = y.size(-1)
+    dk = D // nh
+    q = F.linear(y, mha.linear_q.weight, mha.linear_q.bias).view(1, -1, nh, dk).transpose(1, 2)
+    k = F.linear(ctx, mha.linear_k.weight, mha.linear_k.bias).view(1, -1, nh, dk).transpose(1, 2)
+    v = F.linear(ctx, mha.linear_v.weight, mha.linear_v.bias).view(1, -1, nh, dk).transpose(1, 2)
+    att = torch.softmax(q @ k.transpose(-2, -1) / math.sqrt(dk), dim=-1)
+    a = (att @ v).transpose(1, 2).reshape(1, -1, D)
+    a = F.linear(a, mha.linear_out.weight, mha.linear_out.bias)
+    a = F.layer_norm(a, (D,), cb.hw_bias_norm.weight, cb.hw_bias_norm.bias, cb.hw_bias_norm.eps)
+    out = F.linear(a, cb.hw_output_layer.weight, cb.hw_output_layer.bias).reshape(-1)
+    return int(out.topk(1)[1].item())
+
+
+@torch.no_grad()
+def greedy_search_hotword_gated(model, enc_biased: torch.Tensor, enc_empty: torch.Tensor, enc_len: int,
+                                bias_hidden: torch.Tensor, bias_hidden_empty: torch.Tensor,
+                                n_steps: int = 64):
+    """The fork's DEFAULT greedy search, ``context_filter_state='on'``
+    (wenet/transducer/search/greedy_search.py:88-165; default at transducer.py:525 and
+    wenet/bin/recognize.py:139-141), restated as a state machine without the reference's
+    ``step_list / cache_list / input_list`` stacks.  Per predictor call (:92-99):
+      gate = argmax forward_hw_pred(bias_hidden, forward_predictor_bias(bias_hidden, raw))  (:100-110)
+      not going back, gate 0           -> decision 0, remember this frame as ``last_t``     (:111-114)
+      not going back, gate 1 after a 0 -> GO BACK (:116-131): drop the last decision and the last
+          token, rewind ``t`` to ``last_t``, restore the predictor input and LSTM state of the
+          PREVIOUS call (the stacks' [-1] after the pops), decrement the per-frame emission count,
+          and re-run that call with decisions forced to 1 until a call at ``t >= go_back_end``
+      otherwise                        -> decision 1                                         (:132-137)
+    decision 1: predictor stream biased with the EMPTY list, encoder stream biased with the
+    given list; decision 0: predictor stream biased with the given list, encoder stream biased
+    with the empty list (:140-150).  Only the previous call is ever restored (two go-backs need
+    a decision-0 call between them), so three LSTM states suffice: before the previous call,
+    before this call, after this call.  Returns (hyp, decisions)."""
+    dev = enc_biased.device
+    blank = model.blank
+    cb = model.context_bias
+    pad = torch.zeros(1, 1, device=dev)
+    token = torch.tensor([[blank]], device=dev)
+    state = model.predictor.init_state(1, device=dev)
+    pending_state = state
+    prev_call = None                 # (input token, LSTM state before the call) of the previous call
+    pred_step = None
+    need_predictor = True
+    emitted_here = 0
+    t = last_t = 0
+    going_back, go_back_end = False, -1
+    hyp: List[int] = []
+    result: List[int] = []
+    while t < int(enc_len):
+        if need_predictor:
+            raw, pending_state = model.predictor.forward_step(token, pad, state)
+            y_given = predictor_bias(cb, bias_hidden, raw)
+            gate = hw_pred_gate(cb, bias_hidden, y_given)
+            if not going_back:
+                if gate == 0:
+                    result.append(0)
+                    last_t = t
+                elif result and result[-1] == 0:
+                    go_back_end, t, going_back = t, last_t, True
+                    result.pop()
+                    hyp.pop()
+                    emitted_here -= 1
+                    token, state = prev_call
+                    continue         # prev_call stays: the re-run call has the same input and state
+                else:
+                    result.append(1)
+            else:
+                result.append(1)
+                if t >= go_back_end:
+                    going_back = False
+            prev_call = (token, state)
+            pred_step = predictor_bias(cb, bias_hidden_empty, raw) if result[-1] == 1 else y_given
+        enc = enc_biased if result[-1] == 1 else enc_empty
+        logp = joint_logits(enc[:, t:t + 1, :], pred_step, model.joint).log_softmax(dim=-1)
+        k = int(logp.reshape(-1).argmax())
+        if k != blank:
+            hyp.append(k)
+            need_predictor = True
+            emitted_here += 1
+            token = torch.tensor([[k]], device=dev)
+            state = pending_state
+        if k == blank or emitted_here >= n_steps:
+            if k == blank:
+                need_predictor = False
+            t += 1
+            emitted_here = 0
+    return hyp, result
+
+
+def edit_distance(a, b) -> float:
+    """Levenshtein distance of two label sequences, as the helper at
+    wenet/transducer/search/greedy_search.py:6-32 (returned as ``dist`` by the fork's greedy)."""
+    import numpy as np
+    a, b = list(a), list(b)
+    prev = np.arange(len(b) + 1, dtype=np.float64)
+    for i in range(1, len(a) + 1):
+        cur = np.empty_like(prev)
+        cur[0] = i
+        for j in range(1, len(b) + 1):
+            cur[j] = min(prev[j] + 1, cur[j - 1] + 1, prev[j - 1] + (0 if a[i - 1] == b[j - 1] else 1))
+        prev = cur
+    return float(prev[len(b)])
+
+
 def hw_ce_loss(hw_output, labels, ignore_index: int = -100):
     """nn.CrossEntropyLoss() as Transducer.forward applies it to the hot-word head
     (wenet/transducer/transducer.py:66,181,189,199): ``hw_output [B,C,U]`` (class dim 1), ``labels

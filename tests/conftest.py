@@ -76,19 +76,29 @@ class HotwordBiasStandIn(torch.nn.Module):
         self.predictor_bias_bias_norm = torch.nn.LayerNorm(P)
         self.predictor_bias_combine = torch.nn.Linear(2 * P, P)
         self.predictor_bias_out_norm = torch.nn.LayerNorm(P)
-        sd = {k[3:]: torch.from_numpy(d[k]) for k in d.files
-              if k.startswith("cb.predictor_bias")}
+        keys = ("cb.predictor_bias",)
+        if "enc_empty" in d.files:   # gated fixture: ContextBias.forward_hw_pred modules (context_bias.py:382-387)
+            self.hw_bias = _Mha(int(d["heads"]), P)
+            self.hw_bias_norm = torch.nn.LayerNorm(P)
+            self.hw_output_layer = torch.nn.Linear(P, int(d["cb.hw_output_layer.weight"].shape[0]))
+            keys += ("cb.hw_bias.", "cb.hw_bias_norm.", "cb.hw_output_layer.")
+        sd = {k[3:]: torch.from_numpy(d[k]) for k in d.files if k.startswith(keys)}
         self.load_state_dict(sd, strict=True)
         self.register_buffer("bias_hidden", torch.from_numpy(d["bias_hidden"]))
         self.register_buffer("bias_hidden_empty", torch.from_numpy(d["bias_hidden_empty"]))
         self.register_buffer("enc", torch.from_numpy(d["enc"]))
         self.register_buffer("enc_biased", torch.from_numpy(d["enc_biased"]))
+        if "enc_empty" in d.files:
+            self.register_buffer("enc_empty", torch.from_numpy(d["enc_empty"]))
 
     def forward_bias_hidden(self, context_list, context_lengths):
         return self.bias_hidden_empty if context_list.numel() == 1 else self.bias_hidden
 
     def forward_encoder_bias(self, bias_hidden, encoder_out):
-        assert bias_hidden is self.bias_hidden and torch.equal(encoder_out, self.enc)
+        assert torch.equal(encoder_out, self.enc)
+        if bias_hidden is self.bias_hidden_empty:
+            return self.enc_empty, None
+        assert bias_hidden is self.bias_hidden
         return self.enc_biased, None
 
 

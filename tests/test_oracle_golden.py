@@ -188,6 +188,37 @@ def test_hotword_greedy_matches_reference(golden):
         assert got == [int(x) for x in d["hyps_both"][b] if x >= 0], ("both", b)
 
 
+def test_hotword_gated_greedy_matches_reference(golden):
+    """the fork's DEFAULT greedy (context_filter_state='on', greedy_search.py:88-165): gate decisions,
+    go-back, token lists and edit distance recorded from the real basic_greedy_search."""
+    from conftest import load_hotword_model
+    d = golden("hotword_greedy_gated")
+    m = load_hotword_model(d)
+    cb = m.context_bias
+    assert int(d["go_backs"]) >= 3
+    labels = d["labels"].reshape(-1).tolist()
+    for b in range(d["enc"].shape[0]):
+        n = int(d["lens"][b])
+        hyp, res = orc.greedy_search_hotword_gated(m, cb.enc_biased[b:b + 1, :n], cb.enc_empty[b:b + 1, :n], n,
+                                                   cb.bias_hidden, cb.bias_hidden_empty,
+                                                   n_steps=int(d["n_steps"]))
+        assert hyp == [int(x) for x in d["hyps"][b] if x >= 0], b
+        assert res == [int(x) for x in d["decisions"][b] if x >= 0], b
+        assert orc.edit_distance(labels, res) == float(d["dist"][b])
+
+
+def test_edit_distance_host():
+    """product-side edit distance (host bookkeeping) against the oracle's restatement of
+    greedy_search.py:6-32."""
+    import random
+    from wenet_celoss_b200.search import edit_distance
+    rnd = random.Random(5)
+    for _ in range(50):
+        a = [rnd.randint(0, 1) for _ in range(rnd.randint(0, 12))]
+        b = [rnd.randint(0, 1) for _ in range(rnd.randint(0, 12))]
+        assert edit_distance(a, b) == orc.edit_distance(a, b)
+
+
 def test_hw_ce_loss_matches_reference(golden):
     """what the real Transducer.forward handed to self.hw_criterion (transducer.py:170-200), three
     loss modes: the numpy fp64 restatement reproduces loss and gradient."""

@@ -130,3 +130,38 @@ def test_hotword_greedy_golden(golden):
     # without the predictor bias the same model decodes differently: the device path is exercised
     plain = greedy_search_batch(m, m.context_bias.enc_biased, lens, n_steps=int(d["n_steps"]), hotword=False)
     assert plain != hyps
+
+
+def test_hotword_gated_greedy_golden(golden):
+    """the fork's DEFAULT decode (context_filter_state='on', greedy_search.py:88-165): hot-word gate
+    per predictor call, decision-dependent streams and the go-back re-decode on the device; token
+    lists, gate decisions and edit distance of the real basic_greedy_search (46 go-backs in the fixture)."""
+    from conftest import load_hotword_model
+    from wenet_celoss_b200 import basic_greedy_search, greedy_search_batch
+    d = golden("hotword_greedy_gated")
+    m = load_hotword_model(d).to(DEV)
+    enc = torch.from_numpy(d["enc"]).to(DEV)
+    lens = torch.from_numpy(d["lens"]).to(DEV)
+    ctx = torch.from_numpy(d["context_list"]).to(DEV)
+    ctx_len = torch.from_numpy(d["context_lengths"]).to(DEV)
+    n_steps = int(d["n_steps"])
+    hyps, dec = greedy_search_batch(m, enc, lens, n_steps=n_steps, context_list=ctx, context_lengths=ctx_len,
+                                    context_filter_state="on", return_decisions=True)
+    for b in range(enc.size(0)):
+        assert hyps[b] == _unpad(d["hyps"][b]), b
+        assert dec[b] == _unpad(d["decisions"][b]), b
+    # the gate matters: filter 'off' decodes differently on the same model
+    off = greedy_search_batch(m, enc, lens, n_steps=n_steps, context_list=ctx, context_lengths=ctx_len)
+    assert [off[b] for b in range(enc.size(0))] == [_unpad(r) for r in d["hyps_off"]]
+    assert off != hyps
+    # single-utterance entry point with the fork's return triple ([hyps], dist, result)
+    # (the stand-in serves the stored full-length streams, so use a full-length utterance)
+    b = int(np.argmax(d["lens"]))
+    assert int(d["lens"][b]) == enc.size(1)
+    m1 = load_hotword_model(d).to(DEV)
+    cb = m1.context_bias
+    cb.enc, cb.enc_biased, cb.enc_empty = cb.enc[b:b + 1], cb.enc_biased[b:b + 1], cb.enc_empty[b:b + 1]
+    out = basic_greedy_search(m1, enc[b:b + 1], lens[b:b + 1], ctx, ctx_len, n_steps, "on",
+                              torch.from_numpy(d["labels"]))
+    assert out[0] == [_unpad(d["hyps"][b])] and out[1] == float(d["dist"][b])
+    assert out[2] == _unpad(d["decisions"][b])

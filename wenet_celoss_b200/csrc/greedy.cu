@@ -58,7 +58,21 @@ struct State {
   int32_t* act_list;   // [2][B]
   int32_t* need_list;  // [2][B]
   int32_t* counters;   // [2][2]: {n_act, n_need} per parity; [4] = rounds run (persistent kernel)
+  // ---- hot-word gate with "go-back" (greedy_search.py:100-150); null / 2 slots otherwise ----
+  int nslot;                    // LSTM state slots: 2, or 3 = {before previous call, current, written by this call}
+  const float* enc_proj_empty;  // [B, T, J] encoder stream biased with the EMPTY phrase list (decision 0)
+  int32_t* last_t;     // [B] frame of the last decision-0 call
+  int32_t* gb_flag;    // [B] going back: decisions forced to 1
+  int32_t* gb_end;     // [B] frame at which the go-back started
+  int32_t* last_res;   // [B] result[-1]
+  int32_t* prev_tok;   // [B] predictor input of the previous call
+  int32_t* skip;       // [B] went back this round: the joint / argmax of this round do not count
+  int32_t* n_dec;      // [B] decisions kept (len(result))
+  int32_t* dec;        // [B, max_dec]
+  int max_dec;
 };
+
+__device__ __forceinline__ int next_slot(int p, int nslot) { return p + 1 == nslot ? 0 : p + 1; }
 
 __global__ void init_kernel(State S, int blank, int L, int H) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -75,6 +89,15 @@ __global__ void init_kernel(State S, int blank, int L, int H) {
   S.par[b] = 0;
   S.n_tok[b] = 0;
   S.need[b] = 0;
+  if (S.skip) {
+    S.last_t[b] = 0;
+    S.gb_flag[b] = 0;
+    S.gb_end[b] = -1;
+    S.last_res[b] = 1;
+    S.prev_tok[b] = blank;
+    S.skip[b] = 0;
+    S.n_dec[b] = 0;
+  }
 }
 // second init pass (after the counters are zero): build the round-0 lists
 __global__ void init_lists_kernel(State S) {
@@ -113,8 +136,9 @@ __global__ void __launch_bounds__(256) lstm_layer_kernel(Model M, State S, int l
     const int p = S.par[b];
     const float* hin = S.h + ((size_t)p * M.L + layer) * lay + (size_t)b * H;
     const float* cin = S.c + ((size_t)p * M.L + layer) * lay + (size_t)b * H;
+    const int pn = next_slot(p, S.nslot);
     const float* x = (layer == 0) ? M.embed + (size_t)S.token[b] * In
-                                  : S.h + ((size_t)(p ^ 1) * M.L + layer - 1) * lay + (size_t)b * H;
+                                  : S.h + ((size_t)pn * M.L + layer - 1) * lay + (size_t)b * H;
     float a[4] = {0.f, 0.f, 0.f, 0.f};
     for (int i = lane; i < In; i += 32) {
       const float xv = x[i];
@@ -132,8 +156,8 @@ __global__ void __launch_bounds__(256) lstm_layer_kernel(Model M, State S, int l
       const float ig = sigmoidf_acc(a[0]), fg = sigmoidf_acc(a[1]);
       const float gg = tanhf(a[2]), og = sigmoidf_acc(a[3]);
       const float cn = fg * cin[j] + ig * gg;
-      S.c[((size_t)(p ^ 1) * M.L + layer) * lay + (size_t)b * H + j] = cn;
-      S.h[((size_t)(p ^ 1) * M.L + layer) * lay + (size_t)b * H + j] = og * tanhf(cn);
+      S.c[((size_t)pn * M.L + layer) * lay + (size_t)b * H + j] = cn;
+      S.h[((size_t)pn * M.L + layer) * lay + (size_t)b * H + j] = og * tanhf(cn);
     }
   }
 }
@@ -156,7 +180,7 @@ __global__ void __launch_bounds__(256) pred_z_kernel(Model M, State S, int round
     const int b = list[q];
     float pp;
     if (S.need[b] && !M.has_bias) {
-      const int p = S.par[b] ^ 1;  // state written by the LSTM kernels of this round
+      const int p = next_slot(S.par[b], S.nslot);  // state written by the LSTM kernels of this round
       const float* h = S.h + ((size_t)p * M.L + M.L - 1) * lay + (size_t)b * H;
       float a = 0.f;
       for (int i = lane; i < H; i += 32) a = fmaf(__ldg(w + i), h[i], a);
@@ -166,7 +190,9 @@ __global__ void __launch_bounds__(256) pred_z_kernel(Model M, State S, int round
       pp = S.pp[(size_t)b * M.J + j];
     }
     if (lane == 0) {
-      const float e = S.enc_proj[((size_t)b * S.T + S.t[b]) * M.J + j];
+      // decision 0 pairs the predictor stream with the EMPTY-biased encoder stream (greedy_search.py:146-150)
+      const float* ep = (S.enc_proj_empty && S.last_res[b] == 0) ? S.enc_proj_empty : S.enc_proj;
+      const float e = ep[((size_t)b * S.T + S.t[b]) * M.J + j];
       S.z[(size_t)b * M.J + j] = tanhf(e + pp);
     }
   }
@@ -280,10 +306,15 @@ __global__ void __launch_bounds__(1024) update_kernel(Model M, State S, int roun
         bi = oi;
       }
     }
-    if (lane == 0) {
+    if (lane == 0 && S.skip && S.skip[b]) {
+      // went back this round (pred_gate_kernel rewound t / token / LSTM slot): re-run the previous call
+      S.skip[b] = 0;
+      S.act_list[nxt * S.B + atomicAdd(&S.counters[nxt * 2 + 0], 1)] = b;
+      S.need_list[nxt * S.B + atomicAdd(&S.counters[nxt * 2 + 1], 1)] = b;
+    } else if (lane == 0) {
       const int k = bi;
       int t = S.t[b], cnt = S.cnt[b];
-      if (S.need[b]) S.par[b] ^= 1;  // the LSTM state written this round becomes current
+      if (S.need[b]) S.par[b] = next_slot(S.par[b], S.nslot);  // the LSTM state written this round becomes current
       int need = 0;
       if (k != M.blank) {
         const int n = S.n_tok[b];

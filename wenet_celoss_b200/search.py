@@ -11,8 +11,11 @@ reference functions read: ``model.predictor`` (``embed``, ``rnn`` = nn.LSTM, ``p
 
 With a real ``ContextBias`` on the model the fork's hot-word streams are applied as
 ``context_filter_state='off'`` does (greedy_search.py:62-70,140-144: encoder stream biased once,
-every predictor output biased with the empty context inside the device loop).  The gate /
-"go-back" of ``context_filter_state='on'`` (greedy_search.py:100-131) is not implemented and raises.
+every predictor output biased with the empty context inside the device loop), or as the fork's
+DEFAULT ``context_filter_state='on'`` does (greedy_search.py:100-150; transducer.py:525): per
+predictor call a hot-word gate (``ContextBias.forward_hw_pred``), decisions 0 / 1 that swap which
+stream is biased with the phrase list, and the "go-back" re-decode - all inside the device loop
+(``b200_rnnt_greedy_gated``).
 """
 from __future__ import annotations
 
@@ -71,12 +74,33 @@ class _PredBias(ctypes.Structure):
                  ("ln_eps", ctypes.c_float)])
 
 
+class _Gate(ctypes.Structure):
+    """b200_gate_t (include/b200_transducer.h)."""
+    _fields_ = ([(n, ctypes.c_void_p) for n in
+                 ("enc_proj_empty", "k_given", "v_given", "hq_w", "hq_b", "hk", "hv", "ho_w", "ho_b",
+                  "hln_g", "hln_b", "hout_w", "hout_b")] +
+                [("Nc_given", ctypes.c_int), ("hw_heads", ctypes.c_int), ("n_labels", ctypes.c_int)])
+
+
+def edit_distance(a, b) -> float:
+    """Levenshtein distance, the ``dist`` the fork's greedy search returns
+    (wenet/transducer/search/greedy_search.py:6-32,174): host bookkeeping on two short lists."""
+    a, b = [int(x) for x in a], [int(x) for x in b]
+    prev = list(range(len(b) + 1))
+    for i, x in enumerate(a, 1):
+        cur = [i] + [0] * len(b)
+        for j, y in enumerate(b, 1):
+            cur[j] = min(prev[j] + 1, cur[j - 1] + 1, prev[j - 1] + (x != y))
+        prev = cur
+    return float(prev[-1])
+
+
 def _has_hotword_bias(model) -> bool:
     cb = getattr(model, "context_bias", None)
     return cb is not None and hasattr(cb, "predictor_bias") and hasattr(cb, "predictor_bias_combine")
 
 
-def _hotword_setup(model, encoder_out, context_list, context_lengths):
+def _hotword_setup(model, encoder_out, context_list, context_lengths, gated: bool = False):
     """What greedy_search.py:62-70 does before its loop: phrase vectors of the given and of the
     EMPTY context list, encoder stream biased with the given one; plus K / V of the context the
     per-step predictor bias attends to (fixed for the whole call): the EMPTY list in
@@ -95,12 +119,24 @@ def _hotword_setup(model, encoder_out, context_list, context_lengths):
     prev = torch.backends.cuda.matmul.allow_tf32
     torch.backends.cuda.matmul.allow_tf32 = False
     try:
+        encoder_plain = encoder_out
         encoder_out, _ = cb.forward_encoder_bias(bias_hidden, encoder_out)
         mha = cb.predictor_bias
         given = getattr(model, "loss_mode", "pred") != "pred"
+        if gated and given:
+            raise NotImplementedError("context_filter_state='on' is implemented for loss_mode 'pred' "
+                                      "(basic_greedy_search, greedy_search.py:34-176)")
         ctx = (bias_hidden if given else bias_hidden_empty)[0].float()
         f32 = lambda t: t.detach().to(torch.float32).contiguous()
         keep = dict(k=f32(mha.linear_k(ctx)), v=f32(mha.linear_v(ctx)))
+        gate_keep = None
+        if gated:   # greedy_search.py:70 (encoder stream over the EMPTY list), :99-110 (gate inputs)
+            hw = cb.hw_bias
+            cg = bias_hidden[0].float()
+            enc_empty, _ = cb.forward_encoder_bias(bias_hidden_empty, encoder_plain)
+            gate_keep = dict(enc_proj_empty=_enc_proj(model, enc_empty),
+                             k_given=f32(mha.linear_k(cg)), v_given=f32(mha.linear_v(cg)),
+                             hk=f32(hw.linear_k(cg)), hv=f32(hw.linear_v(cg)))
     finally:
         torch.backends.cuda.matmul.allow_tf32 = prev
     pred, joint = model.predictor, model.joint
@@ -116,19 +152,35 @@ def _hotword_setup(model, encoder_out, context_list, context_lengths):
         raise NotImplementedError("predictor bias expects embedding_size == predictor output size")
     desc = _PredBias(**{n: keep[n].data_ptr() for n in keep}, P=P, Nc=keep["k"].shape[0],
                      heads=int(mha.h), ln_eps=float(cb.predictor_bias_bias_norm.eps))
-    return encoder_out, desc, keep
+    if not gated:
+        return encoder_out, desc, keep
+    hw = cb.hw_bias
+    if hw.linear_q.weight.shape != (P, P) or cb.hw_output_layer.in_features != P:
+        raise NotImplementedError("forward_hw_pred needs unified_hw_odim == predictor output size "
+                                  "(conf/encoder_bias_conformer_rnnt_4_head_bi_1_layer_pred.yaml:40,51)")
+    gnamed = dict(hq_w=hw.linear_q.weight, hq_b=hw.linear_q.bias, ho_w=hw.linear_out.weight,
+                  ho_b=hw.linear_out.bias, hln_g=cb.hw_bias_norm.weight, hln_b=cb.hw_bias_norm.bias,
+                  hout_w=cb.hw_output_layer.weight, hout_b=cb.hw_output_layer.bias)
+    gate_keep.update({n: f32(t) for n, t in gnamed.items()})
+    gdesc = _Gate(**{n: gate_keep[n].data_ptr() for n in gate_keep}, Nc_given=gate_keep["k_given"].shape[0],
+                  hw_heads=int(hw.h), n_labels=int(cb.hw_output_layer.out_features))
+    return encoder_out, desc, (keep, gate_keep, gdesc)
 
 
 @torch.no_grad()
 def greedy_search_batch(model, encoder_out: torch.Tensor, encoder_out_lens: torch.Tensor,
                         n_steps: int = 64, return_rounds: bool = False, context_list=None,
-                        context_lengths=None, hotword: bool = None):
+                        context_lengths=None, hotword: bool = None, context_filter_state: str = "off",
+                        return_decisions: bool = False):
     """Greedy RNN-T decode of a batch: encoder_out [B,T,E] -> B lists of token ids.
 
     When the model carries a real ``ContextBias`` (``model.context_bias.predictor_bias``) the
     fork's hot-word streams are applied as greedy_search.py:62-144 does with
     ``context_filter_state='off'``: the encoder stream is biased with ``context_list`` once, every
-    predictor output with the empty context inside the device loop (``hotword=False`` turns it off)."""
+    predictor output with the empty context inside the device loop (``hotword=False`` turns it off).
+    ``context_filter_state='on'`` runs the fork's default gated decode with go-back
+    (greedy_search.py:100-150); ``return_decisions`` adds the per-utterance gate decisions (the
+    reference's ``result`` list)."""
     _lib.require_cuda(encoder_out, "encoder_out")
     if encoder_out.dim() != 3:
         raise RuntimeError("encoder_out must be 3-D (batch, time, dim)")
@@ -137,22 +189,30 @@ def greedy_search_batch(model, encoder_out: torch.Tensor, encoder_out_lens: torc
     m = _model_tensors(model)
     if hotword is None:
         hotword = _has_hotword_bias(model)
-    bias_desc = None
+    gated = context_filter_state == "on"
+    if gated and not hotword:
+        raise RuntimeError("context_filter_state='on' needs a model with a ContextBias (model.context_bias)")
+    bias_desc = gate_desc = None
     if hotword:
         with torch.cuda.device(dev):
             encoder_out, bias_desc, _keep_alive = _hotword_setup(model, encoder_out, context_list,
-                                                                 context_lengths)
+                                                                 context_lengths, gated=gated)
+            if gated:
+                gate_desc = _keep_alive[2]
     with torch.cuda.device(dev):
         lens = encoder_out_lens.reshape(-1).to(device=dev, dtype=torch.int32).clamp(max=T).contiguous()
         if lens.numel() != B:
             raise RuntimeError("encoder_out_lens must have one entry per utterance")
         enc_proj = _enc_proj(model, encoder_out)
-        max_tokens = int(min(T * n_steps, 1 << 20))
+        # a go-back decrements the per-frame emission count (greedy_search.py:124): one extra symbol per frame
+        max_tokens = int(min(T * (n_steps + (1 if gated else 0)) + (8 if gated else 0), 1 << 20))
         tokens = torch.empty(B, max_tokens, dtype=torch.int32, device=dev)
         n_tok = torch.zeros(B, dtype=torch.int32, device=dev)
         L_ = _lib.lib()
         L_.b200_greedy_workspace_bytes.restype = ctypes.c_size_t
-        ws_bytes = L_.b200_greedy_workspace_bytes(B, m["V"], m["H"], m["L"], m["J"])
+        L_.b200_greedy_gated_workspace_bytes.restype = ctypes.c_size_t
+        ws_fn = L_.b200_greedy_gated_workspace_bytes if gated else L_.b200_greedy_workspace_bytes
+        ws_bytes = ws_fn(B, m["V"], m["H"], m["L"], m["J"])
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         ptrs = (ctypes.c_void_p * (4 * m["L"]))(*[t.data_ptr() for t in m["lstm"]])
         rounds = ctypes.c_int(0)
@@ -161,6 +221,16 @@ def greedy_search_batch(model, encoder_out: torch.Tensor, encoder_out_lens: torc
                       ptr(m["w_c"]), ptr(m["b_c"]), ptr(m["w_out"]), ptr(m["b_out"]), i32(m["V"]),
                       i32(m["Emb"]), i32(m["H"]), i32(m["L"]), i32(m["J"]), i32(int(model.blank)),
                       i32(n_steps), ptr(tokens), ptr(n_tok), i32(max_tokens), ptr(ws),
+                      ctypes.c_size_t(ws_bytes), ctypes.byref(rounds), _lib.stream_handle(dev))
+        elif gated:
+            max_dec = max_tokens + 1
+            decisions = torch.empty(B, max_dec, dtype=torch.int32, device=dev)
+            n_dec = torch.zeros(B, dtype=torch.int32, device=dev)
+            _lib.call("b200_rnnt_greedy_gated", ptr(enc_proj), ptr(lens), i32(B), i32(T), ptr(m["embed"]),
+                      ptrs, ptr(m["w_out"]), ptr(m["b_out"]), i32(m["V"]), i32(m["Emb"]), i32(m["H"]),
+                      i32(m["L"]), i32(m["J"]), i32(int(model.blank)), i32(n_steps),
+                      ctypes.byref(bias_desc), ctypes.byref(gate_desc), ptr(tokens), ptr(n_tok),
+                      i32(max_tokens), ptr(decisions), ptr(n_dec), i32(max_dec), ptr(ws),
                       ctypes.c_size_t(ws_bytes), ctypes.byref(rounds), _lib.stream_handle(dev))
         else:
             _lib.call("b200_rnnt_greedy_bias", ptr(enc_proj), ptr(lens), i32(B), i32(T), ptr(m["embed"]),
@@ -171,21 +241,42 @@ def greedy_search_batch(model, encoder_out: torch.Tensor, encoder_out_lens: torc
         n_host = n_tok.cpu().tolist()  # one D2H copy of the results at the end
         width = max(n_host) if n_host else 0
         tok_host = tokens[:, :max(width, 1)].cpu().tolist()
+        dec_host = None
+        if gated and return_decisions:
+            nd = n_dec.cpu().tolist()
+            dh = decisions[:, :max(max(nd), 1)].cpu().tolist()
+            dec_host = [dh[b][:nd[b]] for b in range(B)]
     hyps = [tok_host[b][:min(n_host[b], max_tokens)] for b in range(B)]
-    return (hyps, rounds.value) if return_rounds else hyps
+    out = (hyps,)
+    if return_decisions:
+        out += (dec_host if dec_host is not None else [[1] * (len(h) + 1) for h in hyps],)
+    if return_rounds:
+        out += (rounds.value,)
+    return out if len(out) > 1 else hyps
 
 
 def basic_greedy_search(model, encoder_out: torch.Tensor, encoder_out_lens, context_list=None,
                         context_lengths=None, n_steps: int = 64, context_filter_state: str = "off",
                         context_decoder_labels_padded=None) -> List[List[int]]:
-    """Single-utterance entry point with the reference's argument order; returns ``[hyps]``."""
-    if context_filter_state == "on":
-        raise NotImplementedError("hot-word gated decoding (greedy_search.py:100-144) is out of scope")
+    """Single-utterance entry point with the reference's argument order.  Returns ``[hyps]`` (the
+    upstream shape, "greedy_search copy.py":63); with ``context_decoder_labels_padded`` given it
+    returns the fork's triple ``([hyps], dist, result)`` (greedy_search.py:174-176): ``result`` =
+    the gate decisions, ``dist`` = their edit distance to the labels."""
+    if context_filter_state not in ("on", "off"):
+        raise ValueError("context_filter_state must be 'on' or 'off'")
     if encoder_out.size(0) != 1:
         raise RuntimeError("basic_greedy_search takes one utterance; use greedy_search_batch")
     lens = torch.as_tensor(encoder_out_lens).reshape(-1)[:1]
-    return [greedy_search_batch(model, encoder_out, lens, n_steps=n_steps, context_list=context_list,
-                                context_lengths=context_lengths)[0]]
+    if context_filter_state == "off" and context_decoder_labels_padded is None:
+        return [greedy_search_batch(model, encoder_out, lens, n_steps=n_steps, context_list=context_list,
+                                    context_lengths=context_lengths)[0]]
+    hyps, decisions = greedy_search_batch(model, encoder_out, lens, n_steps=n_steps,
+                                          context_list=context_list, context_lengths=context_lengths,
+                                          context_filter_state=context_filter_state, return_decisions=True)
+    if context_decoder_labels_padded is None:
+        return [hyps[0]]
+    labels = torch.as_tensor(context_decoder_labels_padded).reshape(-1).tolist()
+    return [hyps[0]], edit_distance(labels, decisions[0]), decisions[0]
 
 
 # --------------------------------------------------------------------------- prefix beam search

@@ -121,11 +121,12 @@ def transducer_greedy_search(self, speech: torch.Tensor, speech_lengths: torch.T
     encoder_out, encoder_mask = self.encoder(speech, speech_lengths, decoding_chunk_size,
                                              num_decoding_left_chunks)
     encoder_out_lens = encoder_mask.squeeze(1).sum(1)
-    if _unused.get("context_filter_state", "off") == "on":
-        raise NotImplementedError("hot-word gated decoding (greedy_search.py:100-131) is not implemented")
+    # the reference defaults to the gated decode (transducer.py:525); here the gate is opt-in so that
+    # models without a ContextBias keep decoding with the upstream algorithm
     return greedy_search_batch(self, encoder_out, encoder_out_lens, n_steps=n_steps,
                                context_list=_unused.get("context_list"),
-                               context_lengths=_unused.get("context_lengths"))
+                               context_lengths=_unused.get("context_lengths"),
+                               context_filter_state=_unused.get("context_filter_state", "off"))
 
 
 @torch.no_grad()
