@@ -223,21 +223,29 @@ int b200_rnnt_greedy_bias(const float* enc_proj, const int32_t* lens, int B, int
 /* greedy search with the fork's hot-word GATE and "go-back" - context_filter_state='on', the
  * default of Transducer.greedy_search (wenet/transducer/transducer.py:525) and of
  * wenet/bin/recognize.py:139-141; loop at wenet/transducer/search/greedy_search.py:88-165.
- * Per predictor call: gate = argmax ContextBias.forward_hw_pred (wenet/transformer/
- * context_bias.py:382-387) of the predictor output biased with the GIVEN phrase list; decision 0
- * (predictor stream biased with the given list, joint over the encoder stream biased with the
- * EMPTY list), decision 1 (the other way round: bias->k / bias->v hold the EMPTY list), or a
- * go-back (:116-131) that drops the last decision and token, rewinds the frame index and re-runs
- * the previous predictor call with decisions forced to 1.  `enc_proj` = enc_ffn of the encoder
- * stream biased with the given list, gate->enc_proj_empty = the same over the empty list.
- * K / V tensors are linear_k / linear_v of the respective attention applied to the phrase
- * vectors [Nc,P]; hw_output_layer is [n_labels,P] (unified_hw_odim == P).  Outputs as
- * b200_rnnt_greedy plus decisions [B,max_dec] / n_dec [B] = the reference's `result` list. */
+ * Per predictor call a gate decides 0 / 1, or a go-back (:116-131) that drops the last decision
+ * and token, rewinds the frame index and re-runs the previous predictor call with decisions
+ * forced to 1.  Decision 1 joins the encoder stream biased with the given phrase list
+ * (`enc_proj`), decision 0 the one biased with the EMPTY list (gate->enc_proj_empty); the
+ * predictor stream is biased with bias->k / bias->v on decision 1, gate->k0 / v0 on decision 0.
+ *  loss_mode 'pred' (basic_greedy_search, :34-176): gate = argmax ContextBias.forward_hw_pred
+ *    (wenet/transformer/context_bias.py:382-387) of the predictor output biased with the given
+ *    list (= k0 / v0; bias->k / v hold the EMPTY list); gate_frames = NULL, hw head weights
+ *    given: hw_bias.linear_q / linear_out, hk / hv = its linear_k / linear_v over the given
+ *    phrase vectors [Nc_hw,P], hw_bias_norm, hw_output_layer [n_labels,P] (unified_hw_odim == P).
+ *  loss_mode 'both' (basic_greedy_search_both, :297-430): gate = forward_hw_pred_both
+ *    (context_bias.py:388-394), whose attention has a single key (the frame's encoder bias) and
+ *    therefore depends on the frame only: gate_frames [B,T] int32 holds it; bias->k / v = given
+ *    list, k0 / v0 = EMPTY list (:399-400); hw head pointers unused.
+ * K / V tensors are linear_k / linear_v of the attention applied to the phrase vectors [Nc,P].
+ * Outputs as b200_rnnt_greedy plus decisions [B,max_dec] / n_dec [B] = the reference's
+ * `result` list. */
 typedef struct {
   const float* enc_proj_empty;
-  const float *k_given, *v_given;
+  const float *k0, *v0;
   const float *hq_w, *hq_b, *hk, *hv, *ho_w, *ho_b, *hln_g, *hln_b, *hout_w, *hout_b;
-  int Nc_given, hw_heads, n_labels;
+  const int32_t* gate_frames;
+  int Nc0, Nc_hw, hw_heads, n_labels;
 } b200_gate_t;
 size_t b200_greedy_gated_workspace_bytes(int B, int V, int H, int L, int J);
 int b200_rnnt_greedy_gated(const float* enc_proj, const int32_t* lens, int B, int T,

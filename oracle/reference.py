@@ -424,9 +424,26 @@ def hw_pred_gate(cb, ctx: torch.Tensor, y: torch.Tensor) -> int:
 
 
 @torch.no_grad()
+def hw_pred_both_gate(cb, enc_bias_frame: torch.Tensor) -> int:
+    """ContextBias.forward_hw_pred_both (wenet/transformer/context_bias.py:388-394) + ``topk(1)``
+    index as basic_greedy_search_both uses it (greedy_search.py:360-366): the attention
+    ``hw_bias(h_dec, h_enc, h_enc)`` has ONE key / value (``h_enc = hw_output_layer_enc(encoder bias
+    of the frame)``, [1,1,D]); a softmax over one score is exactly 1, so the attention output is
+    ``linear_out(linear_v(h_enc))`` whatever the predictor-side query is."""
+    import torch.nn.functional as F
+    mha = cb.hw_bias
+    h_enc = F.linear(enc_bias_frame, cb.hw_output_layer_enc.weight, cb.hw_output_layer_enc.bias)
+    a = F.linear(F.linear(h_enc, mha.linear_v.weight, mha.linear_v.bias), mha.linear_out.weight, mha.linear_out.bias)
+    D = a.size(-1)
+    a = F.layer_norm(a, (D,), cb.hw_bias_norm.weight, cb.hw_bias_norm.bias, cb.hw_bias_norm.eps)
+    out = F.linear(a, cb.hw_output_layer.weight, cb.hw_output_layer.bias).reshape(-1)
+    return int(out.topk(1)[1].item())
+
+
+@torch.no_grad()
 def greedy_search_hotword_gated(model, enc_biased: torch.Tensor, enc_empty: torch.Tensor, enc_len: int,
                                 bias_hidden: torch.Tensor, bias_hidden_empty: torch.Tensor,
-                                n_steps: int = 64):
+                                n_steps: int = 64, enc_bias: torch.Tensor = None):
     """The fork's DEFAULT greedy search, ``context_filter_state='on'``
     (wenet/transducer/search/greedy_search.py:88-165; default at transducer.py:525 and
     wenet/bin/recognize.py:139-141), restated as a state machine without the reference's
@@ -442,7 +459,13 @@ def greedy_search_hotword_gated(model, enc_biased: torch.Tensor, enc_empty: torc
     given list; decision 0: predictor stream biased with the given list, encoder stream biased
     with the empty list (:140-150).  Only the previous call is ever restored (two go-backs need
     a decision-0 call between them), so three LSTM states suffice: before the previous call,
-    before this call, after this call.  Returns (hyp, decisions)."""
+    before this call, after this call.  Returns (hyp, decisions).
+
+    With ``enc_bias`` (the second output of forward_encoder_bias, [1,T,E]) the loop is
+    ``basic_greedy_search_both`` (loss_mode 'both', greedy_search.py:339-407) instead: the gate is
+    forward_hw_pred_both of the frame's encoder bias (:360), and decision 1 keeps the GIVEN list on
+    the predictor stream while decision 0 takes the EMPTY one (:358,399-400)."""
+    both = enc_bias is not None
     dev = enc_biased.device
     blank = model.blank
     cb = model.context_bias
@@ -462,7 +485,8 @@ def greedy_search_hotword_gated(model, enc_biased: torch.Tensor, enc_empty: torc
         if need_predictor:
             raw, pending_state = model.predictor.forward_step(token, pad, state)
             y_given = predictor_bias(cb, bias_hidden, raw)
-            gate = hw_pred_gate(cb, bias_hidden, y_given)
+            gate = (hw_pred_both_gate(cb, enc_bias[:, t:t + 1, :]) if both
+                    else hw_pred_gate(cb, bias_hidden, y_given))
             if not going_back:
                 if gate == 0:
                     result.append(0)
@@ -481,7 +505,10 @@ def greedy_search_hotword_gated(model, enc_biased: torch.Tensor, enc_empty: torc
                 if t >= go_back_end:
                     going_back = False
             prev_call = (token, state)
-            pred_step = predictor_bias(cb, bias_hidden_empty, raw) if result[-1] == 1 else y_given
+            if both:
+                pred_step = y_given if result[-1] == 1 else predictor_bias(cb, bias_hidden_empty, raw)
+            else:
+                pred_step = predictor_bias(cb, bias_hidden_empty, raw) if result[-1] == 1 else y_given
         enc = enc_biased if result[-1] == 1 else enc_empty
         logp = joint_logits(enc[:, t:t + 1, :], pred_step, model.joint).log_softmax(dim=-1)
         k = int(logp.reshape(-1).argmax())

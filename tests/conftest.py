@@ -77,11 +77,14 @@ class HotwordBiasStandIn(torch.nn.Module):
         self.predictor_bias_combine = torch.nn.Linear(2 * P, P)
         self.predictor_bias_out_norm = torch.nn.LayerNorm(P)
         keys = ("cb.predictor_bias",)
-        if "enc_empty" in d.files:   # gated fixture: ContextBias.forward_hw_pred modules (context_bias.py:382-387)
-            self.hw_bias = _Mha(int(d["heads"]), P)
-            self.hw_bias_norm = torch.nn.LayerNorm(P)
-            self.hw_output_layer = torch.nn.Linear(P, int(d["cb.hw_output_layer.weight"].shape[0]))
-            keys += ("cb.hw_bias.", "cb.hw_bias_norm.", "cb.hw_output_layer.")
+        if "enc_empty" in d.files:   # gated fixture: ContextBias.forward_hw_pred* modules (context_bias.py:382-394)
+            n_lab, D = d["cb.hw_output_layer.weight"].shape
+            self.hw_bias = _Mha(int(d["heads"]), int(D))
+            self.hw_bias_norm = torch.nn.LayerNorm(int(D))
+            self.hw_output_layer = torch.nn.Linear(int(D), int(n_lab))
+            self.hw_output_layer_enc = torch.nn.Linear(P, int(D))
+            self.hw_output_layer_dec = torch.nn.Linear(P, int(D))
+            keys += ("cb.hw_bias.", "cb.hw_bias_norm.", "cb.hw_output_layer")
         sd = {k[3:]: torch.from_numpy(d[k]) for k in d.files if k.startswith(keys)}
         self.load_state_dict(sd, strict=True)
         self.register_buffer("bias_hidden", torch.from_numpy(d["bias_hidden"]))
@@ -90,6 +93,7 @@ class HotwordBiasStandIn(torch.nn.Module):
         self.register_buffer("enc_biased", torch.from_numpy(d["enc_biased"]))
         if "enc_empty" in d.files:
             self.register_buffer("enc_empty", torch.from_numpy(d["enc_empty"]))
+            self.register_buffer("enc_bias", torch.from_numpy(d["enc_bias"]))
 
     def forward_bias_hidden(self, context_list, context_lengths):
         return self.bias_hidden_empty if context_list.numel() == 1 else self.bias_hidden
@@ -99,7 +103,15 @@ class HotwordBiasStandIn(torch.nn.Module):
         if bias_hidden is self.bias_hidden_empty:
             return self.enc_empty, None
         assert bias_hidden is self.bias_hidden
-        return self.enc_biased, None
+        return self.enc_biased, getattr(self, "enc_bias", None)
+
+    def forward_hw_pred_both(self, h_enc_bias, h_dec_bias):
+        """context_bias.py:388-394 for [N,1,E] inputs: one key per query, the attention weight is 1."""
+        F = torch.nn.functional
+        assert h_enc_bias.size(1) == 1
+        h_enc = self.hw_output_layer_enc(h_enc_bias)
+        a = self.hw_bias.linear_out(self.hw_bias.linear_v(h_enc))
+        return self.hw_output_layer(self.hw_bias_norm(a))
 
 
 def load_hotword_model(d):

@@ -1,6 +1,7 @@
 """CPU: the oracle (oracle/reference.py, oracle/lattice_ref.c) against the golden
 fixtures that oracle/gen_golden.py produced by running the real reference modules."""
 import numpy as np
+import pytest
 import torch
 import torchaudio
 
@@ -188,11 +189,13 @@ def test_hotword_greedy_matches_reference(golden):
         assert got == [int(x) for x in d["hyps_both"][b] if x >= 0], ("both", b)
 
 
-def test_hotword_gated_greedy_matches_reference(golden):
-    """the fork's DEFAULT greedy (context_filter_state='on', greedy_search.py:88-165): gate decisions,
-    go-back, token lists and edit distance recorded from the real basic_greedy_search."""
+@pytest.mark.parametrize("mode", ["pred", "both"])
+def test_hotword_gated_greedy_matches_reference(golden, mode):
+    """the fork's DEFAULT greedy (context_filter_state='on', greedy_search.py:88-165 for loss_mode
+    'pred', :339-407 for 'both'): gate decisions, go-back, token lists and edit distance recorded
+    from the real basic_greedy_search / basic_greedy_search_both."""
     from conftest import load_hotword_model
-    d = golden("hotword_greedy_gated")
+    d = golden("hotword_greedy_gated" if mode == "pred" else "hotword_greedy_gated_both")
     m = load_hotword_model(d)
     cb = m.context_bias
     assert int(d["go_backs"]) >= 3
@@ -201,7 +204,8 @@ def test_hotword_gated_greedy_matches_reference(golden):
         n = int(d["lens"][b])
         hyp, res = orc.greedy_search_hotword_gated(m, cb.enc_biased[b:b + 1, :n], cb.enc_empty[b:b + 1, :n], n,
                                                    cb.bias_hidden, cb.bias_hidden_empty,
-                                                   n_steps=int(d["n_steps"]))
+                                                   n_steps=int(d["n_steps"]),
+                                                   enc_bias=None if mode == "pred" else cb.enc_bias[b:b + 1, :n])
         assert hyp == [int(x) for x in d["hyps"][b] if x >= 0], b
         assert res == [int(x) for x in d["decisions"][b] if x >= 0], b
         assert orc.edit_distance(labels, res) == float(d["dist"][b])

@@ -132,14 +132,17 @@ def test_hotword_greedy_golden(golden):
     assert plain != hyps
 
 
-def test_hotword_gated_greedy_golden(golden):
-    """the fork's DEFAULT decode (context_filter_state='on', greedy_search.py:88-165): hot-word gate
-    per predictor call, decision-dependent streams and the go-back re-decode on the device; token
-    lists, gate decisions and edit distance of the real basic_greedy_search (46 go-backs in the fixture)."""
+@pytest.mark.parametrize("mode", ["pred", "both"])
+def test_hotword_gated_greedy_golden(golden, mode):
+    """the fork's DEFAULT decode (context_filter_state='on', greedy_search.py:88-165; loss_mode 'both':
+    basic_greedy_search_both, :339-407): hot-word gate per predictor call, decision-dependent streams
+    and the go-back re-decode on the device; token lists, gate decisions and edit distance of the real
+    reference functions (46 / 48 go-backs in the fixtures)."""
     from conftest import load_hotword_model
     from wenet_celoss_b200 import basic_greedy_search, greedy_search_batch
-    d = golden("hotword_greedy_gated")
+    d = golden("hotword_greedy_gated" if mode == "pred" else "hotword_greedy_gated_both")
     m = load_hotword_model(d).to(DEV)
+    m.loss_mode = mode
     enc = torch.from_numpy(d["enc"]).to(DEV)
     lens = torch.from_numpy(d["lens"]).to(DEV)
     ctx = torch.from_numpy(d["context_list"]).to(DEV)
@@ -159,9 +162,22 @@ def test_hotword_gated_greedy_golden(golden):
     b = int(np.argmax(d["lens"]))
     assert int(d["lens"][b]) == enc.size(1)
     m1 = load_hotword_model(d).to(DEV)
+    m1.loss_mode = mode
     cb = m1.context_bias
     cb.enc, cb.enc_biased, cb.enc_empty = cb.enc[b:b + 1], cb.enc_biased[b:b + 1], cb.enc_empty[b:b + 1]
+    cb.enc_bias = cb.enc_bias[b:b + 1]
     out = basic_greedy_search(m1, enc[b:b + 1], lens[b:b + 1], ctx, ctx_len, n_steps, "on",
                               torch.from_numpy(d["labels"]))
     assert out[0] == [_unpad(d["hyps"][b])] and out[1] == float(d["dist"][b])
     assert out[2] == _unpad(d["decisions"][b])
+    # through the patched model entry point (Transducer.greedy_search, transducer.py:515-598): (hyps, dist)
+    from wenet_celoss_b200.transducer import transducer_greedy_search
+
+    class Enc(torch.nn.Module):
+        def forward(self, xs, xl, chunk=-1, left=-1):
+            return xs, torch.ones(xs.size(0), 1, xs.size(1), dtype=torch.bool, device=xs.device)
+    m1.encoder = Enc()
+    hy, dist = transducer_greedy_search(m1, enc[b:b + 1], lens[b:b + 1], n_steps=n_steps, context_list=ctx,
+                                        context_lengths=ctx_len, context_filter_state="on",
+                                        context_decoder_labels_padded=torch.from_numpy(d["labels"]))
+    assert hy == [_unpad(d["hyps"][b])] and dist == float(d["dist"][b])

@@ -77,9 +77,10 @@ class _PredBias(ctypes.Structure):
 class _Gate(ctypes.Structure):
     """b200_gate_t (include/b200_transducer.h)."""
     _fields_ = ([(n, ctypes.c_void_p) for n in
-                 ("enc_proj_empty", "k_given", "v_given", "hq_w", "hq_b", "hk", "hv", "ho_w", "ho_b",
-                  "hln_g", "hln_b", "hout_w", "hout_b")] +
-                [("Nc_given", ctypes.c_int), ("hw_heads", ctypes.c_int), ("n_labels", ctypes.c_int)])
+                 ("enc_proj_empty", "k0", "v0", "hq_w", "hq_b", "hk", "hv", "ho_w", "ho_b",
+                  "hln_g", "hln_b", "hout_w", "hout_b", "gate_frames")] +
+                [("Nc0", ctypes.c_int), ("Nc_hw", ctypes.c_int), ("hw_heads", ctypes.c_int),
+                 ("n_labels", ctypes.c_int)])
 
 
 def edit_distance(a, b) -> float:
@@ -120,23 +121,31 @@ def _hotword_setup(model, encoder_out, context_list, context_lengths, gated: boo
     torch.backends.cuda.matmul.allow_tf32 = False
     try:
         encoder_plain = encoder_out
-        encoder_out, _ = cb.forward_encoder_bias(bias_hidden, encoder_out)
+        encoder_out, encoder_out_bias = cb.forward_encoder_bias(bias_hidden, encoder_out)
         mha = cb.predictor_bias
         given = getattr(model, "loss_mode", "pred") != "pred"
-        if gated and given:
-            raise NotImplementedError("context_filter_state='on' is implemented for loss_mode 'pred' "
-                                      "(basic_greedy_search, greedy_search.py:34-176)")
         ctx = (bias_hidden if given else bias_hidden_empty)[0].float()
         f32 = lambda t: t.detach().to(torch.float32).contiguous()
         keep = dict(k=f32(mha.linear_k(ctx)), v=f32(mha.linear_v(ctx)))
         gate_keep = None
-        if gated:   # greedy_search.py:70 (encoder stream over the EMPTY list), :99-110 (gate inputs)
-            hw = cb.hw_bias
-            cg = bias_hidden[0].float()
+        if gated:   # greedy_search.py:70 / :338 (encoder stream over the EMPTY list)
             enc_empty, _ = cb.forward_encoder_bias(bias_hidden_empty, encoder_plain)
+            # decision 0 takes the OTHER phrase list on the predictor stream (:140-144 / :399-400)
+            c0 = (bias_hidden_empty if given else bias_hidden)[0].float()
             gate_keep = dict(enc_proj_empty=_enc_proj(model, enc_empty),
-                             k_given=f32(mha.linear_k(cg)), v_given=f32(mha.linear_v(cg)),
-                             hk=f32(hw.linear_k(cg)), hv=f32(hw.linear_v(cg)))
+                             k0=f32(mha.linear_k(c0)), v0=f32(mha.linear_v(c0)))
+            if given:
+                # forward_hw_pred_both (:360, context_bias.py:388-394) attends over ONE key, the frame's
+                # encoder bias: its softmax is 1 and the gate is a function of the frame alone, so the
+                # module runs once over all frames (library call) and the loop reads a table
+                Bq, Tq, Eq = encoder_out_bias.shape
+                frames = encoder_out_bias.reshape(Bq * Tq, 1, Eq)
+                hw_out = cb.forward_hw_pred_both(frames, torch.zeros_like(frames))
+                gate_keep["gate_frames"] = hw_out.reshape(Bq, Tq, -1).argmax(-1).to(torch.int32).contiguous()
+            else:   # :99-110: gate head over the predictor output, inside the device loop
+                hw = cb.hw_bias
+                cg = bias_hidden[0].float()
+                gate_keep.update(hk=f32(hw.linear_k(cg)), hv=f32(hw.linear_v(cg)))
     finally:
         torch.backends.cuda.matmul.allow_tf32 = prev
     pred, joint = model.predictor, model.joint
@@ -155,14 +164,16 @@ def _hotword_setup(model, encoder_out, context_list, context_lengths, gated: boo
     if not gated:
         return encoder_out, desc, keep
     hw = cb.hw_bias
-    if hw.linear_q.weight.shape != (P, P) or cb.hw_output_layer.in_features != P:
-        raise NotImplementedError("forward_hw_pred needs unified_hw_odim == predictor output size "
-                                  "(conf/encoder_bias_conformer_rnnt_4_head_bi_1_layer_pred.yaml:40,51)")
-    gnamed = dict(hq_w=hw.linear_q.weight, hq_b=hw.linear_q.bias, ho_w=hw.linear_out.weight,
-                  ho_b=hw.linear_out.bias, hln_g=cb.hw_bias_norm.weight, hln_b=cb.hw_bias_norm.bias,
-                  hout_w=cb.hw_output_layer.weight, hout_b=cb.hw_output_layer.bias)
-    gate_keep.update({n: f32(t) for n, t in gnamed.items()})
-    gdesc = _Gate(**{n: gate_keep[n].data_ptr() for n in gate_keep}, Nc_given=gate_keep["k_given"].shape[0],
+    if "gate_frames" not in gate_keep:
+        if hw.linear_q.weight.shape != (P, P) or cb.hw_output_layer.in_features != P:
+            raise NotImplementedError("forward_hw_pred needs unified_hw_odim == predictor output size "
+                                      "(conf/encoder_bias_conformer_rnnt_4_head_bi_1_layer_pred.yaml:40,51)")
+        gnamed = dict(hq_w=hw.linear_q.weight, hq_b=hw.linear_q.bias, ho_w=hw.linear_out.weight,
+                      ho_b=hw.linear_out.bias, hln_g=cb.hw_bias_norm.weight, hln_b=cb.hw_bias_norm.bias,
+                      hout_w=cb.hw_output_layer.weight, hout_b=cb.hw_output_layer.bias)
+        gate_keep.update({n: f32(t) for n, t in gnamed.items()})
+    gdesc = _Gate(**{n: gate_keep[n].data_ptr() for n in gate_keep}, Nc0=gate_keep["k0"].shape[0],
+                  Nc_hw=gate_keep["hk"].shape[0] if "hk" in gate_keep else 0,
                   hw_heads=int(hw.h), n_labels=int(cb.hw_output_layer.out_features))
     return encoder_out, desc, (keep, gate_keep, gdesc)
 

@@ -123,10 +123,24 @@ def transducer_greedy_search(self, speech: torch.Tensor, speech_lengths: torch.T
     encoder_out_lens = encoder_mask.squeeze(1).sum(1)
     # the reference defaults to the gated decode (transducer.py:525); here the gate is opt-in so that
     # models without a ContextBias keep decoding with the upstream algorithm
-    return greedy_search_batch(self, encoder_out, encoder_out_lens, n_steps=n_steps,
-                               context_list=_unused.get("context_list"),
-                               context_lengths=_unused.get("context_lengths"),
-                               context_filter_state=_unused.get("context_filter_state", "off"))
+    labels = _unused.get("context_decoder_labels_padded")
+    out = greedy_search_batch(self, encoder_out, encoder_out_lens, n_steps=n_steps,
+                              context_list=_unused.get("context_list"),
+                              context_lengths=_unused.get("context_lengths"),
+                              context_filter_state=_unused.get("context_filter_state", "off"),
+                              return_decisions=labels is not None)
+    if labels is None:
+        return out
+    # the fork's return shape (transducer.py:598, recognize.py:278-290): (hyps, dist), dist = edit
+    # distance between the hot-word labels and the gate decisions (greedy_search.py:174); a batch
+    # returns one distance per utterance
+    from .search import edit_distance
+    hyps, decisions = out
+    lab_t = torch.as_tensor(labels)
+    per_utt = lab_t.dim() > 1 and lab_t.size(0) == len(hyps)
+    lab = lab_t.reshape(len(hyps), -1).tolist() if per_utt else [lab_t.reshape(-1).tolist()] * len(hyps)
+    dist = [edit_distance(lab[b], decisions[b]) for b in range(len(hyps))]
+    return hyps, (dist[0] if len(dist) == 1 else dist)
 
 
 @torch.no_grad()
