@@ -500,6 +500,51 @@ class _SearchModel(torch.nn.Module):
             self.predictor.embed.weight.mul_(4.0)
 
 
+class _Mha(torch.nn.Module):
+    """MultiHeadedAttention parameter layout (wenet/transformer/attention.py:35-46)."""
+
+    def __init__(self, heads, dim):
+        super().__init__()
+        self.h = heads
+        self.linear_q, self.linear_k = torch.nn.Linear(dim, dim), torch.nn.Linear(dim, dim)
+        self.linear_v, self.linear_out = torch.nn.Linear(dim, dim), torch.nn.Linear(dim, dim)
+
+    def forward(self, q, k, v):
+        B, Tq, D = q.shape
+        dk = D // self.h
+        sp = lambda x, lin: lin(x).view(x.size(0), -1, self.h, dk).transpose(1, 2)
+        att = torch.softmax(sp(q, self.linear_q) @ sp(k, self.linear_k).transpose(-2, -1) / dk ** 0.5, -1)
+        return self.linear_out((att @ sp(v, self.linear_v)).transpose(1, 2).reshape(B, Tq, D)), None
+
+
+class _ContextBias(torch.nn.Module):
+    """The slice of ContextBias (wenet/transformer/context_bias.py:159-399) the greedy search reads,
+    random-init, dims of conf/encoder_bias_conformer_rnnt_4_head_bi_1_layer_pred.yaml (256, 4 heads,
+    unified_hw_odim 256); the phrase vectors stand in for the BLSTM extractor's output."""
+
+    def __init__(self, D, n_phrases, heads=4):
+        super().__init__()
+        self.encoder_bias, self.predictor_bias, self.hw_bias = _Mha(heads, D), _Mha(heads, D), _Mha(heads, D)
+        LN, Lin = torch.nn.LayerNorm, torch.nn.Linear
+        self.encoder_bias_combine, self.predictor_bias_combine = Lin(2 * D, D), Lin(2 * D, D)
+        self.encdoer_bias_bias_norm, self.encdoer_bias_out_norm = LN(D), LN(D)
+        self.predictor_bias_bias_norm, self.predictor_bias_out_norm = LN(D), LN(D)
+        self.hw_bias_norm, self.hw_output_layer = LN(D), Lin(D, 2)
+        self.register_buffer("phrases", torch.randn(1, n_phrases, D))
+        with torch.no_grad():   # LayerNorm outputs are unit scale: restore the stream scales of _SearchModel
+            self.hw_output_layer.weight.mul_(20.0)
+            self.predictor_bias_out_norm.weight.mul_(24.0)
+            self.encdoer_bias_out_norm.weight.mul_(2.0)
+
+    def forward_bias_hidden(self, context_list, context_lengths):
+        return self.phrases[:, :1] if context_list.numel() == 1 else self.phrases
+
+    def forward_encoder_bias(self, bias_hidden, encoder_out):
+        bh = bias_hidden.expand(encoder_out.shape[0], -1, -1)
+        a = self.encdoer_bias_bias_norm(self.encoder_bias(encoder_out, bh, bh)[0])
+        return self.encdoer_bias_out_norm(self.encoder_bias_combine(torch.cat([encoder_out, a], -1))), a
+
+
 def extra_rows(cfg, dev, pk):
     """Secondary numbers of the same hot path (BASELINE configs 4 and 5), timed with CUDA events."""
     import wenet_celoss_b200 as pkg
@@ -530,6 +575,25 @@ def extra_rows(cfg, dev, pk):
     out["greedy"] = {"value": B4 / (ms * 1e-3), "unit": "utt/s", "ms": ms, "rounds": rounds,
                      "symbols_per_frame": ntok / (B4 * T4),
                      "workload": "cfg4: B=64 T=500 V=5000 greedy, random-init predictor/joint"}
+    # the fork's default decode: hot-word gate + go-back (context_filter_state='on'), 100 phrases
+    model.context_bias = _ContextBias(cfg["P"], 100).to(dev).eval()
+    with torch.no_grad():   # ~0.3 symbols per frame on the biased streams (tuned with the CPU oracle)
+        model.joint.ffn_out.bias[0] -= 2.0
+    ctx_list = torch.zeros(100, 4, dtype=torch.int32, device=dev)
+    ctx_len = torch.full((100,), 4, dtype=torch.int32, device=dev)
+    ms, (hyps_g, dec_g, rounds_g) = timed(lambda: pkg.greedy_search_batch(
+        model, enc, lens, n_steps=64, context_list=ctx_list, context_lengths=ctx_len,
+        context_filter_state="on", return_decisions=True, return_rounds=True), reps=2)
+    n0 = sum(d.count(0) for d in dec_g)
+    out["greedy_hotword_gated"] = {
+        "value": B4 / (ms * 1e-3), "unit": "utt/s", "ms": ms, "rounds": rounds_g,
+        "symbols_per_frame": sum(len(h) for h in hyps_g) / (B4 * T4),
+        "decisions": sum(len(d) for d in dec_g), "decision0_share": n0 / max(1, sum(len(d) for d in dec_g)),
+        "workload": "cfg4 shape, context_filter_state='on' (the fork's default greedy): 100 phrase vectors, "
+                    "gate head + predictor bias per predictor call, go-back re-decodes; per-round kernels"}
+    del model.context_bias
+    with torch.no_grad():
+        model.joint.ffn_out.bias[0] += 2.0
     ms, beams = timed(lambda: pkg.prefix_beam_search_batch(model, enc, lens, beam_size=10), reps=2)
     out["beam10"] = {"value": B4 / (ms * 1e-3), "unit": "utt/s", "ms": ms,
                      "workload": "cfg4: B=64 T=500 V=5000 prefix beam search, beam=10, ctc 0.3 / rnnt 0.7"}
