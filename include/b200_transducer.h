@@ -154,6 +154,16 @@ int b200_joint_fwd(const float* e, const float* p, const void* w_bf16, const flo
                    float* lse, float* lp_blank, float* lp_emit, const float* logit_bound,
                    int max_ctas, b200_stream_t stream);
 
+/* training forward: as b200_joint_fwd, and the A-tile builders also store H = tanh(e + p)
+ * (bf16, [B*T*U1, ldh], ldh >= J, ldh % 8 == 0) through TMA, so that the backward pass
+ * (b200_joint_grad_chunk_h, b200_joint_dw, b200_joint_dz_reduce) does not rebuild it.  H NULL =
+ * b200_joint_fwd. */
+int b200_joint_fwd_h(const float* e, const float* p, const void* w_bf16, const float* bias_pad,
+                     const int32_t* targets, const int32_t* logit_len, const int32_t* target_len,
+                     int B, int T, int U1, int V, int J, int blank,
+                     float* lse, float* lp_blank, float* lp_emit, const float* logit_bound,
+                     void* H, int ldh, int max_ctas, b200_stream_t stream);
+
 /* backward, one chunk of cells [cell0, cell0+ncells) (cell = (b*T+t)*U1+u): recompute the
  * logits tile and write G = d loss / d logits (bf16, [ncells, ldg], ldg % 16 == 0) from the
  * coefficients of b200_rnnt_grad_coef.  H [ncells, ldh] bf16 (ldh >= J, ldh % 8 == 0) is a
@@ -167,6 +177,15 @@ int b200_joint_grad_chunk(const float* e, const float* p, const void* w_bf16,
                           long long cell0, long long ncells,
                           void* G, int ldg, void* H, int ldh, float* db_part,
                           int max_ctas, b200_stream_t stream);
+
+/* the same with H READY: H points at the chunk's first row of the scratch b200_joint_fwd_h
+ * filled (row cell0 of the whole-lattice H); no tanh is recomputed. */
+int b200_joint_grad_chunk_h(const float* e, const float* p, const void* w_bf16,
+                            const float* bias_pad, const int32_t* targets, const float* coef,
+                            int B, int T, int U1, int V, int J, int blank,
+                            long long cell0, long long ncells,
+                            void* G, int ldg, const void* H, int ldh, float* db_part,
+                            int max_ctas, b200_stream_t stream);
 
 /* backward tail: dZ = dH * (1 - H^2), d e[b,t,:] = sum_u dZ, d p[b,u,:] += sum_t dZ
  * (autograd through joint.py:58-68) for nb whole utterances: dH [nb*T*U1, J] fp32,

@@ -309,8 +309,17 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
     const int bw = warp - kBuilderWarp0;  // rows bw*32 .. bw*32+31
     const int rr = lane >> 3;             // row within a group of 4
     const int cc = lane & 7;              // 16-byte chunk within the 128-byte swizzle row
+    // With P.H set (training forward) every finished [32 rows x 64 k] piece also leaves as a TMA
+    // store into the bf16 H scratch: the backward pass reads H instead of recomputing tanh(e + p)
+    // in a kernel of its own (joint_h_kernel: 0.7 ms per cfg3 step).
+    const bool save_h = P.H != nullptr;
+    const uint64_t hs_policy = ptx::l2_policy_evict_first();
     int it = 0;  // slot = pair index kp (the staging holds a whole tile), phase = tile parity
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      if (save_h && it > 0) {  // the previous tile's H stores must have read the staging area
+        if (lane == 0) ptx::bulk_wait_group_read0();
+        __syncwarp();
+      }
       int eoff[8], poff[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -345,9 +354,18 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
         }
         ptx::fence_proxy_async();  // generic-proxy stores -> visible to the tensor-core proxy
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bars->a_ready[kp]));
+        if (lane == 0) {
+          ptx::mbar_arrive(ptx::smem_u32(&bars->a_ready[kp]));
+          if (save_h) {
+            for (int kb = 2 * kp; kb < 2 * kp + 2 && kb < nkb; ++kb)
+              ptx::tma_store_2d_hint(&h_map, base + kb * kABlockBytes + bw * 32 * 128, kb * kBlockK,
+                                     tile * kTileM + bw * 32, hs_policy);
+            ptx::bulk_commit_group();
+          }
+        }
       }
     }
+    if (save_h && lane == 0) ptx::bulk_wait_group0();
   } else if (warp >= kEpiWarp0 && warp < kBuilderWarp0) {
     // ===================== epilogue =====================
 #include "joint_fused_epilogue.inc"

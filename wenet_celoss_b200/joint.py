@@ -70,17 +70,18 @@ def joint_logit_bound(w_bf16, bias_pad, V):
 
 
 def joint_logprobs(e, p, w_bf16, bias_pad, targets, logit_lengths, target_lengths, V, blank,
-                   max_ctas: int = 0, use_bound: bool = True):
-    """lse, lp_blank, lp_emit [B,T,U1] from e [B,T,J], p [B,U1,J] (fp32) and W_out (bf16)."""
+                   max_ctas: int = 0, use_bound: bool = True, H=None):
+    """lse, lp_blank, lp_emit [B,T,U1] from e [B,T,J], p [B,U1,J] (fp32) and W_out (bf16).
+    ``H`` [B*T*U1, ldh] bf16 (optional) receives tanh(e + p) for the backward pass."""
     B, T, J = e.shape
     U1 = p.shape[1]
     lat = torch.empty(3, B, T, U1, dtype=torch.float32, device=e.device)
     lse, lpb, lpe = lat.unbind(0)
     bound = joint_logit_bound(w_bf16, bias_pad, V) if use_bound else None
-    _lib.call("b200_joint_fwd", ptr(e), ptr(p), ptr(w_bf16), ptr(bias_pad), ptr(targets),
+    _lib.call("b200_joint_fwd_h", ptr(e), ptr(p), ptr(w_bf16), ptr(bias_pad), ptr(targets),
               ptr(logit_lengths), ptr(target_lengths), i32(B), i32(T), i32(U1), i32(V), i32(J),
-              i32(blank), ptr(lse), ptr(lpb), ptr(lpe), ptr(bound), i32(max_ctas),
-              _lib.stream_handle(e.device))
+              i32(blank), ptr(lse), ptr(lpb), ptr(lpe), ptr(bound), ptr(H),
+              i32(H.stride(0) if H is not None else 0), i32(max_ctas), _lib.stream_handle(e.device))
     return lse, lpb, lpe
 
 
@@ -101,11 +102,16 @@ class _FusedJointLossFn(torch.autograd.Function):
             V, J = w_out.shape
             w_bf16 = w_out.detach().to(torch.bfloat16).contiguous()
             bias_pad = _pad_bias(b_out, V)
+            # when a gradient will be asked for, the forward kernel keeps H = tanh(e + p) (bf16,
+            # J / (2 V) of the logits' size: 1.65 GB at cfg3) for the backward kernels
+            need_grad = any(ctx.needs_input_grad[:4])
+            H = (torch.empty(e32.shape[0] * e32.shape[1] * p32.shape[1], J, dtype=torch.bfloat16, device=dev)
+                 if need_grad else None)
             lse, lpb, lpe = joint_logprobs(e32, p32, w_bf16, bias_pad, targets, logit_lengths,
-                                           target_lengths, V, blank)
+                                           target_lengths, V, blank, H=H)
             alpha, beta, costs, diag_off = rnnt_lattice(lpb, lpe, logit_lengths, target_lengths)
         ctx.save_for_backward(e32, p32, w_bf16, bias_pad, targets, logit_lengths, target_lengths,
-                              lse, alpha, beta, diag_off)
+                              lse, alpha, beta, diag_off, H)
         ctx.blank = blank
         ctx.in_dtypes = (e.dtype, p.dtype, w_out.dtype, b_out.dtype)
         return costs
@@ -113,7 +119,7 @@ class _FusedJointLossFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         (e32, p32, w_bf16, bias_pad, targets, logit_lengths, target_lengths, lse, alpha, beta,
-         diag_off) = ctx.saved_tensors
+         diag_off, H_all) = ctx.saved_tensors
         B, T, J = e32.shape
         U1 = p32.shape[1]
         V = w_bf16.shape[0]
@@ -130,7 +136,6 @@ class _FusedJointLossFn(torch.autograd.Function):
             sms = torch.cuda.get_device_properties(dev).multi_processor_count
             nb = _chunk_utts(B, per_utt, ldg, sms)
             G = torch.empty(nb * per_utt, ldg, dtype=torch.bfloat16, device=dev)
-            H = torch.empty(nb * per_utt, ldh, dtype=torch.bfloat16, device=dev)
             # d b_out = column sums of G: accumulated by the joint kernel's epilogue into 16
             # partial rows (an augmented ones column made the dW GEMM 520 wide: 25 % slower)
             db_part = torch.zeros(16, (V + _TILE_M - 1) // _TILE_M * _TILE_M, dtype=torch.float32,
@@ -142,7 +147,8 @@ class _FusedJointLossFn(torch.autograd.Function):
             for b0 in range(0, B, nb):
                 b1 = min(B, b0 + nb)
                 n = (b1 - b0) * per_utt
-                _lib.call("b200_joint_grad_chunk", ptr(e32), ptr(p32), ptr(w_bf16), ptr(bias_pad),
+                H = H_all[b0 * per_utt:b1 * per_utt]  # written by the forward kernel
+                _lib.call("b200_joint_grad_chunk_h", ptr(e32), ptr(p32), ptr(w_bf16), ptr(bias_pad),
                           ptr(targets), ptr(coef), i32(B), i32(T), i32(U1), i32(V), i32(J),
                           i32(blank), _i64(b0 * per_utt), _i64(n), ptr(G), i32(ldg), ptr(H), i32(ldh),
                           ptr(db_part), i32(0), st)
