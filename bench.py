@@ -391,8 +391,11 @@ class RnntFusedWorkload:
         st = _lib.stream_handle(self.dev)
         box = {}
 
-        def k_fwd():
-            box["lat"] = joint_logprobs(e, p, w, bias, self.targets, self.tl, self.ul, V, 0)
+        per_utt = T * U1
+        H_all = torch.empty(B * per_utt, J, dtype=torch.bfloat16, device=self.dev)
+
+        def k_fwd():  # the training forward: also stores H = tanh(e + p) for the backward kernels
+            box["lat"] = joint_logprobs(e, p, w, bias, self.targets, self.tl, self.ul, V, 0, H=H_all)
 
         lat_out = [torch.empty(B, T, U1, device=self.dev), torch.empty(B, T, U1, device=self.dev),
                    torch.empty(B, device=self.dev),
@@ -404,32 +407,29 @@ class RnntFusedWorkload:
                       ptr(lat_out[2]), ptr(lat_out[3]), st)
             box["ab"] = lat_out
 
-        per_utt = T * U1
-        ldg, ldh = (V + 15) // 16 * 16, J + 8
-        G = torch.empty(per_utt, ldg, dtype=torch.bfloat16, device=self.dev)
-        H = torch.zeros(per_utt, ldh, dtype=torch.bfloat16, device=self.dev)
+        ldg = (V + 15) // 16 * 16
+        G = torch.empty(B * per_utt, ldg, dtype=torch.bfloat16, device=self.dev)
+        dbp = torch.zeros(16, (V + 127) // 128 * 128, device=self.dev)
         dy = torch.full((B,), 1.0 / B, device=self.dev)
 
-        def k_grad():
-            _lib.call("b200_joint_grad_chunk", ptr(e), ptr(p), ptr(w), ptr(bias), ptr(self.targets),
+        def k_grad():  # the launch the step makes: all B utterances in one chunk, H from the forward
+            _lib.call("b200_joint_grad_chunk_h", ptr(e), ptr(p), ptr(w), ptr(bias), ptr(self.targets),
                       ptr(box["coef"]), i32(B), i32(T), i32(U1), i32(V), i32(J), i32(0), _i64(0),
-                      _i64(per_utt), ptr(G), i32(ldg), ptr(H), i32(ldh), ptr(None), i32(0), st)
+                      _i64(B * per_utt), ptr(G), i32(ldg), ptr(H_all), i32(J), ptr(dbp), i32(0), st)
 
         from wenet_celoss_b200.joint import joint_dw
-        G8 = torch.zeros(8 * per_utt, ldg, dtype=torch.bfloat16, device=self.dev)
-        H8 = torch.zeros(8 * per_utt, J, dtype=torch.bfloat16, device=self.dev)
         dW8 = torch.zeros(V, J, device=self.dev)
 
         def k_dw():
-            joint_dw(G8, H8, 8 * per_utt, V, J, dW8)
+            joint_dw(G, H_all, B * per_utt, V, J, dW8)
 
         out = {}
         k_fwd(); k_lat()
         alpha, beta, costs, doff = box["ab"]
         box["coef"] = rnnt_grad_coef(box["lat"][0], alpha, beta, doff, dy, self.targets, self.tl, self.ul, 0)
         for name, fn in (("joint_kernel<FWD> (all cells)", k_fwd), ("rnnt_lattice_kernel", k_lat),
-                         ("joint_kernel<GRAD> (1 utterance chunk)", k_grad),
-                         ("joint_dw_kernel (8 utterance chunk)", k_dw)):
+                         ("joint_kernel<GRAD> (all cells, one chunk)", k_grad),
+                         ("joint_dw_kernel (all cells)", k_dw)):
             ts = []
             for _ in range(iters + 1):
                 e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
@@ -447,9 +447,8 @@ class RnntFusedWorkload:
         flops_fwd = 2.0 * self.cells * cfg["J"] * cfg["V"]
         t_fwd = kb["joint_kernel<FWD> (all cells)"]
         achieved = flops_fwd / (t_fwd * 1e-3) / 1e12
-        flops_chunk = 2.0 * cfg["T"] * (cfg["U"] + 1) * cfg["J"] * cfg["V"]
-        ach_g = flops_chunk / (kb["joint_kernel<GRAD> (1 utterance chunk)"] * 1e-3) / 1e12
-        ach_dw = 8 * flops_chunk / (kb["joint_dw_kernel (8 utterance chunk)"] * 1e-3) / 1e12
+        ach_g = flops_fwd / (kb["joint_kernel<GRAD> (all cells, one chunk)"] * 1e-3) / 1e12
+        ach_dw = flops_fwd / (kb["joint_dw_kernel (all cells)"] * 1e-3) / 1e12
         counted = 6.0 * self.cells * cfg["J"] * cfg["V"]
         traffic = None
         try:  # per-launch DRAM bytes of this kernel from the committed ncu --set full capture

@@ -181,3 +181,43 @@ def test_hotword_gated_greedy_golden(golden, mode):
                                         context_lengths=ctx_len, context_filter_state="on",
                                         context_decoder_labels_padded=torch.from_numpy(d["labels"]))
     assert hy == [_unpad(d["hyps"][b])] and dist == float(d["dist"][b])
+
+
+@pytest.mark.parametrize("mode", ["off", "on"])
+def test_hotword_greedy_full_dims_vs_oracle(mode):
+    """Reference dims (P = 256, 4 heads, 100 phrase vectors: the 16-byte-load paths of pred_bias /
+    pred_gate kernels) against the CPU oracle restatements; utterances whose smallest argmax or
+    gate margin could flip under fp32 reordering are reported, not compared."""
+    import bench
+    from wenet_celoss_b200 import greedy_search_batch
+    m = _search_model(1000, seed=21)
+    torch.manual_seed(22)
+    cb = bench._ContextBias(256, 100).eval()
+    with torch.no_grad():
+        m.joint.ffn_out.bias[0] -= 4.5
+    m.context_bias = cb
+    m.loss_mode = "pred"
+    g = torch.Generator().manual_seed(23)
+    B, T = 4, 24
+    enc = torch.randn(B, T, 256, generator=g) * 2.0
+    lens = torch.tensor([24, 17, 24, 9])
+    ctx = torch.zeros(100, 4, dtype=torch.int32)
+    ctx_len = torch.full((100,), 4, dtype=torch.int32)
+    with torch.no_grad():
+        bh, bhe = cb.phrases, cb.phrases[:, :1]
+        eb, _ = cb.forward_encoder_bias(bh, enc)
+        ee, _ = cb.forward_encoder_bias(bhe, enc)
+    want = []
+    for b in range(B):
+        n = int(lens[b])
+        if mode == "on":
+            want.append(orc.greedy_search_hotword_gated(m, eb[b:b + 1, :n], ee[b:b + 1, :n], n, bh, bhe, n_steps=5))
+        else:
+            want.append((orc.greedy_search_hotword(m, eb[b:b + 1, :n], n, bhe, n_steps=5), None))
+    assert any(len(h) > 0 for h, _ in want)
+    md = copy.deepcopy(m).to(DEV)
+    hyps, dec = greedy_search_batch(md, enc.to(DEV), lens.to(DEV), n_steps=5, context_list=ctx.to(DEV),
+                                    context_lengths=ctx_len.to(DEV), context_filter_state=mode,
+                                    return_decisions=True)
+    same = sum(hyps[b] == want[b][0] and (mode == "off" or dec[b] == want[b][1]) for b in range(B))
+    assert same == B, (same, [(hyps[b][:8], want[b][0][:8]) for b in range(B)])

@@ -63,9 +63,13 @@ template <int MODE> struct Cfg {
   static constexpr int kBuilderWarp0 = kEpiWarp0 + kEpiWarps;  // MODE_FWD: 4 builder warps
   static constexpr int kThreads = MODE == 0 ? 512 : 640;
   static constexpr int kASlots = MODE == 0 ? 4 : 2;
-  static constexpr int kStages = MODE == 0 ? 3 : 4;
+#ifndef B200_GRAD_GBUFS
+#define B200_GRAD_GBUFS 1
+#endif
+  static constexpr int kGBufs = MODE == 0 ? 0 : B200_GRAD_GBUFS;  // G staging tiles per epilogue warp
+  static constexpr int kStages = MODE == 0 ? 3 : (B200_GRAD_GBUFS == 2 ? 3 : 4);
   static constexpr int kABytes = kASlots * kASlotBytes;
-  static constexpr int kGStageBytes = MODE == 0 ? 0 : 16 * 2048;
+  static constexpr int kGStageBytes = kGBufs * 16 * 2048;
 };
 constexpr int kWBlockBytes = kTileN * kBlockK * 2;      // 16 KB per k-block
 constexpr int kWStageBytes = 2 * kWBlockBytes;          // 32 KB

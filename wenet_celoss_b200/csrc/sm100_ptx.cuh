@@ -111,6 +111,10 @@ __device__ __forceinline__ void bulk_commit_group() {
 __device__ __forceinline__ void bulk_wait_group_read0() {
   asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
+// all but the most recent bulk group have finished reading
+__device__ __forceinline__ void bulk_wait_group_read1() {
+  asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+}
 // ... and are complete (writes performed)
 __device__ __forceinline__ void bulk_wait_group0() {
   asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
