@@ -315,11 +315,38 @@ ctc_grad_kernel(const T* __restrict__ logits, const float* __restrict__ lse,
     }
   }
   const float xblank = Elem<T>::to_float(row[blank]);
+  // the first kOcc * 32 states: all four loads of every state issued before the first use (a
+  // rolled loop with the shared-memory atomic in its body paid one memory round trip per 32 states)
+  constexpr int kOcc = 8;
+  float pa[kOcc], pb[kOcc], pl[kOcc];
+  int pd[kOcc];
+#pragma unroll
+  for (int i = 0; i < kOcc; ++i) {
+    const int s = lane + 32 * i;
+    pa[i] = pb[i] = pl[i] = 0.f;
+    pd[i] = 0;
+    if (s < S) {
+      pa[i] = al[s];
+      pb[i] = be[s];
+      pl[i] = lp[s];
+      pd[i] = ld[s];
+    }
+  }
   for (int s = lane; s < S; s += 32) occ[s] = 0.f;
   __syncwarp();
   float occ_blank = 0.f;
-  for (int s = lane; s < S; s += 32) {
+#pragma unroll
+  for (int i = 0; i < kOcc; ++i) {
+    const int s = lane + 32 * i;
+    if (s >= S) continue;
     // alpha*beta counts the emission at t twice: take lp out once
+    const float post = expf(pa[i] + pb[i] + nl - pl[i]);
+    if (s & 1)
+      atomicAdd(&occ[pd[i]], post);
+    else
+      occ_blank += post;
+  }
+  for (int s = lane + 32 * kOcc; s < S; s += 32) {  // longer label sequences
     float post = expf(al[s] + be[s] + nl - lp[s]);
     if (s & 1)
       atomicAdd(&occ[ld[s]], post);
