@@ -198,12 +198,14 @@ __global__ void __launch_bounds__(256) pred_z_kernel(Model M, State S, int round
   }
 }
 
-// ---- logits for a tile of 32 vocabulary rows x all active utterances, partial argmax ----
-constexpr int kVT = 32;   // vocabulary rows per CTA
+// ---- logits for a tile of kVT vocabulary rows x all active utterances, partial argmax ----
+// 34 rows: V = 5000 is 148 tiles, one per SM (32 rows gave 157 CTAs: nine SMs ran two)
+constexpr int kVT = 34;   // vocabulary rows per CTA (even)
+constexpr int kLaThreads = 8 * (kVT / 2);  // 8 utterance pairs x kVT/2 row slots
 constexpr int kUG = 16;   // utterances per shared-memory group
 constexpr int kPad = 4;   // floats of row padding (bank spread)
 
-__global__ void __launch_bounds__(128) logits_argmax_kernel(Model M, State S, int round) {
+__global__ void __launch_bounds__(kLaThreads) logits_argmax_kernel(Model M, State S, int round) {
   extern __shared__ float sm[];
   const int set = round & 1;
   const int n_act = S.counters[set * 2 + 0];
@@ -221,9 +223,9 @@ __global__ void __launch_bounds__(128) logits_argmax_kernel(Model M, State S, in
     *reinterpret_cast<float4*>(sw + r * ld + k4 * 4) = v;
   }
   const int u2 = tid & 7;    // utterance pair within the group
-  const int rs = tid >> 3;   // rows rs and rs + 16
+  const int rs = tid >> 3;   // rows rs and rs + kVT / 2
   const float b0 = (v0 + rs < M.V) ? M.b_out[v0 + rs] : 0.f;
-  const float b1 = (v0 + rs + 16 < M.V) ? M.b_out[v0 + rs + 16] : 0.f;
+  const float b1 = (v0 + rs + kVT / 2 < M.V) ? M.b_out[v0 + rs + kVT / 2] : 0.f;
   const int* list = S.act_list + set * S.B;
   for (int g0 = 0; g0 < n_act; g0 += kUG) {
     __syncthreads();
@@ -237,7 +239,7 @@ __global__ void __launch_bounds__(128) logits_argmax_kernel(Model M, State S, in
     __syncthreads();
     float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f;  // [row][utt]
     const float* w0 = sw + rs * ld;
-    const float* w1 = sw + (rs + 16) * ld;
+    const float* w1 = sw + (rs + kVT / 2) * ld;
     const float* z0 = sz + (2 * u2) * ld;
     const float* z1 = sz + (2 * u2 + 1) * ld;
 #pragma unroll 4
@@ -253,8 +255,8 @@ __global__ void __launch_bounds__(128) logits_argmax_kernel(Model M, State S, in
     }
     sl[(2 * u2) * (kVT + 1) + rs] = a00 + b0;
     sl[(2 * u2 + 1) * (kVT + 1) + rs] = a01 + b0;
-    sl[(2 * u2) * (kVT + 1) + rs + 16] = a10 + b1;
-    sl[(2 * u2 + 1) * (kVT + 1) + rs + 16] = a11 + b1;
+    sl[(2 * u2) * (kVT + 1) + rs + kVT / 2] = a10 + b1;
+    sl[(2 * u2 + 1) * (kVT + 1) + rs + kVT / 2] = a11 + b1;
     __syncthreads();
     if (tid < kUG && g0 + tid < n_act) {
       float best = -INFINITY;
