@@ -30,7 +30,7 @@ __device__ __forceinline__ int ext_label(const long long* __restrict__ ys, int s
 // pass 1: one warp per (b,t) row: lse + gather of the S extended-label log-probs
 // ---------------------------------------------------------------------------
 template <typename T>
-__global__ void __launch_bounds__(kRowWarps * 32)
+__global__ void __launch_bounds__(kRowWarps * 32, 4)
 ctc_logprobs_kernel(const T* __restrict__ logits, const long long* __restrict__ ys_pad,
                     const int32_t* __restrict__ hlens, const int32_t* __restrict__ ys_lens, int B,
                     int Tm, int V, int Lmax, int blank, float* __restrict__ lse,
