@@ -23,7 +23,7 @@ namespace b200 {
 // pass 1: one warp per lattice cell; online (max, sum-exp) over the V logits.
 // ---------------------------------------------------------------------------
 template <typename T>
-__global__ void __launch_bounds__(kRowWarps * 32)
+__global__ void __launch_bounds__(kRowWarps * 32, 4)
 rnnt_logprobs_kernel(const T* __restrict__ logits, const int32_t* __restrict__ targets,
                      const int32_t* __restrict__ logit_len, const int32_t* __restrict__ target_len,
                      int B, int Tm, int U1, int V, int blank, float* __restrict__ lse,
