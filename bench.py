@@ -423,13 +423,25 @@ class RnntFusedWorkload:
         def k_dw():
             joint_dw(G, H_all, B * per_utt, V, J, dW8)
 
+        de = torch.empty(B, T, J, device=self.dev)
+        dp = torch.zeros(B, U1, J, device=self.dev)
+
+        def k_dh_lib():  # the one library GEMM left in the backward (replaced by joint_dh_kernel)
+            box["dH"] = torch.mm(G[:, :V], w, out_dtype=torch.float32)
+
+        def k_dz():
+            _lib.call("b200_joint_dz_reduce", ptr(box["dH"]), ptr(H_all), i32(J), i32(B), i32(T), i32(U1), i32(J),
+                      ptr(de), ptr(dp), st)
+
         out = {}
         k_fwd(); k_lat()
         alpha, beta, costs, doff = box["ab"]
         box["coef"] = rnnt_grad_coef(box["lat"][0], alpha, beta, doff, dy, self.targets, self.tl, self.ul, 0)
         for name, fn in (("joint_kernel<FWD> (all cells)", k_fwd), ("rnnt_lattice_kernel", k_lat),
                          ("joint_kernel<GRAD> (all cells, one chunk)", k_grad),
-                         ("joint_dw_kernel (all cells)", k_dw)):
+                         ("joint_dw_kernel (all cells)", k_dw),
+                         ("library GEMM dH = G.W (cuBLAS)", k_dh_lib),
+                         ("joint_dz_reduce_kernel", k_dz)):
             ts = []
             for _ in range(iters + 1):
                 e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
@@ -442,30 +454,64 @@ class RnntFusedWorkload:
         return out
 
     def roofline(self, pk, ms_step):
+        """Roofline of the kernel with the LARGEST time per step (tensor-pipe bound); the other
+        tensor-core kernels of the step under ``other``.  ``traffic`` = DRAM bytes per launch of that
+        kernel from the committed ncu --set full capture of this round (profiles/r02_traffic.json,
+        keyed by kernel; null when no capture of the current kernel exists)."""
         kb = self.kernel_breakdown()
         cfg = self.cfg
-        flops_fwd = 2.0 * self.cells * cfg["J"] * cfg["V"]
-        t_fwd = kb["joint_kernel<FWD> (all cells)"]
-        achieved = flops_fwd / (t_fwd * 1e-3) / 1e12
-        ach_g = flops_fwd / (kb["joint_kernel<GRAD> (all cells, one chunk)"] * 1e-3) / 1e12
-        ach_dw = flops_fwd / (kb["joint_dw_kernel (all cells)"] * 1e-3) / 1e12
+        flops = 2.0 * self.cells * cfg["J"] * cfg["V"]  # per GEMM-shaped launch (SURVEY 8d: 2*cells*J*V)
+        tensor_kernels = {k: v for k, v in kb.items()
+                          if k.startswith(("joint_kernel", "joint_dw_kernel", "joint_dh_kernel"))}
+        dom = max(tensor_kernels, key=tensor_kernels.get)
+        ach = {k: flops / (v * 1e-3) / 1e12 for k, v in tensor_kernels.items()}
         counted = 6.0 * self.cells * cfg["J"] * cfg["V"]
-        traffic = None
-        try:  # per-launch DRAM bytes of this kernel from the committed ncu --set full capture
-            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles",
-                                   "r01_traffic.json")) as fh:
-                traffic = json.load(fh)["joint_kernel<FWD>"]["bytes"]
+        traffic, traffic_src = None, None
+        try:
+            with open(ROOT / "profiles" / "r02_traffic.json") as fh:
+                tj = json.load(fh)
+            key = dom.split(" ")[0]
+            traffic, traffic_src = tj[key]["bytes"], tj[key].get("source")
         except (OSError, KeyError, ValueError):
             pass
-        return {"bound": "tensor", "kernel": "joint_kernel<FWD>", "achieved": achieved,
-                "peak": pk["bf16"], "unit": "TFLOP/s", "frac": achieved / pk["bf16"], "traffic": traffic,
+        return {"bound": "tensor", "kernel": dom, "achieved": ach[dom], "peak": pk["bf16"],
+                "unit": "TFLOP/s", "frac": ach[dom] / pk["bf16"], "traffic": traffic,
+                "traffic_source": traffic_src,
                 "peak_source": pk["source"] + " (burst: kernel timed alone)",
-                "algorithmic_flops_per_launch": flops_fwd, "kernel_ms": kb,
-                "other": {"joint_kernel<GRAD>": {"achieved": ach_g, "frac": ach_g / pk["bf16"]},
-                          "joint_dw_kernel": {"achieved": ach_dw, "frac": ach_dw / pk["bf16"]}},
+                "algorithmic_flops_per_launch": flops, "kernel_ms": kb,
+                "other": {k: {"achieved": a, "frac": a / pk["bf16"]} for k, a in ach.items() if k != dom},
                 "step_frac_of_tensor_roofline":
                     counted / (ms_step * 1e-3) / 1e12 / pk["bf16_sustained"],
                 "step_counted_flops": counted}
+
+    def self_check(self):
+        """Before timing: the fused loss of utterance 0 against (a) this package's rnnt_loss and
+        (b) torchaudio's CUDA rnnt_loss on the SAME bf16-rounded operands, materialised for that one
+        utterance (1 GB of fp32 logits).  Raises when they disagree (rtol 2e-3)."""
+        import torchaudio
+        with torch.no_grad():
+            j = self.joint
+            fused = self.pkg.fused_joint_rnnt_loss(j, self.enc, self.pred, self.targets, self.tl, self.ul,
+                                                   blank=0, reduction="none")
+            e = j.enc_ffn(self.enc[:1]).float()
+            p = j.pred_ffn(self.pred[:1]).float()
+            h = torch.tanh(e[:, :, None] + p[:, None]).to(torch.bfloat16)
+            w = j.ffn_out.weight.to(torch.bfloat16)
+            logits = (h.reshape(-1, h.shape[-1]) @ w.t()).float().add_(j.ffn_out.bias.float())
+            logits = logits.view(1, e.shape[1], p.shape[1], -1).contiguous()
+            tl0, ul0 = self.tl[:1].clone(), self.ul[:1].clone()
+            Tm, Um = int(tl0[0]), int(ul0[0])
+            logits = logits[:, :Tm, :Um + 1].contiguous()
+            tg = self.targets[:1, :Um].contiguous()
+            mine = self.pkg.rnnt_loss(logits, tg, tl0, ul0, blank=0, reduction="none")
+            ta = torchaudio.functional.rnnt_loss(logits, tg, tl0, ul0, blank=0, reduction="none")
+        f0, m0, t0 = float(fused[0]), float(mine[0]), float(ta[0])
+        ok = abs(f0 - t0) <= 2e-3 * abs(t0) and abs(m0 - t0) <= 1e-4 * abs(t0)
+        res = {"fused_cost_utt0": f0, "materialised_b200_cost_utt0": m0,
+               "torchaudio_cuda_cost_utt0": t0, "rtol_fused": 2e-3, "ok": bool(ok)}
+        if not ok:
+            raise AssertionError(f"bench self-check failed: {res}")
+        return res
 
     def describe(self):
         return (FUSED_DESC,
@@ -596,6 +642,14 @@ def extra_rows(cfg, dev, pk):
     ms, beams = timed(lambda: pkg.prefix_beam_search_batch(model, enc, lens, beam_size=10), reps=2)
     out["beam10"] = {"value": B4 / (ms * 1e-3), "unit": "utt/s", "ms": ms,
                      "workload": "cfg4: B=64 T=500 V=5000 prefix beam search, beam=10, ctc 0.3 / rnnt 0.7"}
+    try:  # the reference's per-utterance Python loops with the model on the GPU (baseline leg)
+        out["search_gpu_reference"] = gpu_reference_search(cfg, dev, model, enc, lens)
+        out["greedy"]["vs_python_cuda"] = (out["greedy"]["value"] /
+                                           out["search_gpu_reference"]["greedy_python_cuda_utts_per_sec"])
+        out["beam10"]["vs_python_cuda"] = (out["beam10"]["value"] /
+                                           out["search_gpu_reference"]["beam10_python_cuda_utts_per_sec"])
+    except Exception as exc:  # noqa: BLE001
+        out["search_gpu_reference"] = {"error": repr(exc)[:300]}
     # cfg5: CTC module fwd+bwd B=64 T=1000 V=5000
     B5, T5, L5, V = 64, 1000, 100, cfg["V"]
     ctc = pkg.CTC(V, cfg["E"]).to(dev)
@@ -656,6 +710,235 @@ def extra_rows(cfg, dev, pk):
         out["ctc_prefix_beam10"]["cpu_port_error"] = repr(exc)
     return out
 
+
+
+# --------------------------------------------------------------------------- GPU reference
+CFG2 = dict(B=32, T=250, U=40, V=4233, E=256, P=256, J=512)
+
+
+def _eager_joint(joint, enc, pred):
+    """TransducerJoint.forward as the reference runs it (wenet/transducer/joint.py:55-69): two Linear
+    layers, broadcast add, tanh, ffn_out -> materialised [B,T,U1,V] logits (library kernels)."""
+    e = joint.enc_ffn(enc)
+    p = joint.pred_ffn(pred)
+    return joint.ffn_out(torch.tanh(e.unsqueeze(2) + p.unsqueeze(1)))
+
+
+def _timed_cuda(fn, reps=2, warm=1):
+    for _ in range(warm):
+        fn()
+    ts = []
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record()
+        fn()
+        e1.record()
+        e1.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return statistics.median(ts)
+
+
+def gpu_reference(cfg, dev, pk):
+    """The reference's own GPU path on THIS B200 (SURVEY 8d last row): eager joint +
+    torchaudio CUDA rnnt_loss (wenet/transducer/transducer.py:132-147), torchaudio CUDA rnnt_loss alone
+    on materialised logits, log_softmax + torch CTC loss (wenet/transformer/ctc.py:57-63), next to the
+    same step through this package.  Library kernels only on the reference side; CUDA events."""
+    import torchaudio
+    import wenet_celoss_b200 as pkg
+    out = {"note": "reference call sites reproduced on cuda:0 with the installed torchaudio/ATen sm_100 "
+                   "kernels (fp32, allow_tf32=False as torch defaults); 'ours' = this package on the same inputs"}
+    g = torch.Generator().manual_seed(777)
+
+    def fused_pair(c, tag, dtype_note):
+        B, T, U, V, E, P, J = (c[k] for k in ("B", "T", "U", "V", "E", "P", "J"))
+        torch.manual_seed(1234)
+        joint = _Joint(V, E, P, J).to(dev)
+        params = list(joint.parameters())
+        tgt = torch.randint(1, V, (B, U), generator=g, dtype=torch.int32).to(dev)
+        row = {"shape": dict(c), "dtype": dtype_note}
+        ours_ms = None
+        b_ref = B
+        while b_ref >= 1:
+            try:
+                torch.cuda.empty_cache()
+                torch.cuda.reset_peak_memory_stats()
+                enc = torch.randn(b_ref, T, E, generator=g).to(dev).requires_grad_(True)
+                pred = torch.randn(b_ref, U + 1, P, generator=g).to(dev).requires_grad_(True)
+                tl = torch.full((b_ref,), T, dtype=torch.int32, device=dev)
+                ul = torch.full((b_ref,), U, dtype=torch.int32, device=dev)
+
+                def ref_step():
+                    enc.grad = pred.grad = None
+                    for p_ in params:
+                        p_.grad = None
+                    loss = torchaudio.functional.rnnt_loss(_eager_joint(joint, enc, pred), tgt[:b_ref], tl, ul,
+                                                           blank=0, reduction="mean")
+                    loss.backward()
+                    return loss
+
+                ms = _timed_cuda(ref_step)
+                row.update(reference_B=b_ref, reference_ms=ms, reference_utts_per_sec=b_ref / (ms * 1e-3),
+                           reference_peak_mem_gb=torch.cuda.max_memory_allocated() / 1e9,
+                           reference_loss=float(ref_step().item()))
+
+                def our_step():
+                    enc.grad = pred.grad = None
+                    for p_ in params:
+                        p_.grad = None
+                    loss = pkg.fused_joint_rnnt_loss(joint, enc, pred, tgt[:b_ref], tl, ul, blank=0,
+                                                     reduction="mean")
+                    loss.backward()
+                    return loss
+
+                ours_ms = _timed_cuda(our_step, reps=3)
+                row.update(ours_ms=ours_ms, ours_utts_per_sec=b_ref / (ours_ms * 1e-3),
+                           ours_loss=float(our_step().item()), speedup=ms / ours_ms)
+                break
+            except torch.OutOfMemoryError:
+                b_ref //= 2
+        out[tag] = row
+        del joint
+        torch.cuda.empty_cache()
+
+    fused_pair(CFG2, "cfg2_joint_rnnt", "reference fp32 (SIMT GEMMs); ours bf16 MMA operands")
+    fused_pair(cfg, "cfg3_joint_rnnt", "reference fp32 (SIMT GEMMs); ours bf16 MMA operands")
+
+    # (b) rnnt_loss alone on materialised logits: torchaudio CUDA vs this package, same tensor
+    for tag, c, dt in (("cfg2_rnnt_loss_fp32", CFG2, torch.float32), ("cfg3_rnnt_loss_fp16", cfg, torch.float16)):
+        B, T, U, V = c["B"], c["T"], c["U"], c["V"]
+        try:
+            torch.cuda.empty_cache()
+            logits = torch.empty(B, T, U + 1, V, dtype=dt, device=dev)
+            gd = torch.Generator(device=dev).manual_seed(5)
+            for b in range(B):
+                logits[b] = torch.randn(T, U + 1, V, generator=gd, device=dev)
+            logits.requires_grad_(True)
+            tgt = torch.randint(1, V, (B, U), generator=g, dtype=torch.int32).to(dev)
+            tl = torch.full((B,), T, dtype=torch.int32, device=dev)
+            ul = torch.full((B,), U, dtype=torch.int32, device=dev)
+
+            def step(fn):
+                def run():
+                    logits.grad = None
+                    l = fn(logits, tgt, tl, ul, blank=0, reduction="mean")
+                    l.backward()
+                    return l
+                return run
+            ms_ref = _timed_cuda(step(torchaudio.functional.rnnt_loss))
+            ms_our = _timed_cuda(step(pkg.rnnt_loss), reps=3)
+            nbytes = 3.0 * logits.numel() * logits.element_size()
+            out[tag] = {"reference_ms": ms_ref, "ours_ms": ms_our, "speedup": ms_ref / ms_our,
+                        "reference_utts_per_sec": B / (ms_ref * 1e-3), "ours_utts_per_sec": B / (ms_our * 1e-3),
+                        "ours_frac_of_hbm_roofline": nbytes / (ms_our * 1e-3) / 1e9 / pk["hbm"],
+                        "reference_frac_of_hbm_roofline": nbytes / (ms_ref * 1e-3) / 1e9 / pk["hbm"],
+                        "reference_loss": float(step(torchaudio.functional.rnnt_loss)().item()),
+                        "ours_loss": float(step(pkg.rnnt_loss)().item())}
+            del logits
+        except torch.OutOfMemoryError as exc:
+            out[tag] = {"error": repr(exc)[:200]}
+        torch.cuda.empty_cache()
+
+    # (c) cfg5 CTC: CTC.forward of the reference (ctc_lo, log_softmax on [T,B,V], torch CTC loss) vs ours
+    B5, T5, L5, V = 64, 1000, 100, cfg["V"]
+    ctc = pkg.CTC(V, cfg["E"]).to(dev)
+    hs = torch.randn(B5, T5, cfg["E"], generator=g).to(dev).requires_grad_(True)
+    yl = torch.randint(50, L5 + 1, (B5,), generator=g)
+    ys = torch.randint(1, V, (B5, L5), generator=g)
+    ys = torch.where(torch.arange(L5)[None] < yl[:, None], ys, torch.full_like(ys, -1)).to(dev)
+    hl = torch.full((B5,), T5, dtype=torch.int32, device=dev)
+    yl = yl.to(dev)
+
+    def ctc_ref_step():  # wenet/transformer/ctc.py:57-63
+        hs.grad = None
+        for p_ in ctc.parameters():
+            p_.grad = None
+        ys_hat = ctc.ctc_lo(hs).transpose(0, 1).log_softmax(2)
+        l = torch.nn.functional.ctc_loss(ys_hat, ys, hl, yl, reduction="sum") / B5
+        l.backward()
+        return l
+
+    def ctc_our_step():
+        hs.grad = None
+        for p_ in ctc.parameters():
+            p_.grad = None
+        l = ctc(hs, hl, ys, yl)
+        l.backward()
+        return l
+    ms_ref = _timed_cuda(ctc_ref_step, reps=3)
+    ms_our = _timed_cuda(ctc_our_step, reps=5)
+    logits5 = torch.randn(B5, T5, V, generator=g).to(dev).requires_grad_(True)
+
+    def ctc_loss_ref():
+        logits5.grad = None
+        l = torch.nn.functional.ctc_loss(logits5.transpose(0, 1).log_softmax(2), ys, hl, yl,
+                                         reduction="sum") / B5
+        l.backward()
+        return l
+
+    def ctc_loss_our():
+        logits5.grad = None
+        l = pkg.ctc_loss(logits5, ys, hl, yl, reduction="sum") / B5
+        l.backward()
+        return l
+    ms_ref_k = _timed_cuda(ctc_loss_ref, reps=3)
+    ms_our_k = _timed_cuda(ctc_loss_our, reps=5)
+    out["cfg5_ctc"] = {"module_reference_ms": ms_ref, "module_ours_ms": ms_our, "module_speedup": ms_ref / ms_our,
+                       "loss_only_reference_ms": ms_ref_k, "loss_only_ours_ms": ms_our_k,
+                       "loss_only_speedup": ms_ref_k / ms_our_k,
+                       "reference_loss": float(ctc_ref_step().item()), "ours_loss": float(ctc_our_step().item())}
+    del logits5
+    torch.cuda.empty_cache()
+    return out
+
+
+def logits_row(cfg, pk, steps=5):
+    """The metric's "% HBM peak" half: rnnt_loss(logits) fwd+bwd over materialised bf16 logits at cfg3
+    (algorithmic bytes 3*N*2), whole step and per kernel, CUDA events."""
+    wl = RnntLogitsWorkload(cfg, 0)
+    for _ in range(3):
+        wl.step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+    e0.record()
+    for _ in range(steps):
+        wl.step()
+    e1.record()
+    e1.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    roof = wl.roofline(pk, ms)
+    desc, l2 = wl.describe()
+    return {"value": cfg["B"] / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "workload": desc, "l2": l2,
+            "algorithmic_bytes_per_step": wl.algorithmic_bytes(),
+            "step_frac_of_hbm_roofline": roof["step_frac_of_hbm_roofline"],
+            "kernel_ms": roof["kernel_ms"],
+            "kernel_frac_of_hbm_peak": {
+                "rnnt_grad_kernel": roof["frac"],
+                "rnnt_logprobs_kernel": roof["other"]["rnnt_logprobs_kernel"]["frac"]},
+            "hbm_peak_gbs": pk["hbm"], "peak_source": pk["source"]}
+
+
+def gpu_reference_search(cfg, dev, model, enc, lens):
+    """Per-utterance Python greedy / prefix beam search of the reference (search/greedy_search.py:34-176,
+    prefix_beam_search.py:42-148; restated in oracle/reference.py) with the model ON THE GPU: ~10 kernel
+    launches and a device->host sync per lattice step, i.e. launch-bound.  Baseline leg only."""
+    from oracle import reference as orc
+    om = orc.OracleModel(cfg["V"], cfg["E"], cfg["P"], cfg["J"], 256, 256, 2, blank=0).to(dev).eval()
+    om.load_state_dict(model.state_dict(), strict=False)
+    res = {}
+    T = int(lens[0])
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    n = 2
+    for b in range(n):
+        orc.greedy_search(om, enc[b:b + 1], T, n_steps=64)
+    torch.cuda.synchronize()
+    res["greedy_python_cuda_utts_per_sec"] = n / (time.perf_counter() - t0)
+    t0 = time.perf_counter()
+    orc.prefix_beam_search(om, enc[0:1], beam_size=10)
+    torch.cuda.synchronize()
+    res["beam10_python_cuda_utts_per_sec"] = 1.0 / (time.perf_counter() - t0)
+    res["sample"] = f"greedy: {n} utterances x T={T}; beam 10: 1 utterance x T={T}; model on cuda:0, launch-bound"
+    return res
 
 
 WORKLOADS = {"rnnt_logits": RnntLogitsWorkload, "rnnt_fused": RnntFusedWorkload}
@@ -726,6 +1009,7 @@ def main():
             wl.allreduce(dist)
         return loss
 
+    check = wl.self_check() if hasattr(wl, "self_check") else None
     for _ in range(args.warmup):
         full_step()
     sync_all()
@@ -773,13 +1057,26 @@ def main():
             "config": {"workload": desc, "global_batch": world * B, **cfg,
                        "ragged": bool(args.ragged), "l2": l2, "parallelism": f"dp{world}"},
             "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cb,
-            "clocks": clocks, "loss": float(loss.item()),
+            "clocks": clocks, "loss": float(loss.item()), "self_check": check,
         }
         if not args.no_extras and world == 1:
-            try:
-                line["extra"] = extra_rows(cfg, wl.dev, pk)
-            except Exception as exc:  # secondary rows never hide the headline
-                line["extra"] = {"error": repr(exc)}
+            dev = wl.dev
+            del wl, loss
+            torch.cuda.empty_cache()
+            extra = {}
+            for name, fn in (("rows", lambda: extra_rows(cfg, dev, pk)),
+                             ("rnnt_logits", lambda: logits_row(cfg, pk)),
+                             ("gpu_reference", lambda: gpu_reference(cfg, dev, pk))):
+                try:  # secondary rows never hide the headline
+                    r = fn()
+                    if name == "rows":
+                        extra.update(r)
+                    else:
+                        extra[name] = r
+                except Exception as exc:  # noqa: BLE001
+                    extra[name] = {"error": repr(exc)[:400]}
+                torch.cuda.empty_cache()
+            line["extra"] = extra
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()

@@ -1,0 +1,180 @@
+"""GPU parity on the code paths bench.py actually times ("next round" item 1).
+
+The persistent joint / dW / dH kernels walk many 128-cell tiles per CTA at cfg3; the small
+shapes of test_joint_gpu.py never make a CTA process a second tile.  Here:
+
+  * ``_max_ctas`` caps the persistent grids so that every CTA walks >= 10 tiles (A-staging
+    phase flips, TMEM accumulator phase wrap, H-store drain, dW K-split units, dH tile ranges);
+  * cfg3- and cfg2-shaped slices (B=2, full T/U/V/J) run against the fp32 reference chain
+    TransducerJoint.forward + torchaudio.functional.rnnt_loss (transducer.py:132-147) on the host;
+  * the running-maximum epilogue (taken when max_v(|W_v|_1 + |b_v|) * log2(e) >= 100, or when no
+    bound is supplied) is forced;
+  * the multi-chunk backward loop is forced through a small SCRATCH_BYTES;
+  * greedy and beam-10 decode bench.py's own cfg4 model (V=5000, T=500) against the oracle.
+
+Tolerance: bf16 MMA operands -> north_star's bf16 bar, rtol 1e-2 (relative L2 and max-abs
+relative to the largest entry for gradients).
+"""
+import copy
+
+import numpy as np
+import pytest
+import torch
+import torchaudio
+
+from oracle import reference as orc
+from test_joint_gpu import _case, _close, _mine, _reference
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _mine_kw(case, reduction="none", **kw):
+    from wenet_celoss_b200 import fused_joint_rnnt_loss
+    joint, enc, pred, tgt, tl, ul = case
+    j = copy.deepcopy(joint).to(DEV)
+    enc = enc.to(DEV).requires_grad_(True)
+    pred = pred.to(DEV).requires_grad_(True)
+    loss = fused_joint_rnnt_loss(j, enc, pred, tgt.to(DEV), tl.to(DEV), ul.to(DEV), blank=0,
+                                 reduction=reduction, **kw)
+    loss.sum().backward()
+    grads = {"enc": enc.grad.cpu(), "pred": pred.grad.cpu()}
+    grads.update({n: p.grad.cpu() for n, p in j.named_parameters()})
+    return loss.detach().cpu(), grads
+
+
+def _check(case, **kw):
+    ref_loss, ref_g = _reference(*case, reduction="none")
+    loss, g = _mine_kw(case, **kw)
+    np.testing.assert_allclose(loss.numpy(), ref_loss.numpy(), rtol=1e-2)
+    for k in ref_g:
+        _close(k, g[k], ref_g[k])
+    _, _, _, _, tl, ul = case
+    for b in range(len(tl)):  # padded frames / labels receive exactly zero gradient
+        assert torch.count_nonzero(g["enc"][b, tl[b]:]) == 0
+        assert torch.count_nonzero(g["pred"][b, ul[b] + 1:]) == 0
+    return loss, g
+
+
+@pytest.mark.parametrize("max_ctas", [2, 4])
+@pytest.mark.parametrize("ragged", [False, True])
+def test_many_tiles_per_cta(max_ctas, ragged):
+    """9000 cells = 71 tiles of 128 over 2 / 4 persistent CTAs (>= 17 tiles each); the dW kernel
+    runs 3 V tiles x 2 K splits = 3 units per pair with max_ctas = 4."""
+    case = _case(3, 50, 59, 700, 64, 512, seed=11, ragged=ragged)
+    _check(case, _max_ctas=max_ctas)
+
+
+def test_many_tiles_j256():
+    case = _case(2, 40, 63, 1100, 64, 256, seed=12, ragged=True)
+    _check(case, _max_ctas=2)
+
+
+@pytest.mark.parametrize("ragged", [False, True])
+def test_cfg3_slice(ragged):
+    """B=2 of the headline shape: T=500, U=100, V=5000, E=P=256, J=512 (2 GB of fp32 logits on the
+    host for the reference chain).  790 tiles over 148 CTAs: 5-6 tiles per CTA, last wave partial."""
+    case = _case(2, 500, 100, 5000, 256, 512, seed=13, ragged=ragged)
+    _check(case)
+
+
+def test_cfg2_slice():
+    """B=2 of cfg2: T=250, U=40, V=4233 (vocabulary tail tile of 9 classes), J=512."""
+    case = _case(2, 250, 40, 4233, 256, 512, seed=14, ragged=True)
+    _check(case)
+
+
+def test_running_max_epilogue_large_weights():
+    """ffn_out scaled until max_v(|W_v|_1 + |b_v|) * log2(e) > 100: the forward epilogue must take
+    the running-maximum branch by itself."""
+    from wenet_celoss_b200.joint import _pad_bias, joint_logit_bound
+    case = _case(3, 30, 10, 700, 64, 512, seed=15, ragged=True)
+    joint = case[0]
+    with torch.no_grad():
+        joint.ffn_out.weight.mul_(5.0)  # x2 in _case -> x10 of the default init
+    w = joint.ffn_out.weight.to(DEV).to(torch.bfloat16).contiguous()
+    bound = joint_logit_bound(w, _pad_bias(joint.ffn_out.bias.to(DEV), 700), 700)
+    assert float(bound) * 1.4427 > 100.0, float(bound)
+    _check(case)
+    _check(case, _max_ctas=3)
+
+
+def test_running_max_epilogue_no_bound():
+    """use_bound=False: same inputs as the fast path, results must agree with it and the reference."""
+    case = _case(3, 30, 10, 700, 64, 512, seed=16, ragged=True)
+    slow, gs = _check(case, _use_bound=False)
+    fast, gf = _mine_kw(case)
+    np.testing.assert_allclose(slow.numpy(), fast.numpy(), rtol=1e-5)
+    for k in gs:
+        _close(k, gs[k], gf[k], tol=1e-3)
+
+
+def test_multi_chunk_backward(monkeypatch):
+    """SCRATCH_BYTES forced small: 5 utterances in chunks of 2 + a ragged last chunk of 1;
+    dW, d b_out and d p accumulate across chunks."""
+    from wenet_celoss_b200 import joint as jmod
+    case = _case(5, 24, 9, 700, 64, 512, seed=17, ragged=True)
+    per_utt, ldg = 24 * 10, 704
+    monkeypatch.setattr(jmod, "SCRATCH_BYTES", 2 * per_utt * ldg * 2 + 64)
+    assert jmod._chunk_utts(5, per_utt, ldg, 148) <= 2
+    _check(case)
+    _check(case, _max_ctas=2)
+
+
+# ----------------------------------------------------------------------------- cfg4 searches
+def _bench_search_model():
+    """bench.py's own cfg4 model and an OracleModel carrying the same weights."""
+    import bench
+    torch.manual_seed(4321)
+    cfg = dict(bench.CFG3)
+    m = bench._SearchModel(cfg).eval()
+    om = orc.OracleModel(cfg["V"], cfg["E"], cfg["P"], cfg["J"], 256, 256, 2, blank=0).eval()
+    missing = om.load_state_dict(m.state_dict(), strict=False)
+    assert not missing.unexpected_keys and not missing.missing_keys, missing
+    return cfg, m, om
+
+
+def test_greedy_cfg4_shape_vs_oracle():
+    """V=5000, T=500 (the bench's decode), 4 utterances: token lists identical.  An utterance whose
+    oracle run saw a top-2 margin below 1e-5 is reported, not failed (sub-ulp tie)."""
+    from wenet_celoss_b200 import greedy_search_batch
+    cfg, m, om = _bench_search_model()
+    g = torch.Generator().manual_seed(4321)
+    B, T = 4, 500
+    enc = torch.randn(B, T, cfg["E"], generator=g) * 2.0
+    lens = torch.tensor([500, 500, 431, 377], dtype=torch.int32)
+    got = greedy_search_batch(m.to(DEV), enc.to(DEV), lens.to(DEV), n_steps=64)
+    ties = []
+    for b in range(B):
+        want, margin = orc.greedy_search(om, enc[b:b + 1, :lens[b]], int(lens[b]), n_steps=64,
+                                         record_margin=True)
+        assert len(want) > 20  # the synthetic model really emits symbols
+        if got[b] != want:
+            if margin < 1e-5:
+                ties.append((b, margin))
+                continue
+            raise AssertionError(f"utt {b}: token lists differ (min top-2 margin {margin:.3e})")
+    assert len(ties) <= 1, ties
+
+
+def test_beam10_cfg4_shape_vs_oracle():
+    """beam 10, V=5000, T=500, 2 utterances: n-best token lists identical, scores rtol 1e-5."""
+    from wenet_celoss_b200 import prefix_beam_search_batch
+    cfg, m, om = _bench_search_model()
+    g = torch.Generator().manual_seed(99)
+    B, T = 2, 500
+    enc = torch.randn(B, T, cfg["E"], generator=g) * 2.0
+    lens = torch.tensor([500, 389], dtype=torch.int32)
+    beams = prefix_beam_search_batch(m.to(DEV), enc.to(DEV), lens.to(DEV), beam_size=10)
+    for b in range(B):
+        want = orc.prefix_beam_search(om, enc[b:b + 1, :lens[b]], beam_size=10)
+        got_h, want_h = [s.hyp for s in beams[b]], [s.hyp for s in want]
+        if got_h != want_h:
+            # n-best ORDER may differ only between hypotheses whose scores tie to fp32 rounding
+            ws = {tuple(s.hyp): s.score for s in want}
+            assert sorted(map(tuple, got_h)) == sorted(map(tuple, want_h)), b
+            for s in beams[b]:
+                np.testing.assert_allclose(s.score, ws[tuple(s.hyp)], rtol=1e-5)
+            continue
+        np.testing.assert_allclose([s.score for s in beams[b]], [s.score for s in want], rtol=1e-5)
+        assert len(want[0].hyp) > 20

@@ -105,7 +105,9 @@ def test_transducer_score_and_decoders():
     # decoders: batch of 2 through the model-level entry points
     enc = torch.randn(2, T, 32, generator=g) * 2
     lens = torch.tensor([T, 11])
-    hyps_g = tm.greedy_search(enc.to(DEV), lens.to(DEV), n_steps=4)
+    # (hyps, dist) as transducer.py:598; no ContextBias on this model -> upstream decode, dist 0
+    hyps_g, dist = tm.greedy_search(enc.to(DEV), lens.to(DEV), -1, -1, False, 4)
+    assert dist == 0
     for b in range(2):
         assert hyps_g[b] == orc.greedy_search(om, enc[b:b + 1, :lens[b]], int(lens[b]), n_steps=4)
     best = tm.beam_search(enc[:1].to(DEV), lens[:1].to(DEV), beam_size=5)

@@ -386,12 +386,9 @@ extern "C" int b200_joint_dw(const void* G, int ldg, const void* H, int ldh, lon
   P.nsplit = best;
   P.dW = dW;
   const int smem = dw::kStages * dw::stage_bytes(J) + 1024;
-  static bool attr_set = false;
-  if (!attr_set) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(dw::joint_dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         dw::kStages * dw::stage_bytes(dw::kMaxJ) + 1024));
-    attr_set = true;
-  }
+  // per device, and cheap: set on every call (a process may drive several GPUs)
+  B200_CHECK_CUDA(cudaFuncSetAttribute(dw::joint_dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dw::kStages * dw::stage_bytes(dw::kMaxJ) + 1024));
   int grid = 2 * npairs;
   if (P.nvt * P.nsplit < npairs) grid = 2 * P.nvt * P.nsplit;
   dw::joint_dw_kernel<<<grid, dw::kThreads, smem, (cudaStream_t)stream>>>(gmap, hmap, P);

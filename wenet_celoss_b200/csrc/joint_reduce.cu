@@ -121,12 +121,9 @@ extern "C" int b200_joint_dz_reduce(const float* dH, const void* H, int ldh, int
                  "b200_joint_dz_reduce: dH, de, dp must be 16-byte aligned, H 8-byte aligned");
   const size_t smem = ((size_t)U1 * 32 + kDzPh * 32) * sizeof(float4);
   B200_CHECK_ARG(smem <= 200 * 1024, "b200_joint_dz_reduce: U+1 = %d too large for shared memory", U1);
-  static bool attr_set = false;
-  if (!attr_set) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(joint_dz_reduce_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_set = true;
-  }
+  // per device, and cheap: set on every call (a process may drive several GPUs)
+  B200_CHECK_CUDA(cudaFuncSetAttribute(joint_dz_reduce_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   // frames per CTA: about 8 CTAs per SM, but at least 4 frames (bounds the d p atomics)
   int sms = 148;
   {

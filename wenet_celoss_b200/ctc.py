@@ -11,6 +11,7 @@ from __future__ import annotations
 import types
 
 import torch
+from torch.amp import custom_bwd, custom_fwd
 import torch.nn.functional as F
 
 from . import _lib
@@ -19,6 +20,7 @@ from ._lib import i32, ptr
 
 class _CtcLossFn(torch.autograd.Function):
     @staticmethod
+    @custom_fwd(device_type="cuda")
     def forward(ctx, logits, ys_pad, hlens, ys_lens, blank):
         B, T, V = logits.shape
         Lmax = ys_pad.size(1)
@@ -44,6 +46,7 @@ class _CtcLossFn(torch.autograd.Function):
         return nll
 
     @staticmethod
+    @custom_bwd(device_type="cuda")
     def backward(ctx, dy):
         logits, ys_pad, hlens, ys_lens, lse, lp_ext, alpha, beta, frame_off, leader = ctx.saved_tensors
         B, T, V = logits.shape
@@ -80,6 +83,14 @@ def ctc_loss(logits: torch.Tensor, ys_pad: torch.Tensor, hlens: torch.Tensor, ys
     ys = ys_pad.to(device=dev, dtype=torch.int64).contiguous()
     hl = hlens.to(device=dev, dtype=torch.int32).contiguous()
     yl = ys_lens.to(device=dev, dtype=torch.int32).contiguous()
+    # lengths beyond the tensors would run the trellis kernels out of bounds; torch.nn.CTCLoss raises too
+    mx = torch.stack([hl.max(), yl.max(), -hl.min(), -yl.min()]).tolist()
+    if mx[0] > logits.size(1) or mx[2] > 0:
+        raise RuntimeError(f"Expected input_lengths to have value at most {logits.size(1)}, but got value "
+                           f"{mx[0] if mx[0] > logits.size(1) else -mx[2]} (while checking arguments for ctc_loss)")
+    if mx[1] > ys.size(1) or mx[3] > 0:
+        raise RuntimeError(f"Expected target_lengths to have value at most {ys.size(1)}, but got value "
+                           f"{mx[1] if mx[1] > ys.size(1) else -mx[3]} (while checking arguments for ctc_loss)")
     nll = _CtcLossFn.apply(logits, ys, hl, yl, int(blank))
     if reduction == "sum":
         return nll.sum()

@@ -12,6 +12,7 @@ from __future__ import annotations
 import ctypes
 
 import torch
+from torch.amp import custom_bwd, custom_fwd
 
 from . import _lib
 from ._lib import i32, ptr
@@ -19,12 +20,16 @@ from ._lib import i32, ptr
 
 class _CeLossFn(torch.autograd.Function):
     @staticmethod
+    @custom_fwd(device_type="cuda", cast_inputs=torch.float32)
     def forward(ctx, logits, labels, ignore_index):
         B, C, U = logits.shape
         dev = logits.device
         with torch.cuda.device(dev):
             x = logits.detach().float().contiguous()
             y = labels.to(device=dev, dtype=torch.int64).contiguous()
+            # nn.CrossEntropyLoss asserts on the device for labels outside [0, C); so does this path
+            torch._assert_async(((y == ignore_index) | ((y >= 0) & (y < C))).all(),
+                                "hw_ce_loss: label out of range [0, C) and not ignore_index")
             out = torch.empty(2, dtype=torch.float32, device=dev)
             _lib.call("b200_ce_loss_fwd", ptr(x), ptr(y), i32(B), i32(C), i32(U),
                       ctypes.c_longlong(ignore_index), ptr(out[0:1]), ptr(out[1:2]),
@@ -35,6 +40,7 @@ class _CeLossFn(torch.autograd.Function):
         return out[0].clone()
 
     @staticmethod
+    @custom_bwd(device_type="cuda")
     def backward(ctx, dy):
         x, y, out = ctx.saved_tensors
         B, C, U = x.shape

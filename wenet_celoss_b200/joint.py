@@ -25,6 +25,7 @@ rtol 1e-2 (north_star's bf16 bar).
 from __future__ import annotations
 
 import torch
+from torch.amp import custom_bwd, custom_fwd
 import torch.nn.functional as F
 
 from . import _lib
@@ -94,7 +95,9 @@ def joint_dw(G, H, n, V, J, dW, max_ctas: int = 0):
 
 class _FusedJointLossFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, e, p, w_out, b_out, targets, logit_lengths, target_lengths, blank):
+    @custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    def forward(ctx, e, p, w_out, b_out, targets, logit_lengths, target_lengths, blank,
+                max_ctas=0, use_bound=True):
         dev = e.device
         with torch.cuda.device(dev):
             e32 = e.detach().float().contiguous()
@@ -108,15 +111,18 @@ class _FusedJointLossFn(torch.autograd.Function):
             H = (torch.empty(e32.shape[0] * e32.shape[1] * p32.shape[1], J, dtype=torch.bfloat16, device=dev)
                  if need_grad else None)
             lse, lpb, lpe = joint_logprobs(e32, p32, w_bf16, bias_pad, targets, logit_lengths,
-                                           target_lengths, V, blank, H=H)
+                                           target_lengths, V, blank, max_ctas=max_ctas,
+                                           use_bound=use_bound, H=H)
             alpha, beta, costs, diag_off = rnnt_lattice(lpb, lpe, logit_lengths, target_lengths)
         ctx.save_for_backward(e32, p32, w_bf16, bias_pad, targets, logit_lengths, target_lengths,
                               lse, alpha, beta, diag_off, H)
         ctx.blank = blank
+        ctx.max_ctas = max_ctas  # tests only: fewer persistent CTAs -> more tiles per CTA
         ctx.in_dtypes = (e.dtype, p.dtype, w_out.dtype, b_out.dtype)
         return costs
 
     @staticmethod
+    @custom_bwd(device_type="cuda")
     def backward(ctx, dy):
         (e32, p32, w_bf16, bias_pad, targets, logit_lengths, target_lengths, lse, alpha, beta,
          diag_off, H_all) = ctx.saved_tensors
@@ -151,17 +157,17 @@ class _FusedJointLossFn(torch.autograd.Function):
                 _lib.call("b200_joint_grad_chunk_h", ptr(e32), ptr(p32), ptr(w_bf16), ptr(bias_pad),
                           ptr(targets), ptr(coef), i32(B), i32(T), i32(U1), i32(V), i32(J),
                           i32(blank), _i64(b0 * per_utt), _i64(n), ptr(G), i32(ldg), ptr(H), i32(ldh),
-                          ptr(db_part), i32(0), st)
+                          ptr(db_part), i32(ctx.max_ctas), st)
                 dH = torch.mm(G[:n, :V], w_bf16, out_dtype=torch.float32)  # [n, J]
                 if own_dw:
-                    joint_dw(G, H, n, V, J, dW)
+                    joint_dw(G, H, n, V, J, dW, max_ctas=ctx.max_ctas)
                 else:
                     dW += torch.mm(G[:n, :V].t(), H[:n], out_dtype=torch.float32)
                 _lib.call("b200_joint_dz_reduce", ptr(dH), ptr(H), i32(ldh), i32(b1 - b0), i32(T),
                           i32(U1), i32(J), ptr(de[b0:b1]), ptr(dp[b0:b1]), st)
         dt_e, dt_p, dt_w, dt_b = ctx.in_dtypes
         return (de.to(dt_e), dp.to(dt_p), dW.to(dt_w), db_part.sum(0)[:V].to(dt_b), None,
-                None, None, None)
+                None, None, None, None, None)
 
 
 def _check_joint_module(joint) -> None:
@@ -183,11 +189,15 @@ def _check_joint_module(joint) -> None:
 def fused_joint_rnnt_loss(joint, enc_out: torch.Tensor, pred_out: torch.Tensor,
                           targets: torch.Tensor, logit_lengths: torch.Tensor,
                           target_lengths: torch.Tensor, blank: int = 0,
-                          reduction: str = "mean") -> torch.Tensor:
+                          reduction: str = "mean", *, _max_ctas: int = 0,
+                          _use_bound: bool = True) -> torch.Tensor:
     """RNN-T loss of ``joint(enc_out, pred_out)`` without materialising the logits.
 
     enc_out [B,T,E], pred_out [B,U+1,P]; targets [B,U] int32 zero-padded; lengths int32
-    (exactly what transducer.py:137-141 prepares for torchaudio)."""
+    (exactly what transducer.py:137-141 prepares for torchaudio).
+
+    ``_max_ctas`` / ``_use_bound`` are test hooks: cap the persistent grids (so that every CTA
+    walks many tiles on small shapes) and force the running-maximum epilogue."""
     if reduction not in ("none", "mean", "sum"):
         raise ValueError('reduction should be one of "none", "mean", or "sum"')
     _check_joint_module(joint)
@@ -202,7 +212,8 @@ def fused_joint_rnnt_loss(joint, enc_out: torch.Tensor, pred_out: torch.Tensor,
     e = joint.enc_ffn(enc_out)    # [B,T,J]   library GEMM (joint.py:55)
     p = joint.pred_ffn(pred_out)  # [B,U1,J]  library GEMM (joint.py:56)
     costs = _FusedJointLossFn.apply(e, p, joint.ffn_out.weight, joint.ffn_out.bias, targets,
-                                    logit_lengths, target_lengths, int(blank))
+                                    logit_lengths, target_lengths, int(blank), int(_max_ctas),
+                                    bool(_use_bound))
     if reduction == "mean":
         return costs.mean()
     if reduction == "sum":

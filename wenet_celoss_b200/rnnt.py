@@ -13,6 +13,7 @@ traffic per fwd+bwd instead of >= 6*N*s).
 from __future__ import annotations
 
 import torch
+from torch.amp import custom_bwd, custom_fwd
 
 from . import _lib
 from ._lib import c_void_p, f32, i32, ptr
@@ -90,6 +91,7 @@ def rnnt_grad_coef(lse, alpha, beta, diag_off, dy, targets, logit_lengths, targe
 
 class _RnntLossFn(torch.autograd.Function):
     @staticmethod
+    @custom_fwd(device_type="cuda")
     def forward(ctx, logits, targets, logit_lengths, target_lengths, blank, clamp):
         B, T, U1, V = logits.shape
         dev = logits.device
@@ -111,6 +113,7 @@ class _RnntLossFn(torch.autograd.Function):
         return costs.to(torch.float16) if logits.dtype == torch.float16 else costs
 
     @staticmethod
+    @custom_bwd(device_type="cuda")
     def backward(ctx, dy):
         logits, targets, logit_lengths, target_lengths, lse, alpha, beta, diag_off = ctx.saved_tensors
         B, T, U1, V = logits.shape

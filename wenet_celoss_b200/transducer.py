@@ -114,29 +114,44 @@ def transducer_score(self, encoder_out: torch.Tensor, encoder_mask: torch.Tensor
 @torch.no_grad()
 def transducer_greedy_search(self, speech: torch.Tensor, speech_lengths: torch.Tensor,
                              decoding_chunk_size: int = -1, num_decoding_left_chunks: int = -1,
-                             simulate_streaming: bool = False, n_steps: int = 64, **_unused):
-    """Batched greedy decode: returns one token list per utterance."""
+                             simulate_streaming: bool = False, n_steps: int = 64,
+                             context_list: Optional[torch.Tensor] = None,
+                             context_lengths: Optional[torch.Tensor] = None,
+                             context_filter_state: str = "on",
+                             context_decoder_labels_padded: Optional[torch.Tensor] = None):
+    """``Transducer.greedy_search`` (transducer.py:515-598): same positional order and defaults -
+    ``context_filter_state='on'`` (the fork's gated decode with go-back), context tensors defaulting to
+    ``IntTensor([0])`` - and the same return shape ``(hyps, dist)``: ``dist`` = edit distance between
+    ``context_decoder_labels_padded`` (default ``[0]``) and the gate decisions (greedy_search.py:174),
+    0 for loss modes that return no distance (transducer.py:589-598).  Batched: ``hyps`` holds one
+    token list per utterance (the reference asserts batch == 1) and ``dist`` is a list when B > 1.
+
+    A model WITHOUT a ``ContextBias`` cannot run the gate; it decodes with the upstream algorithm
+    ("greedy_search copy.py":6-63) and returns ``dist = 0``."""
     assert speech.shape[0] == speech_lengths.shape[0]
     assert decoding_chunk_size != 0
+    if context_filter_state not in ("on", "off"):
+        raise ValueError("context_filter_state must be 'on' or 'off'")
+    _ = simulate_streaming
     encoder_out, encoder_mask = self.encoder(speech, speech_lengths, decoding_chunk_size,
                                              num_decoding_left_chunks)
     encoder_out_lens = encoder_mask.squeeze(1).sum(1)
-    # the reference defaults to the gated decode (transducer.py:525); here the gate is opt-in so that
-    # models without a ContextBias keep decoding with the upstream algorithm
-    labels = _unused.get("context_decoder_labels_padded")
-    out = greedy_search_batch(self, encoder_out, encoder_out_lens, n_steps=n_steps,
-                              context_list=_unused.get("context_list"),
-                              context_lengths=_unused.get("context_lengths"),
-                              context_filter_state=_unused.get("context_filter_state", "off"),
-                              return_decisions=labels is not None)
-    if labels is None:
-        return out
-    # the fork's return shape (transducer.py:598, recognize.py:278-290): (hyps, dist), dist = edit
-    # distance between the hot-word labels and the gate decisions (greedy_search.py:174); a batch
-    # returns one distance per utterance
-    from .search import edit_distance
-    hyps, decisions = out
-    lab_t = torch.as_tensor(labels)
+    from .search import _has_hotword_bias, edit_distance
+    if not _has_hotword_bias(self):
+        return greedy_search_batch(self, encoder_out, encoder_out_lens, n_steps=n_steps), 0
+    if context_list is None:
+        context_list = torch.IntTensor([0])
+    if context_lengths is None:
+        context_lengths = torch.IntTensor([0])
+    if context_decoder_labels_padded is None:
+        context_decoder_labels_padded = torch.IntTensor([0])
+    hyps, decisions = greedy_search_batch(self, encoder_out, encoder_out_lens, n_steps=n_steps,
+                                          context_list=context_list, context_lengths=context_lengths,
+                                          context_filter_state=context_filter_state,
+                                          return_decisions=True)
+    if getattr(self, "loss_mode", "pred") not in ("pred", "both"):
+        return hyps, 0  # transducer.py:589-598: this branch returns the hypotheses only, dist stays 0
+    lab_t = torch.as_tensor(context_decoder_labels_padded)
     per_utt = lab_t.dim() > 1 and lab_t.size(0) == len(hyps)
     lab = lab_t.reshape(len(hyps), -1).tolist() if per_utt else [lab_t.reshape(-1).tolist()] * len(hyps)
     dist = [edit_distance(lab[b], decisions[b]) for b in range(len(hyps))]
