@@ -200,6 +200,17 @@ int b200_joint_dz_reduce(const float* dH, const void* H, int ldh, int nb, int T,
 int b200_joint_dw(const void* G, int ldg, const void* H, int ldh, long long n, int V, int J,
                   float* dW, int max_ctas, b200_stream_t stream);
 
+/* hidden-side gradient of the fused joint for one chunk of nb whole utterances, in ONE kernel:
+ * dH = G W_out (autograd of ffn_out, joint.py:68-69), dZ = dH * (1 - H^2) (tanh, joint.py:63-64),
+ * de [nb,T,J] += sum_u dZ, dp [nb,U1,J] += sum_t dZ (broadcast add, joint.py:58-60) - both outputs are
+ * ACCUMULATED with fp32 atomics: zero them first.  G [nb*T*U1, ldg] bf16, H [nb*T*U1, ldh] bf16 as
+ * written by b200_joint_grad_chunk / b200_joint_fwd_h, w_bf16 [V, J].  2-CTA tcgen05 kernel computing
+ * the product transposed (TMEM lane = j, columns = cells); J must be 256 or 512.  logit_len / target_len
+ * (optional, [nb]) let it skip tiles beyond an utterance's lengths, where G is exactly zero. */
+int b200_joint_dh(const void* G, int ldg, const void* w_bf16, const void* H, int ldh, int nb, int T,
+                  int U1, int V, int J, const int32_t* logit_len, const int32_t* target_len,
+                  float* de, float* dp, int max_ctas, b200_stream_t stream);
+
 /* ---- Batched RNN-T greedy search ------------------------------------------
  * replaces the Python loop of wenet/transducer/search/greedy_search.py:34-176 (core
  * algorithm: "greedy_search copy.py":6-63): per lattice step predictor.forward_step

@@ -56,10 +56,10 @@ def test_c_caller_decodes_fixture(tmp_path, golden):
     fx = tmp_path / "fixture.bin"
     with open(fx, "wb") as f:
         f.write(struct.pack("<10i", B, T, mt["V"], mt["Emb"], mt["H"], mt["L"], mt["J"], 0, n_steps, max_tokens))
-        f.write(enc_proj.cpu().numpy().astype("<f4").tobytes())
+        f.write(enc_proj.detach().cpu().numpy().astype("<f4").tobytes())
         f.write(lens.numpy().astype("<i4").tobytes())
         for t in [mt["embed"], *mt["lstm"], mt["w_c"], mt["b_c"], mt["w_out"], mt["b_out"]]:
-            f.write(t.cpu().numpy().astype("<f4").tobytes())
+            f.write(t.detach().cpu().numpy().astype("<f4").tobytes())
     exe = _build(tmp_path)
     out = tmp_path / "out.bin"
     r = subprocess.run([str(exe), str(fx), str(out)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT,

@@ -34,6 +34,7 @@ from .rnnt import rnnt_grad_coef, rnnt_lattice
 
 _TILE_N = 256
 _TILE_M = 128
+_FORCE_LIBRARY_DH = False  # debugging aid: compare joint_dh_kernel with torch.mm + joint_dz_reduce
 SCRATCH_BYTES = 20 << 30  # bound on the bf16 G scratch of the backward pass (cfg3: 16.2 GB, one chunk)
 
 
@@ -147,8 +148,9 @@ class _FusedJointLossFn(torch.autograd.Function):
             db_part = torch.zeros(16, (V + _TILE_M - 1) // _TILE_M * _TILE_M, dtype=torch.float32,
                                   device=dev)
             own_dw = J % 128 == 0  # csrc/joint_dw.cu; other join dims: library GEMM
+            own_dh = J in (256, 512)  # csrc/joint_dh.cu (the reference's join_dim is 512)
             dW = torch.zeros(V, J, dtype=torch.float32, device=dev)
-            de = torch.empty(B, T, J, dtype=torch.float32, device=dev)
+            de = torch.zeros(B, T, J, dtype=torch.float32, device=dev)
             dp = torch.zeros(B, U1, J, dtype=torch.float32, device=dev)
             for b0 in range(0, B, nb):
                 b1 = min(B, b0 + nb)
@@ -158,13 +160,20 @@ class _FusedJointLossFn(torch.autograd.Function):
                           ptr(targets), ptr(coef), i32(B), i32(T), i32(U1), i32(V), i32(J),
                           i32(blank), _i64(b0 * per_utt), _i64(n), ptr(G), i32(ldg), ptr(H), i32(ldh),
                           ptr(db_part), i32(ctx.max_ctas), st)
-                dH = torch.mm(G[:n, :V], w_bf16, out_dtype=torch.float32)  # [n, J]
                 if own_dw:
                     joint_dw(G, H, n, V, J, dW, max_ctas=ctx.max_ctas)
                 else:
                     dW += torch.mm(G[:n, :V].t(), H[:n], out_dtype=torch.float32)
-                _lib.call("b200_joint_dz_reduce", ptr(dH), ptr(H), i32(ldh), i32(b1 - b0), i32(T),
-                          i32(U1), i32(J), ptr(de[b0:b1]), ptr(dp[b0:b1]), st)
+                if own_dh and not _FORCE_LIBRARY_DH:
+                    # dH = G W, tanh', sums over u / t in one tcgen05 kernel: dH never leaves the SM
+                    _lib.call("b200_joint_dh", ptr(G), i32(ldg), ptr(w_bf16), ptr(H), i32(ldh), i32(b1 - b0),
+                              i32(T), i32(U1), i32(V), i32(J), ptr(logit_lengths[b0:b1]),
+                              ptr(target_lengths[b0:b1]), ptr(de[b0:b1]), ptr(dp[b0:b1]),
+                              i32(ctx.max_ctas), st)
+                else:  # join dims the own kernel does not cover: library GEMM + reduction kernel
+                    dH = torch.mm(G[:n, :V], w_bf16, out_dtype=torch.float32)  # [n, J]
+                    _lib.call("b200_joint_dz_reduce", ptr(dH), ptr(H), i32(ldh), i32(b1 - b0), i32(T),
+                              i32(U1), i32(J), ptr(de[b0:b1]), ptr(dp[b0:b1]), st)
         dt_e, dt_p, dt_w, dt_b = ctx.in_dtypes
         return (de.to(dt_e), dp.to(dt_p), dW.to(dt_w), db_part.sum(0)[:V].to(dt_b), None,
                 None, None, None, None, None)
