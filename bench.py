@@ -423,15 +423,13 @@ class RnntFusedWorkload:
         def k_dw():
             joint_dw(G, H_all, B * per_utt, V, J, dW8)
 
-        de = torch.empty(B, T, J, device=self.dev)
+        de = torch.zeros(B, T, J, device=self.dev)
         dp = torch.zeros(B, U1, J, device=self.dev)
 
-        def k_dh_lib():  # the one library GEMM left in the backward (replaced by joint_dh_kernel)
-            box["dH"] = torch.mm(G[:, :V], w, out_dtype=torch.float32)
-
-        def k_dz():
-            _lib.call("b200_joint_dz_reduce", ptr(box["dH"]), ptr(H_all), i32(J), i32(B), i32(T), i32(U1), i32(J),
-                      ptr(de), ptr(dp), st)
+        def k_dh():  # dH = G.W with tanh' and the sums over u / t in the epilogue: d e, d p
+            de.zero_(); dp.zero_()
+            _lib.call("b200_joint_dh", ptr(G), i32(ldg), ptr(w), ptr(H_all), i32(J), i32(B), i32(T), i32(U1),
+                      i32(V), i32(J), ptr(self.tl), ptr(self.ul), ptr(de), ptr(dp), i32(0), st)
 
         out = {}
         k_fwd(); k_lat()
@@ -440,8 +438,7 @@ class RnntFusedWorkload:
         for name, fn in (("joint_kernel<FWD> (all cells)", k_fwd), ("rnnt_lattice_kernel", k_lat),
                          ("joint_kernel<GRAD> (all cells, one chunk)", k_grad),
                          ("joint_dw_kernel (all cells)", k_dw),
-                         ("library GEMM dH = G.W (cuBLAS)", k_dh_lib),
-                         ("joint_dz_reduce_kernel", k_dz)):
+                         ("joint_dh_kernel (all cells)", k_dh)):
             ts = []
             for _ in range(iters + 1):
                 e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
@@ -757,7 +754,13 @@ def gpu_reference(cfg, dev, pk):
         tgt = torch.randint(1, V, (B, U), generator=g, dtype=torch.int32).to(dev)
         row = {"shape": dict(c), "dtype": dtype_note}
         ours_ms = None
+        # torchaudio's CUDA kernels index the logits with 32-bit ints: B*T*U1*V must stay below 2^31 (cfg3 at
+        # B=32 is 8.08e9 elements and faults with an illegal memory access - observed on this box)
         b_ref = B
+        while b_ref > 1 and b_ref * T * (U + 1) * V >= 2 ** 31:
+            b_ref //= 2
+        row["reference_batch_limit"] = ("largest power-of-two fraction of B with B*T*U1*V < 2^31 "
+                                        "(32-bit indexing in torchaudio's CUDA rnnt_loss)")
         while b_ref >= 1:
             try:
                 torch.cuda.empty_cache()
@@ -806,6 +809,8 @@ def gpu_reference(cfg, dev, pk):
     # (b) rnnt_loss alone on materialised logits: torchaudio CUDA vs this package, same tensor
     for tag, c, dt in (("cfg2_rnnt_loss_fp32", CFG2, torch.float32), ("cfg3_rnnt_loss_fp16", cfg, torch.float16)):
         B, T, U, V = c["B"], c["T"], c["U"], c["V"]
+        while B > 1 and B * T * (U + 1) * V >= 2 ** 31:  # 32-bit indexing in the reference kernel
+            B //= 2
         try:
             torch.cuda.empty_cache()
             logits = torch.empty(B, T, U + 1, V, dtype=dt, device=dev)
@@ -827,7 +832,7 @@ def gpu_reference(cfg, dev, pk):
             ms_ref = _timed_cuda(step(torchaudio.functional.rnnt_loss))
             ms_our = _timed_cuda(step(pkg.rnnt_loss), reps=3)
             nbytes = 3.0 * logits.numel() * logits.element_size()
-            out[tag] = {"reference_ms": ms_ref, "ours_ms": ms_our, "speedup": ms_ref / ms_our,
+            out[tag] = {"B": B, "reference_ms": ms_ref, "ours_ms": ms_our, "speedup": ms_ref / ms_our,
                         "reference_utts_per_sec": B / (ms_ref * 1e-3), "ours_utts_per_sec": B / (ms_our * 1e-3),
                         "ours_frac_of_hbm_roofline": nbytes / (ms_our * 1e-3) / 1e9 / pk["hbm"],
                         "reference_frac_of_hbm_roofline": nbytes / (ms_ref * 1e-3) / 1e9 / pk["hbm"],
