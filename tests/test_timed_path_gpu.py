@@ -48,7 +48,7 @@ def _check(case, tol_inputs=1e-2, **kw):
     loss, g = _mine_kw(case, **kw)
     np.testing.assert_allclose(loss.numpy(), ref_loss.numpy(), rtol=1e-2)
     for k in ref_g:
-        _close(k, g[k], ref_g[k], tol=tol_inputs if k in ("enc", "pred") else 1e-2)
+        _close(k, g[k], ref_g[k], tol=1e-2 if k.startswith("ffn_out") else tol_inputs)
     _, _, _, _, tl, ul = case
     for b in range(len(tl)):  # padded frames / labels receive exactly zero gradient
         assert torch.count_nonzero(g["enc"][b, tl[b]:]) == 0
@@ -75,7 +75,8 @@ def test_cfg3_slice(ragged):
     """B=2 of the headline shape: T=500, U=100, V=5000, E=P=256, J=512 (2 GB of fp32 logits on the
     host for the reference chain).  790 tiles over 148 CTAs: 5-6 tiles per CTA, last wave partial."""
     case = _case(2, 500, 100, 5000, 256, 512, seed=13, ragged=ragged)
-    # d enc_out / d pred_out: measured 0.8-1.3e-2 relative L2 at this shape.  scripts/dbg_prec.py traces it:
+    # everything downstream of d e / d p (d enc_out, d pred_out, enc_ffn / pred_ffn gradients): measured
+    # 0.8-1.3e-2 relative L2 at this shape.  scripts/dbg_prec.py traces it:
     # the kernels reproduce a torch emulation of the bf16 operand roundings to 2e-5 (d p) / 3e-4 (d e); at
     # the e / p level the gradients sit 1.8e-3 / 2.5e-3 from fp32 (W_out's bf16 rounding, coherent over the
     # 500 frames a d p entry sums), and the pred_ffn / enc_ffn backward GEMMs amplify that: the true
