@@ -11,8 +11,11 @@ from pathlib import Path
 
 import torch
 
+import os
+
 _PKG = Path(__file__).resolve().parent
-LIB_PATH = _PKG / "libb200_transducer.so"
+# B200_LIB: load another build of the same library (kernel experiments, scripts/grad_variants.sh)
+LIB_PATH = Path(os.environ["B200_LIB"]) if os.environ.get("B200_LIB") else _PKG / "libb200_transducer.so"
 
 F32, F16, BF16 = 0, 1, 2
 _DTYPES = {torch.float32: F32, torch.float16: F16, torch.bfloat16: BF16}

@@ -65,6 +65,11 @@ template <int MODE> struct Cfg {
   static constexpr int kASlots = MODE == 0 ? 4 : 2;
 // -DB200_GRAD_GBUFS=2: a second G staging tile per epilogue warp (W ring 3 stages to fit). Measured at
 // cfg3, all cells: 8.69 ms against 8.66 ms with one tile -> the TMA-store drain does not bound GRAD.
+// -DB200_GRAD_DBG=bits: timing knock-outs of the GRAD epilogue (results are wrong): 1 = no G store, 2 = no
+// d b_out column sums, 4 = no exponentials (scripts/grad_variants.sh)
+#ifndef B200_GRAD_DBG
+#define B200_GRAD_DBG 0
+#endif
 #ifndef B200_GRAD_GBUFS
 #define B200_GRAD_GBUFS 1
 #endif
