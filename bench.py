@@ -115,7 +115,7 @@ class RnntLogitsWorkload:
     """rnnt_loss(logits, ...) fwd+bwd over materialised bf16 logits (HBM-resident)."""
     name = "rnnt_logits"
 
-    def __init__(self, cfg, rank, ragged=False):
+    def __init__(self, cfg, rank, ragged=False, world=1):
         import wenet_celoss_b200 as pkg
         self.pkg = pkg
         self.cfg = cfg
@@ -212,6 +212,7 @@ class RnntLogitsWorkload:
         l = self.step()
         self.loss_pin.copy_(l.detach().float(), non_blocking=True)
         torch.cuda.current_stream().synchronize()
+        return l
 
     def e2e_bytes(self):
         return int(4 * (self.tgt_pin.numel() + self.tl_pin.numel() + self.ul_pin.numel())), 4
@@ -235,7 +236,7 @@ class RnntLogitsWorkload:
         return ("rnnt_logits: rnnt_loss fwd+bwd over materialised bf16 logits, B=32 T=500 U=100 "
                 "V=5000 per GPU (cfg3)", "inputs (16.2 GB logits) larger than L2")
 
-    def allreduce(self, dist):
+    def allreduce(self, dist, loss):
         return None  # independent utterances, no data-path collective
 
 
@@ -318,16 +319,27 @@ class RnntFusedWorkload:
     name = "rnnt_fused"
     dtype = "bf16"
 
-    def __init__(self, cfg, rank, ragged=False):
+    def __init__(self, cfg, rank, ragged=False, world=1):
         import wenet_celoss_b200 as pkg
+        from wenet_celoss_b200.dist import shard_batch
         self.pkg = pkg
         self.cfg = cfg
         B, T, U, V, E, P, J = (cfg[k] for k in ("B", "T", "U", "V", "E", "P", "J"))
         self.dev = torch.device("cuda", torch.cuda.current_device())
         torch.manual_seed(1234)  # identical replicated weights on every rank
         self.joint = _Joint(V, E, P, J).to(self.dev)
-        g = torch.Generator().manual_seed(1234 + rank)
-        self.tl_h, self.ul_h = synth_lengths(B, T, U, g, ragged)
+        if ragged and world > 1:
+            # ONE global ragged batch of world*B utterances (same seed on every rank), dealt by work
+            # T_b*U_b as dist.shard_batch does (sort by work, round-robin)
+            gg = torch.Generator().manual_seed(1234)
+            tl_g, ul_g = synth_lengths(world * B, T, U, gg, True)
+            idx = shard_batch(world * B, rank, world, weights=(tl_g.double() * (ul_g.double() + 1)).tolist())
+            self.tl_h, self.ul_h = tl_g[idx].contiguous(), ul_g[idx].contiguous()
+            self.tl_h[0], self.ul_h[-1] = T, U  # torchaudio's contract: the maxima equal the tensor sizes
+            g = torch.Generator().manual_seed(1234 + rank)
+        else:
+            g = torch.Generator().manual_seed(1234 + rank)
+            self.tl_h, self.ul_h = synth_lengths(B, T, U, g, ragged)
         self.targets_h = torch.randint(1, V, (B, U), generator=g, dtype=torch.int32)
         self.enc_h = torch.randn(B, T, E, generator=g)
         self.pred_h = torch.randn(B, U + 1, P, generator=g)
@@ -337,7 +349,9 @@ class RnntFusedWorkload:
         self.tl = self.tl_h.to(self.dev)
         self.ul = self.ul_h.to(self.dev)
         self.cells = B * T * (U + 1)
+        self.live_cells = int((self.tl_h.long() * (self.ul_h.long() + 1)).sum())
         self.params = list(self.joint.parameters())
+        self.reduction = "sum" if world > 1 else "mean"
 
     def step(self):
         self.enc.grad = None
@@ -345,16 +359,17 @@ class RnntFusedWorkload:
         for p in self.params:
             p.grad = None
         loss = self.pkg.fused_joint_rnnt_loss(self.joint, self.enc, self.pred, self.targets, self.tl,
-                                              self.ul, blank=0, reduction="mean")
+                                              self.ul, blank=0, reduction=self.reduction)
         loss.backward()
         return loss
 
-    def allreduce(self, dist):
-        """What DDP does for these parameters (wenet/bin/train.py:231): one flat all-reduce of the
-        joint weight gradients + the scalar loss over NCCL."""
-        flat = torch.cat([p.grad.reshape(-1) for p in self.params])
-        dist.all_reduce(flat)
-        return flat
+    def allreduce(self, dist, loss):
+        """The package's own exchange (wenet_celoss_b200/dist.py: what DDP does for these parameters at
+        wenet/bin/train.py:231): gradients of the local SUM of costs + {sum, batch} in ONE flat NCCL
+        all-reduce, then the global mean.  Returns the global mean loss."""
+        from wenet_celoss_b200.dist import allreduce_step
+        mean, _ = allreduce_step(self.params, loss.detach(), self.cfg["B"])
+        return mean
 
     def e2e_setup(self):
         self.pins = [t.pin_memory() for t in (self.enc_h, self.pred_h, self.targets_h, self.tl_h,
@@ -368,6 +383,7 @@ class RnntFusedWorkload:
         l = self.step()
         self.loss_pin.copy_(l.detach().float(), non_blocking=True)
         torch.cuda.current_stream().synchronize()
+        return l
 
     def e2e_bytes(self):
         return int(sum(t.numel() * t.element_size() for t in self.pins)), 4
@@ -946,7 +962,144 @@ def gpu_reference_search(cfg, dev, model, enc, lens):
     return res
 
 
-WORKLOADS = {"rnnt_logits": RnntLogitsWorkload, "rnnt_fused": RnntFusedWorkload}
+# --------------------------------------------------------------------------- sharded secondary workloads
+CFG5 = dict(B=64, T=1000, L=100, V=5000, E=256)
+CFG4 = dict(B=64, T=500, V=5000, E=256, P=256, J=512)
+
+
+class CtcWorkload:
+    """BASELINE configs[4]: CTC.forward + backward (wenet/transformer/ctc.py:46-64), B=64 T=1000 V=5000,
+    utterances sharded over the ranks; the ctc_lo gradients are the only thing that crosses ranks."""
+    name, dtype, base_cfg, metric = "ctc", "f32", CFG5, "ctc_loss_fwd_bwd_utts_per_sec"
+
+    def __init__(self, cfg, rank, ragged=False, world=1):
+        import wenet_celoss_b200 as pkg
+        self.pkg, self.cfg = pkg, cfg
+        B, T, L, V, E = (cfg[k] for k in ("B", "T", "L", "V", "E"))
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        torch.manual_seed(1234)
+        self.ctc = pkg.CTC(V, E).to(self.dev)
+        self.params = list(self.ctc.parameters())
+        g = torch.Generator().manual_seed(4321 + rank)
+        self.hs_h = torch.randn(B, T, E, generator=g)
+        yl = torch.randint(L // 2, L + 1, (B,), generator=g)
+        ys = torch.randint(1, V, (B, L), generator=g)
+        self.ys_h = torch.where(torch.arange(L)[None] < yl[:, None], ys, torch.full_like(ys, -1))
+        hl = torch.full((B,), T, dtype=torch.int32)
+        if ragged:
+            hl = torch.randint(int(0.6 * T), T + 1, (B,), generator=g, dtype=torch.int32)
+            hl[0] = T
+        self.hl_h, self.yl_h = hl, yl.to(torch.int32)
+        self.hs = self.hs_h.to(self.dev).requires_grad_(True)
+        self.ys, self.hl, self.yl = self.ys_h.to(self.dev), self.hl_h.to(self.dev), self.yl_h.to(self.dev)
+
+    def step(self):
+        self.hs.grad = None
+        for p in self.params:
+            p.grad = None
+        loss = self.ctc(self.hs, self.hl, self.ys, self.yl) * self.cfg["B"]  # local SUM of nll
+        loss.backward()
+        return loss
+
+    def allreduce(self, dist, loss):
+        from wenet_celoss_b200.dist import allreduce_step
+        return allreduce_step(self.params, loss.detach(), self.cfg["B"])[0]
+
+    def e2e_setup(self):
+        self.pins = [t.pin_memory() for t in (self.hs_h, self.ys_h, self.hl_h, self.yl_h)]
+        self.loss_pin = torch.empty((), dtype=torch.float32).pin_memory()
+
+    def e2e_step(self):
+        with torch.no_grad():
+            for dst, src in zip((self.hs, self.ys, self.hl, self.yl), self.pins):
+                dst.copy_(src, non_blocking=True)
+        l = self.step()
+        self.loss_pin.copy_(l.detach().float(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return l
+
+    def e2e_bytes(self):
+        return int(sum(t.numel() * t.element_size() for t in self.pins)), 4
+
+    e2e_note = "CTC.forward API: encoder outputs, padded labels and lengths copied from pinned host memory every step"
+
+    def roofline(self, pk, ms_step):
+        c = self.cfg
+        nbytes = 3.0 * c["B"] * c["T"] * c["V"] * 4
+        return {"bound": "hbm", "kernel": "CTC.forward+backward (whole step)", "achieved": nbytes / (ms_step * 1e-3) / 1e9,
+                "peak": pk["hbm"], "unit": "GB/s", "frac": nbytes / (ms_step * 1e-3) / 1e9 / pk["hbm"], "traffic": None,
+                "peak_source": pk["source"], "algorithmic_bytes_per_step": nbytes}
+
+    def describe(self):
+        c = self.cfg
+        return (f"ctc: CTC.forward+backward B={c['B']} T={c['T']} V={c['V']} L<={c['L']} per GPU (cfg5), fp32",
+                "logits (1.28 GB at B=64) larger than L2")
+
+
+class SearchWorkload:
+    """BASELINE configs[3]: batched greedy / prefix beam search (beam 10) over synthetic encoder outputs,
+    utterances sharded over the ranks, no collective (results are gathered on the host by the caller)."""
+    dtype, base_cfg = "f32", CFG4
+    mode = "greedy"
+
+    def __init__(self, cfg, rank, ragged=False, world=1):
+        import wenet_celoss_b200 as pkg
+        self.pkg, self.cfg = pkg, cfg
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        torch.manual_seed(4321)
+        self.model = _SearchModel(dict(CFG3, **cfg)).to(self.dev).eval()
+        g = torch.Generator().manual_seed(4321 + rank)
+        B, T = cfg["B"], cfg["T"]
+        self.enc_h = torch.randn(B, T, cfg["E"], generator=g) * 2.0
+        self.lens_h = torch.full((B,), T, dtype=torch.int32)
+        if ragged:
+            self.lens_h = torch.randint(int(0.6 * T), T + 1, (B,), generator=g, dtype=torch.int32)
+        self.enc, self.lens = self.enc_h.to(self.dev), self.lens_h.to(self.dev)
+        self.metric = f"rnnt_{self.mode}_search_utts_per_sec"
+        self.name = self.mode
+
+    def step(self):
+        if self.mode == "greedy":
+            self.out = self.pkg.greedy_search_batch(self.model, self.enc, self.lens, n_steps=64)
+        else:
+            self.out = self.pkg.prefix_beam_search_batch(self.model, self.enc, self.lens, beam_size=10)
+        return None
+
+    def allreduce(self, dist, loss):
+        return None
+
+    def e2e_setup(self):
+        self.pins = [self.enc_h.pin_memory(), self.lens_h.pin_memory()]
+
+    def e2e_step(self):
+        self.enc.copy_(self.pins[0], non_blocking=True)
+        self.lens.copy_(self.pins[1], non_blocking=True)
+        self.step()  # the token lists come back to the host inside the call
+        return None
+
+    def e2e_bytes(self):
+        n_out = sum(len(h) if self.mode == "greedy" else sum(len(s.hyp) for s in h) for h in self.out)
+        return int(sum(t.numel() * t.element_size() for t in self.pins)), int(4 * n_out)
+
+    e2e_note = "encoder outputs copied from pinned host memory every step; token lists returned as Python lists"
+
+    def roofline(self, pk, ms_step):
+        return {"bound": "hbm", "kernel": f"{self.mode} decode (dependency chain of T + emitted lattice steps; weights "
+                "L2-resident: no bandwidth roofline applies, SURVEY 8d-v)", "achieved": None, "peak": pk["hbm"],
+                "unit": "GB/s", "frac": None, "traffic": None, "peak_source": pk["source"]}
+
+    def describe(self):
+        c = self.cfg
+        return (f"{self.mode}: B={c['B']} T={c['T']} V={c['V']} per GPU (cfg4), random-init predictor/joint"
+                + (", beam=10, ctc 0.3 / rnnt 0.7" if self.mode == "beam" else ""), "weights L2-resident")
+
+
+class BeamWorkload(SearchWorkload):
+    mode = "beam"
+
+
+WORKLOADS = {"rnnt_logits": RnntLogitsWorkload, "rnnt_fused": RnntFusedWorkload, "ctc": CtcWorkload,
+             "greedy": SearchWorkload, "beam": BeamWorkload}
 
 
 # --------------------------------------------------------------------------- main arm
@@ -970,6 +1123,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="rnnt_fused", choices=sorted(WORKLOADS))
     ap.add_argument("--ragged", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: the config's batch PER GPU; strong: the config's batch split over the GPUs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     args = ap.parse_args()
@@ -992,7 +1147,13 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     import wenet_celoss_b200 as pkg
-    wl = WORKLOADS[args.workload](cfg, rank, ragged=args.ragged)
+    wcls = WORKLOADS[args.workload]
+    cfg = dict(getattr(wcls, "base_cfg", CFG3))
+    global_B = cfg["B"] * world if args.scaling == "weak" else cfg["B"]
+    if args.scaling == "strong":
+        assert cfg["B"] % world == 0, "strong scaling splits the config's batch evenly"
+        cfg["B"] //= world
+    wl = wcls(cfg, rank, ragged=args.ragged, world=world)
     pk = peaks()
 
     def sync_all():
@@ -1003,15 +1164,18 @@ def main():
 
     def max_over_ranks(ms):
         if dist is None:
-            return ms
+            return ms, [ms]
         t = torch.tensor([ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        per = [float(x.item()) for x in allt]
+        return max(per), per
 
     def full_step():
         loss = wl.step()
         if dist is not None:
-            wl.allreduce(dist)
+            red = wl.allreduce(dist, loss)
+            loss = red if red is not None else loss
         return loss
 
     check = wl.self_check() if hasattr(wl, "self_check") else None
@@ -1028,7 +1192,7 @@ def main():
         loss = full_step()
     e1.record()
     sync_all()
-    ms = max_over_ranks(e0.elapsed_time(e1))
+    ms, per_rank_ms = max_over_ranks(e0.elapsed_time(e1))
     launches = pkg.launch_count() - n0
     clocks = sampler.stop() if rank == 0 else None
     B = cfg["B"]
@@ -1041,37 +1205,69 @@ def main():
     f0, f1 = torch.cuda.Event(True), torch.cuda.Event(True)
     f0.record()
     for _ in range(args.steps):
-        wl.e2e_step()
+        l_e2e = wl.e2e_step()
         if dist is not None:
-            wl.allreduce(dist)
+            wl.allreduce(dist, l_e2e)
     f1.record()
     sync_all()
-    ms_e2e = max_over_ranks(f0.elapsed_time(f1))
+    ms_e2e, _ = max_over_ranks(f0.elapsed_time(f1))
     h2d, d2h = wl.e2e_bytes()
     e2e = {"value": world * B * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
            "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "note": wl.e2e_note}
 
+    exchange = None
+    if dist is not None and hasattr(wl, "params"):
+        # the collective alone (same flat payload, back to back) and the step WITHOUT it: names what the
+        # weak-scaling loss is made of (max over ranks of power-capped GPUs vs the exchange itself)
+        from wenet_celoss_b200.dist import flatten_grads
+        flat, _ = flatten_grads(wl.params, [torch.zeros(2, device="cuda")])
+        for _ in range(3):
+            dist.all_reduce(flat)
+        sync_all()
+        a0, a1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        a0.record()
+        for _ in range(20):
+            dist.all_reduce(flat)
+        a1.record()
+        sync_all()
+        ar_ms, _ = max_over_ranks(a0.elapsed_time(a1) / 20)
+        c0, c1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        c0.record()
+        for _ in range(args.steps):
+            wl.step()
+        c1.record()
+        sync_all()
+        _, local_ms = max_over_ranks(c0.elapsed_time(c1) / args.steps)
+        exchange = {"payload_bytes": int(flat.numel() * 4), "allreduce_alone_ms": ar_ms,
+                    "step_without_exchange_ms_per_rank": local_ms,
+                    "step_with_exchange_ms_per_rank": [t / args.steps for t in per_rank_ms],
+                    "api": "wenet_celoss_b200.dist.allreduce_step (one flat NCCL all-reduce per step)"}
+
     if rank == 0:
         roof = wl.roofline(pk, ms / args.steps)
-        cb = None if args.no_cpu_baseline else cpu_baseline(cfg)
+        cb = None if args.no_cpu_baseline else cpu_baseline(dict(CFG3))
         desc, l2 = wl.describe()
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": wl.dtype, "data": "synthetic",
-            "config": {"workload": desc, "global_batch": world * B, **cfg,
+            "metric": getattr(wl, "metric", METRIC), "value": value, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": wl.dtype,
+            "data": "synthetic",
+            "config": {"workload": desc, "global_batch": global_B, **cfg,
                        "ragged": bool(args.ragged), "l2": l2, "parallelism": f"dp{world}"},
             "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cb,
-            "clocks": clocks, "loss": float(loss.item()), "self_check": check,
+            "clocks": clocks, "loss": float(loss.item()) if torch.is_tensor(loss) else None,
+            "self_check": check, "exchange": exchange,
         }
-        if not args.no_extras and world == 1:
+        if args.ragged and hasattr(wl, "live_cells"):
+            line["config"]["live_cell_fraction_rank0"] = wl.live_cells / wl.cells
+        if not args.no_extras and world == 1 and args.workload == "rnnt_fused":
             dev = wl.dev
             del wl, loss
             torch.cuda.empty_cache()
             extra = {}
-            for name, fn in (("rows", lambda: extra_rows(cfg, dev, pk)),
-                             ("rnnt_logits", lambda: logits_row(cfg, pk)),
-                             ("gpu_reference", lambda: gpu_reference(cfg, dev, pk))):
+            for name, fn in (("rows", lambda: extra_rows(dict(CFG3), dev, pk)),
+                             ("rnnt_logits", lambda: logits_row(dict(CFG3), pk)),
+                             ("gpu_reference", lambda: gpu_reference(dict(CFG3), dev, pk))):
                 try:  # secondary rows never hide the headline
                     r = fn()
                     if name == "rows":

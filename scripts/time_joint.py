@@ -41,6 +41,14 @@ def grad():
     _lib.call("b200_joint_grad_chunk_h", ptr(e), ptr(p), ptr(w), ptr(bias), ptr(tgt), ptr(coef), i32(B), i32(T),
               i32(U1), i32(V), i32(J), i32(0), _i64(0), _i64(n), ptr(G), i32(ldg), ptr(H), i32(J), ptr(dbp), i32(0), st)
 t_grad = timed(grad)
+from wenet_celoss_b200.joint import joint_dw
+dW = torch.zeros(V, J, device=dev); de = torch.zeros(B, T, J, device=dev); dp = torch.zeros(B, U1, J, device=dev)
+t_dw = timed(lambda: joint_dw(G, H, n, V, J, dW))
+def dh():
+    _lib.call("b200_joint_dh", ptr(G), i32(ldg), ptr(w), ptr(H), i32(J), i32(B), i32(T), i32(U1), i32(V), i32(J),
+              ptr(tl), ptr(ul), ptr(de), ptr(dp), i32(0), st)
+t_dh = timed(dh)
 flops = 2.0 * n * J * V
+print(f"   dW {t_dw:.3f} ms ({flops / t_dw / 1e9:.0f} TF/s)  dH {t_dh:.3f} ms ({flops / t_dh / 1e9:.0f} TF/s)")
 print(f"{os.environ.get('B200_LIB', 'default'):40s} B={B} FWD {t_fwd:.3f} ms ({flops / t_fwd / 1e9:.0f} TF/s)  "
       f"GRAD {t_grad:.3f} ms ({flops / t_grad / 1e9:.0f} TF/s)  costs[0] {costs[0].item():.3f}", flush=True)
