@@ -211,6 +211,90 @@ int b200_joint_dh(const void* G, int ldg, const void* w_bf16, const void* H, int
                   int U1, int V, int J, const int32_t* logit_len, const int32_t* target_len,
                   float* de, float* dp, int max_ctas, b200_stream_t stream);
 
+/* ---- fp32-accurate (split-bf16) tensor-core path -----------------------------------
+ * For the configurations the reference runs in fp32 (BASELINE configs[1]: joint.py:58-69 +
+ * torchaudio rnnt_loss, rtol 1e-4; and the ctc_lo projection + log_softmax + CTCLoss of
+ * wenet/transformer/ctc.py:57-61).  Every GEMM operand is a PAIR of bf16 arrays,
+ * X = X_hi + X_lo with X_hi = bf16(X), X_lo = bf16(X - X_hi), and each product is issued as
+ * hi.hi + lo.hi + hi.lo on tcgen05 with fp32 accumulation (~2^-17 relative operand error; the
+ * few logits the lattices read are recomputed as exact fp32 dot products).  The logits never
+ * reach HBM.  *_lo == NULL everywhere = plain bf16 operands (one product). */
+
+/* x [rows, cols] fp32 (pitch ldx) -> hi, lo [rows, cols] bf16 (pitch ldo) */
+int b200_split_f32(const float* x, long long rows, int cols, long long ldx, void* hi, void* lo,
+                   long long ldo, b200_stream_t stream);
+
+/* x[r,c] = sum_k A[r,k] B[c,k] + bias[c]; A [rows, K] (pitch lda), B [N, K] (pitch ldb), both
+ * bf16 pairs, K % 8 == 0; bias_pad fp32 with ceil(N/256)*256 entries.
+ *  _lse: lse[r] = log sum_c exp x[r,c]                        (log_softmax denominators)
+ *  _exp: G[r,c] = scale_r exp(x[r,c] + c0_r), coef [rows] float4 {c0, -, -, scale}, written as
+ *        the split pair g_hi / g_lo [rows, N] bf16 (pitch ldg): the softmax part of the loss
+ *        gradient; the sparse posterior terms follow through b200_rnnt_fixup / b200_ctc_fixup
+ *  _lsm: out[r,c] = x[r,c] - lse[r] in fp32 (pitch ldo)       (CTC.log_softmax, ctc.py:66-74) */
+int b200_split_gemm_lse(const void* a_hi, const void* a_lo, long long rows, int K, int lda,
+                        const void* b_hi, const void* b_lo, int N, int ldb, const float* bias_pad,
+                        float* lse, int max_ctas, b200_stream_t stream);
+int b200_split_gemm_exp(const void* a_hi, const void* a_lo, long long rows, int K, int lda,
+                        const void* b_hi, const void* b_lo, int N, int ldb, const float* bias_pad,
+                        const float* coef, void* g_hi, void* g_lo, long long ldg, int max_ctas,
+                        b200_stream_t stream);
+int b200_split_gemm_lsm(const void* a_hi, const void* a_lo, long long rows, int K, int lda,
+                        const void* b_hi, const void* b_lo, int N, int ldb, const float* bias_pad,
+                        const float* lse, float* out, long long ldo, int max_ctas,
+                        b200_stream_t stream);
+
+/* out [rows, J] fp32 = G W: G [rows, V] bf16 pair (pitch ldg), W [V, J] bf16 pair, J 256 or 512
+ * (d hs of the ctc_lo projection: autograd of ctc.py:57) */
+int b200_split_gemm_nn(const void* G_hi, const void* G_lo, int ldg, const void* w_hi,
+                       const void* w_lo, long long rows, int V, int J, float* out, int max_ctas,
+                       b200_stream_t stream);
+
+/* H = tanh(e[b,t,:] + p[b,u,:]) in fp32 (joint.py:58-64) as a split pair [B*T*U1, ldh] */
+int b200_joint_h_split(const float* e, const float* p, int B, int T, int U1, int J, void* H_hi,
+                       void* H_lo, int ldh, b200_stream_t stream);
+
+/* the two logits per lattice cell the RNN-T lattice reads (blank, target), as fp32 dot products
+ * with W [V, J] fp32: lp_blank / lp_emit = logit - lse [B,T,U1] (cells beyond the lengths are
+ * not written), xbe [B,T,U1,2] = the raw logits for b200_rnnt_fixup */
+int b200_joint_pick(const float* e, const float* p, const float* W, const float* bias,
+                    const int32_t* targets, const int32_t* logit_len, const int32_t* target_len,
+                    int B, int T, int U1, int V, int J, int blank, const float* lse,
+                    float* lp_blank, float* lp_emit, float* xbe, b200_stream_t stream);
+
+/* lp_ext [B,T,2*Lmax+1] of b200_ctc_logprobs from hs [B,T,E] and ctc_lo (W [V,E], bias) directly:
+ * fp32 dot products with the gathered rows of the blank and the utterance's labels, minus lse */
+int b200_ctc_lp_ext(const float* hs, const float* W, const float* bias, const int64_t* ys_pad,
+                    const int32_t* hlens, const int32_t* ys_lens, int B, int T, int E, int V,
+                    int Lmax, int blank, const float* lse, float* lp_ext, b200_stream_t stream);
+
+/* G[cell, blank] -= scale exp(x_blank + cb), G[cell, y] -= scale exp(x_y + ce) with coef [cell]
+ * = {c0, cb, ce, scale} of b200_joint_grad_coef (the sparse terms of the rnnt_loss gradient) */
+int b200_rnnt_fixup(const float* coef, const float* xbe, const int32_t* targets, int B, int T,
+                    int U1, int V, int blank, void* G_hi, void* G_lo, long long ldg,
+                    b200_stream_t stream);
+
+/* G[b,t,c] -= scale[b] * posterior(c at t) for the blank and every distinct label (the sparse
+ * terms of pass 3 of the CTC loss); alpha / beta / frame_off / leader as b200_ctc_lattice wrote */
+int b200_ctc_fixup(const float* lp_ext, const float* alpha, const float* beta,
+                   const double* frame_off, const float* scale, const int64_t* ys_pad,
+                   const int32_t* hlens, const int32_t* ys_lens, const int32_t* leader, int B,
+                   int T, int V, int Lmax, int blank, void* G_hi, void* G_lo, long long ldg,
+                   b200_stream_t stream);
+
+/* out[c] += sum_r (G_hi + G_lo)[r, c] (the bias gradient); out must be zeroed first */
+int b200_colsum_split(const void* G_hi, const void* G_lo, long long rows, int N, long long ldg,
+                      float* out, b200_stream_t stream);
+
+/* b200_joint_dw / b200_joint_dh on split operands (three products each) */
+int b200_joint_dw_split(const void* G_hi, const void* G_lo, int ldg, const void* H_hi,
+                        const void* H_lo, int ldh, long long n, int V, int J, float* dW,
+                        int max_ctas, b200_stream_t stream);
+int b200_joint_dh_split(const void* G_hi, const void* G_lo, int ldg, const void* w_hi,
+                        const void* w_lo, const void* H_hi, const void* H_lo, int ldh, int nb,
+                        int T, int U1, int V, int J, const int32_t* logit_len,
+                        const int32_t* target_len, float* de, float* dp, int max_ctas,
+                        b200_stream_t stream);
+
 /* ---- Batched RNN-T greedy search ------------------------------------------
  * replaces the Python loop of wenet/transducer/search/greedy_search.py:34-176 (core
  * algorithm: "greedy_search copy.py":6-63): per lattice step predictor.forward_step

@@ -49,13 +49,13 @@ def _reference(joint, enc, pred, tgt, tl, ul, reduction="mean"):
     return loss.detach(), grads
 
 
-def _mine(joint, enc, pred, tgt, tl, ul, reduction="mean"):
+def _mine(joint, enc, pred, tgt, tl, ul, reduction="mean", precision="bf16"):
     from wenet_celoss_b200 import fused_joint_rnnt_loss
     j = copy.deepcopy(joint).to(DEV)
     enc = enc.to(DEV).requires_grad_(True)
     pred = pred.to(DEV).requires_grad_(True)
     loss = fused_joint_rnnt_loss(j, enc, pred, tgt.to(DEV), tl.to(DEV), ul.to(DEV), blank=0,
-                                 reduction=reduction)
+                                 reduction=reduction, precision=precision)
     loss.sum().backward()
     grads = {"enc": enc.grad.cpu(), "pred": pred.grad.cpu()}
     grads.update({n: p.grad.cpu() for n, p in j.named_parameters()})
@@ -109,7 +109,7 @@ def test_matches_materialised_path_on_same_bf16_operands():
     joint, enc, pred, tgt, tl, ul = _case(2, 25, 8, 1000, 64, 512, seed=9)
     j = joint.to(DEV)
     enc, pred, tgt, tl, ul = (x.to(DEV) for x in (enc, pred, tgt, tl, ul))
-    fused = fused_joint_rnnt_loss(j, enc, pred, tgt, tl, ul, blank=0, reduction="none")
+    fused = fused_joint_rnnt_loss(j, enc, pred, tgt, tl, ul, blank=0, reduction="none", precision="bf16")
     h = torch.tanh(j.enc_ffn(enc)[:, :, None] + j.pred_ffn(pred)[:, None]).to(torch.bfloat16).float()
     logits = h @ j.ffn_out.weight.to(torch.bfloat16).float().t() + j.ffn_out.bias
     mat = rnnt_loss(logits.contiguous(), tgt, tl, ul, blank=0, reduction="none")

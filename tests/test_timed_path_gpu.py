@@ -32,6 +32,7 @@ DEV = "cuda:0"
 def _mine_kw(case, reduction="none", **kw):
     from wenet_celoss_b200 import fused_joint_rnnt_loss
     joint, enc, pred, tgt, tl, ul = case
+    kw.setdefault("precision", "bf16")
     j = copy.deepcopy(joint).to(DEV)
     enc = enc.to(DEV).requires_grad_(True)
     pred = pred.to(DEV).requires_grad_(True)

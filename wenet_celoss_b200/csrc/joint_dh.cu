@@ -43,7 +43,11 @@ struct Params {
   int ntb, nub;          // frame blocks / label blocks per utterance
   int kblocks;           // ceil(V / 64)
   const __nv_bfloat16* H;  // [nb*T*U1, ldh]
+  const __nv_bfloat16* H_lo;  // optional: H = H + H_lo (split operands, fp32-accurate mode)
   int ldh;
+  int npass;             // 1: G.W   3: G_hi.W_hi + G_lo.W_hi + G_hi.W_lo
+  long long rows;        // PLAIN: rows of G (= nb, with T = U1 = 1 unused)
+  float* out;            // PLAIN: [rows, J] fp32 = G.W, written (no tanh', no sums)
   const int32_t* logit_len;   // optional [nb]: tiles beyond T_b / U_b are skipped (their G is zero)
   const int32_t* target_len;
   float* de;             // [nb, T, J]  accumulated (zero it first)
@@ -94,9 +98,12 @@ __device__ __forceinline__ Tile decode(const Params& P, int u, int tb) {
   return t;
 }
 
-template <int UB>
+// PLAIN: the same product for a plain row-major G [rows, ldg] (2-D TMA map, tiles of 256 consecutive rows),
+// epilogue out[row, j] = (G W)[row, j] - the d hs GEMM of the CTC projection (autograd of ctc.py:57)
+template <int UB, bool PLAIN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     joint_dh_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUtensorMap gmap,
+                    const __grid_constant__ CUtensorMap wmap_lo, const __grid_constant__ CUtensorMap gmap_lo,
                     const Params P) {
   constexpr int TBH = 128 / UB;  // frames per CTA half of a tile
   constexpr int TB = 2 * TBH;    // frames per tile
@@ -138,12 +145,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
   ptx::tc_fence_after();
   const uint32_t tmem_base = tmem_holder;
 
-  const int nunits = P.nb * P.ntb * P.nub;
+  const int nunits = PLAIN ? (int)((P.rows + 255) / 256) : P.nb * P.ntb * P.nub;
   const int pair_id = (int)cluster_id_x();
   const int npairs = (int)nclusters_x();
   // a tile whose frames / labels all lie beyond the utterance's lengths holds G == 0: every role skips it
   auto live = [&](const Tile& t) {
-    if (P.logit_len == nullptr) return true;
+    if (PLAIN || P.logit_len == nullptr) return true;
     return t.t0 < __ldg(P.logit_len + t.b) && t.u0 * UB <= __ldg(P.target_len + t.b);
   };
 
@@ -156,28 +163,34 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     for (int u = pair_id; u < nunits; u += npairs) {
       const Tile tl = decode(P, u, TB);
       if (!live(tl)) continue;
-      for (int kb = 0; kb < P.kblocks; ++kb, ++it) {
-        const int s = (int)(it % kStages);
-        const uint32_t ph = (uint32_t)((it / kStages) & 1);
-        ptx::mbar_wait(empty_bar(s), ph ^ 1u);
-        if (ptx::elect_one()) {
-          if (rank == 0) ptx::mbar_arrive_expect_tx(full_bar(s), 2u * (uint32_t)sbytes);
-          const uint32_t bar = leader_full0 + 8u * s;
-          const uint32_t dst = smem_base + (uint32_t)s * sbytes;
-          const int v0 = kb * kBlockK;
-          // A: W^T, this CTA's 128 j of every accumulator (two boxes of 64 j); shared by all tiles
-          uint32_t adst = dst;
-          for (int a = 0; a < nacc; ++a) {
-            const int j0 = 256 * a + (int)rank * 128;
-            tma_load_2d_pair(adst, &wmap, bar, j0, v0, pol_keep);
-            tma_load_2d_pair(adst + kBoxBytes, &wmap, bar, j0 + 64, v0, pol_keep);
-            adst += 2 * kBoxBytes;
+      for (int pass = 0; pass < P.npass; ++pass) {
+        const CUtensorMap* wm = pass == 2 ? &wmap_lo : &wmap;
+        const CUtensorMap* gm = pass == 1 ? &gmap_lo : &gmap;
+        for (int kb = 0; kb < P.kblocks; ++kb, ++it) {
+          const int s = (int)(it % kStages);
+          const uint32_t ph = (uint32_t)((it / kStages) & 1);
+          ptx::mbar_wait(empty_bar(s), ph ^ 1u);
+          if (ptx::elect_one()) {
+            if (rank == 0) ptx::mbar_arrive_expect_tx(full_bar(s), 2u * (uint32_t)sbytes);
+            const uint32_t bar = leader_full0 + 8u * s;
+            const uint32_t dst = smem_base + (uint32_t)s * sbytes;
+            const int v0 = kb * kBlockK;
+            // A: W^T, this CTA's 128 j of every accumulator (two boxes of 64 j); shared by all tiles
+            uint32_t adst = dst;
+            for (int a = 0; a < nacc; ++a) {
+              const int j0 = 256 * a + (int)rank * 128;
+              tma_load_2d_pair(adst, wm, bar, j0, v0, pol_keep);
+              tma_load_2d_pair(adst + kBoxBytes, wm, bar, j0 + 64, v0, pol_keep);
+              adst += 2 * kBoxBytes;
+            }
+            // B: G rows of UB labels x TBH frames (this CTA's half of the tile); read once per pass
+            if (PLAIN)
+              tma_load_2d_pair(dst + abytes, gm, bar, v0, u * 256 + (int)rank * 128, pol_stream);
+            else
+              tma_load_4d_pair(dst + abytes, gm, bar, v0, tl.u0 * UB, tl.t0 + (int)rank * TBH, tl.b, pol_stream);
           }
-          // B: G rows of UB labels x TBH frames (this CTA's half of the tile); read once
-          tma_load_4d_pair(dst + abytes, &gmap, bar, v0, tl.u0 * UB, tl.t0 + (int)rank * TBH, tl.b,
-                           pol_stream);
+          __syncwarp();
         }
-        __syncwarp();
       }
     }
   } else if (warp == 1) {
@@ -192,27 +205,28 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         ptx::mbar_wait(acc_empty, (uint32_t)((nu & 1) ^ 1));  // drained by both CTAs' epilogues
         ++nu;
         ptx::tc_fence_after();
-        for (int kb = 0; kb < P.kblocks; ++kb, ++it) {
-          const int s = (int)(it % kStages);
-          const uint32_t ph = (uint32_t)((it / kStages) & 1);
-          ptx::mbar_wait(full_bar(s), ph);
-          ptx::tc_fence_after();
-          if (ptx::elect_one()) {
-            const uint32_t sa = smem_base + (uint32_t)s * sbytes;
-            const uint64_t bdesc0 = ptx::make_sw128_kmajor_desc(sa + abytes);
+        for (int pass = 0; pass < P.npass; ++pass)
+          for (int kb = 0; kb < P.kblocks; ++kb, ++it) {
+            const int s = (int)(it % kStages);
+            const uint32_t ph = (uint32_t)((it / kStages) & 1);
+            ptx::mbar_wait(full_bar(s), ph);
+            ptx::tc_fence_after();
+            if (ptx::elect_one()) {
+              const uint32_t sa = smem_base + (uint32_t)s * sbytes;
+              const uint64_t bdesc0 = ptx::make_sw128_kmajor_desc(sa + abytes);
 #pragma unroll
-            for (int k = 0; k < kBlockK / 16; ++k) {
-              for (int a = 0; a < nacc; ++a) {
-                const uint64_t adesc = make_sw128_mnmajor_desc(sa + a * 2 * kBoxBytes + k * 2048);
-                umma_bf16_pair(tmem_base + 256u * a, adesc, bdesc0 + 2 * k, idesc,
-                               (kb > 0 || k > 0) ? 1u : 0u);
+              for (int k = 0; k < kBlockK / 16; ++k) {
+                for (int a = 0; a < nacc; ++a) {
+                  const uint64_t adesc = make_sw128_mnmajor_desc(sa + a * 2 * kBoxBytes + k * 2048);
+                  umma_bf16_pair(tmem_base + 256u * a, adesc, bdesc0 + 2 * k, idesc,
+                                 (pass > 0 || kb > 0 || k > 0) ? 1u : 0u);
+                }
               }
+              umma_commit_pair(empty_bar(s));
+              if (pass == P.npass - 1 && kb == P.kblocks - 1) umma_commit_pair(acc_full);
             }
-            umma_commit_pair(empty_bar(s));
-            if (kb == P.kblocks - 1) umma_commit_pair(acc_full);
+            __syncwarp();
           }
-          __syncwarp();
-        }
       }
     }
   } else if (warp - kEpiWarp0 < 4 * nacc) {
@@ -226,25 +240,50 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
       const Tile tl = decode(P, u, TB);
       if (!live(tl)) continue;
       const int u0 = tl.u0 * UB;
+      if (PLAIN) {
+        // out[row, j] for the 256 rows of this tile (column c = row u * 256 + c): plain coalesced stores
+        ptx::mbar_wait(acc_full, (uint32_t)(nu & 1));
+        ++nu;
+        ptx::tc_fence_after();
+        const long long row0 = (long long)u * 256;
+#pragma unroll 1
+        for (int ch = 0; ch < 16; ++ch) {
+          uint32_t r[16];
+          ptx::tmem_ld16(taddr + ch * 16, r);
+          ptx::tmem_ld_wait();
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            const long long row = row0 + ch * 16 + k;
+            if (row < P.rows) P.out[row * J + j] = __uint_as_float(r[k]);
+          }
+        }
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(map_to_cta(acc_empty, 0));
+        continue;
+      }
       // chunk ch = columns 16ch .. 16ch+15 = rows (ch & 7) * 16 + k of CTA half ch >> 3; row r of a half is
       // frame r / UB, label r % UB of the tile (the order the 4-D TMA box lays the G rows out).  Frames /
       // labels beyond T / U1 have a zero accumulator: their H index is clamped, the value is irrelevant
       const uint16_t* Hj = reinterpret_cast<const uint16_t*>(P.H) + j;
-      auto load_h = [&](int ch, uint16_t* h) {
+      const uint16_t* Hlj = P.H_lo ? reinterpret_cast<const uint16_t*>(P.H_lo) + j : nullptr;
+      auto load_h = [&](int ch, uint16_t* h, uint16_t* hl) {
 #pragma unroll
         for (int k = 0; k < 16; ++k) {
           const int row = (ch & 7) * 16 + k;
           const int t = min(tl.t0 + (ch >> 3) * TBH + row / UB, P.T - 1);
           const int uu = min(u0 + row % UB, P.U1 - 1);
-          h[k] = __ldg(Hj + (uint32_t)(((tl.b * P.T + t) * P.U1 + uu) * P.ldh));  // < 2^31 (host check)
+          const uint32_t off = (uint32_t)(((tl.b * P.T + t) * P.U1 + uu) * P.ldh);  // < 2^31 (host check)
+          h[k] = __ldg(Hj + off);
+          if (Hlj) hl[k] = __ldg(Hlj + off);
         }
       };
       float dp_acc[UB];
 #pragma unroll
       for (int i = 0; i < UB; ++i) dp_acc[i] = 0.f;
       float de_run = 0.f;
-      uint16_t hbuf[2][16];
-      load_h(0, hbuf[0]);
+      uint16_t hbuf[2][16], lbuf[2][16];
+      load_h(0, hbuf[0], lbuf[0]);
       ptx::mbar_wait(acc_full, (uint32_t)(nu & 1));
       ++nu;
       ptx::tc_fence_after();
@@ -255,13 +294,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
           const int ch = 2 * c2 + hh;
           uint32_t r[16];
           ptx::tmem_ld16(taddr + ch * 16, r);
-          if (ch + 1 < 16) load_h(ch + 1, hbuf[hh ^ 1]);
+          if (ch + 1 < 16) load_h(ch + 1, hbuf[hh ^ 1], lbuf[hh ^ 1]);
           ptx::tmem_ld_wait();
           const uint16_t* h = hbuf[hh];
+          const uint16_t* hl = lbuf[hh];
 #pragma unroll
           for (int k = 0; k < 16; ++k) {
             const int rs = hh * 16 + k;  // row within a pair of chunks; UB divides 32
-            const float hv = __uint_as_float((uint32_t)h[k] << 16);
+            float hv = __uint_as_float((uint32_t)h[k] << 16);
+            if (Hlj) hv += __uint_as_float((uint32_t)hl[k] << 16);
             const float z = __uint_as_float(r[k]) * fmaf(-hv, hv, 1.f);
             dp_acc[rs % UB] += z;
             de_run += z;
@@ -331,53 +372,56 @@ int encode(CUtensorMap* map, const void* ptr, int rank, const cuuint64_t* dims, 
   return B200_OK;
 }
 
-template <int UB>
-int launch_dh(const CUtensorMap& wmap, const void* G, int ldg, dh::Params P, int ctas, cudaStream_t st) {
+template <int UB, bool PLAIN>
+int launch_dh(const CUtensorMap& wmap, const CUtensorMap& wmap_lo, const void* G, const void* G_lo, int ldg,
+              dh::Params P, int ctas, cudaStream_t st) {
   constexpr int TBH = 128 / UB;
-  P.ntb = (P.T + 2 * TBH - 1) / (2 * TBH);
-  P.nub = (P.U1 + UB - 1) / UB;
-  // G [nb*T*U1, ldg] viewed as [b, t, u, v]; v beyond V, u beyond U1, t beyond T read as zero
-  CUtensorMap gmap;
-  cuuint64_t dims[4] = {(cuuint64_t)P.V, (cuuint64_t)P.U1, (cuuint64_t)P.T, (cuuint64_t)P.nb};
-  cuuint64_t strides[3] = {(cuuint64_t)ldg * 2, (cuuint64_t)P.U1 * ldg * 2, (cuuint64_t)P.T * P.U1 * ldg * 2};
-  cuuint32_t box[4] = {(cuuint32_t)dh::kBlockK, (cuuint32_t)UB, (cuuint32_t)TBH, 1};
-  if (int rc = encode(&gmap, G, 4, dims, strides, box)) return rc;
+  CUtensorMap gmap, gmap_lo;
+  long long units;
+  if (PLAIN) {
+    // G [rows, ldg]: boxes of [128 rows x 64 v]; rows beyond `rows`, v beyond V read as zero
+    cuuint64_t dims[2] = {(cuuint64_t)P.V, (cuuint64_t)P.rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ldg * 2};
+    cuuint32_t box[2] = {(cuuint32_t)dh::kBlockK, 128};
+    if (int rc = encode(&gmap, G, 2, dims, strides, box)) return rc;
+    gmap_lo = gmap;
+    if (G_lo)
+      if (int rc = encode(&gmap_lo, G_lo, 2, dims, strides, box)) return rc;
+    units = (P.rows + 255) / 256;
+    P.nb = (int)units;
+    P.ntb = P.nub = 1;
+  } else {
+    P.ntb = (P.T + 2 * TBH - 1) / (2 * TBH);
+    P.nub = (P.U1 + UB - 1) / UB;
+    // G [nb*T*U1, ldg] viewed as [b, t, u, v]; v beyond V, u beyond U1, t beyond T read as zero
+    cuuint64_t dims[4] = {(cuuint64_t)P.V, (cuuint64_t)P.U1, (cuuint64_t)P.T, (cuuint64_t)P.nb};
+    cuuint64_t strides[3] = {(cuuint64_t)ldg * 2, (cuuint64_t)P.U1 * ldg * 2, (cuuint64_t)P.T * P.U1 * ldg * 2};
+    cuuint32_t box[4] = {(cuuint32_t)dh::kBlockK, (cuuint32_t)UB, (cuuint32_t)TBH, 1};
+    if (int rc = encode(&gmap, G, 4, dims, strides, box)) return rc;
+    gmap_lo = gmap;
+    if (G_lo)
+      if (int rc = encode(&gmap_lo, G_lo, 4, dims, strides, box)) return rc;
+    units = (long long)P.nb * P.ntb * P.nub;
+  }
   const int smem = dh::kStages * dh::stage_bytes(P.J) + 1024;
-  B200_CHECK_CUDA(cudaFuncSetAttribute(dh::joint_dh_kernel<UB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  B200_CHECK_CUDA(cudaFuncSetAttribute(dh::joint_dh_kernel<UB, PLAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dh::kStages * dh::stage_bytes(dh::kMaxJ) + 1024));
-  const long long units = (long long)P.nb * P.ntb * P.nub;
   int grid = ctas;
   if (units < grid / 2) grid = 2 * (int)units;
-  dh::joint_dh_kernel<UB><<<grid, dh::kThreads, smem, st>>>(wmap, gmap, P);
+  dh::joint_dh_kernel<UB, PLAIN><<<grid, dh::kThreads, smem, st>>>(wmap, gmap, wmap_lo, gmap_lo, P);
   B200_CHECK_LAUNCH("joint_dh_kernel");
   return B200_OK;
 }
 
-}  // namespace
+int encode_w(CUtensorMap* wmap, const void* w, int V, int J) {
+  // W [V, J] bf16: boxes of [64 v x 64 j] (MN-major A operand); rows beyond V read as zero
+  cuuint64_t dims[2] = {(cuuint64_t)J, (cuuint64_t)V};
+  cuuint64_t strides[1] = {(cuuint64_t)J * 2};
+  cuuint32_t box[2] = {64, (cuuint32_t)dh::kBlockK};
+  return encode(wmap, w, 2, dims, strides, box);
+}
 
-extern "C" int b200_joint_dh(const void* G, int ldg, const void* w_bf16, const void* H, int ldh, int nb, int T,
-                             int U1, int V, int J, const int32_t* logit_len, const int32_t* target_len,
-                             float* de, float* dp, int max_ctas, b200_stream_t stream) {
-  B200_CHECK_ARG(G && w_bf16 && H && de && dp, "b200_joint_dh: null pointer");
-  B200_CHECK_ARG(nb > 0 && T > 0 && U1 > 0 && V > 0, "b200_joint_dh: bad shape nb=%d T=%d U1=%d V=%d", nb, T,
-                 U1, V);
-  B200_CHECK_ARG(J == 256 || J == 512, "b200_joint_dh: join dim J=%d must be 256 or 512", J);
-  B200_CHECK_ARG(ldg >= V && ldg % 8 == 0 && ((uintptr_t)G & 15) == 0,
-                 "b200_joint_dh: ldg=%d must be >= V and a multiple of 8, G 16-byte aligned", ldg);
-  B200_CHECK_ARG(ldh >= J && ((uintptr_t)H & 1) == 0, "b200_joint_dh: ldh=%d must be >= J", ldh);
-  B200_CHECK_ARG(((uintptr_t)w_bf16 & 15) == 0, "b200_joint_dh: W must be 16-byte aligned");
-  B200_CHECK_ARG((long long)nb * T * U1 * ldh < (1ll << 31),
-                 "b200_joint_dh: chunk of %d utterances too large (H chunk must stay below 2^31 elements)", nb);
-  B200_CHECK_ARG((logit_len == nullptr) == (target_len == nullptr),
-                 "b200_joint_dh: logit_len and target_len go together");
-  // W_out [V, J] bf16: boxes of [64 v x 64 j] (MN-major A operand); rows beyond V read as zero
-  CUtensorMap wmap;
-  {
-    cuuint64_t dims[2] = {(cuuint64_t)J, (cuuint64_t)V};
-    cuuint64_t strides[1] = {(cuuint64_t)J * 2};
-    cuuint32_t box[2] = {64, (cuuint32_t)dh::kBlockK};
-    if (int rc = encode(&wmap, w_bf16, 2, dims, strides, box)) return rc;
-  }
+int dh_ctas(int max_ctas) {
   int sms = 0, dev = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -385,6 +429,32 @@ extern "C" int b200_joint_dh(const void* G, int ldg, const void* w_bf16, const v
   int ctas = sms & ~1;
   if (max_ctas > 0 && max_ctas < ctas) ctas = max_ctas & ~1;
   if (ctas < 2) ctas = 2;
+  return ctas;
+}
+
+int joint_dh_impl(const void* G, const void* G_lo, int ldg, const void* w, const void* w_lo, const void* H,
+                  const void* H_lo, int ldh, int nb, int T, int U1, int V, int J, const int32_t* logit_len,
+                  const int32_t* target_len, float* de, float* dp, int max_ctas, b200_stream_t stream) {
+  B200_CHECK_ARG(G && w && H && de && dp, "b200_joint_dh: null pointer");
+  B200_CHECK_ARG(nb > 0 && T > 0 && U1 > 0 && V > 0, "b200_joint_dh: bad shape nb=%d T=%d U1=%d V=%d", nb, T,
+                 U1, V);
+  B200_CHECK_ARG(J == 256 || J == 512, "b200_joint_dh: join dim J=%d must be 256 or 512", J);
+  B200_CHECK_ARG(ldg >= V && ldg % 8 == 0 && ((uintptr_t)G & 15) == 0 && ((uintptr_t)G_lo & 15) == 0,
+                 "b200_joint_dh: ldg=%d must be >= V and a multiple of 8, G 16-byte aligned", ldg);
+  B200_CHECK_ARG(ldh >= J && ((uintptr_t)H & 1) == 0, "b200_joint_dh: ldh=%d must be >= J", ldh);
+  B200_CHECK_ARG(((uintptr_t)w & 15) == 0 && ((uintptr_t)w_lo & 15) == 0,
+                 "b200_joint_dh: W must be 16-byte aligned");
+  B200_CHECK_ARG((long long)nb * T * U1 * ldh < (1ll << 31),
+                 "b200_joint_dh: chunk of %d utterances too large (H chunk must stay below 2^31 elements)", nb);
+  B200_CHECK_ARG((logit_len == nullptr) == (target_len == nullptr),
+                 "b200_joint_dh: logit_len and target_len go together");
+  B200_CHECK_ARG((G_lo == nullptr) == (w_lo == nullptr), "b200_joint_dh: G_lo and W_lo go together");
+  CUtensorMap wmap, wmap_lo;
+  if (int rc = encode_w(&wmap, w, V, J)) return rc;
+  wmap_lo = wmap;
+  if (w_lo)
+    if (int rc = encode_w(&wmap_lo, w_lo, V, J)) return rc;
+  const int ctas = dh_ctas(max_ctas);
   dh::Params P{};
   P.nb = nb;
   P.T = T;
@@ -393,7 +463,9 @@ extern "C" int b200_joint_dh(const void* G, int ldg, const void* w_bf16, const v
   P.J = J;
   P.kblocks = (V + dh::kBlockK - 1) / dh::kBlockK;
   P.H = reinterpret_cast<const __nv_bfloat16*>(H);
+  P.H_lo = reinterpret_cast<const __nv_bfloat16*>(H_lo);
   P.ldh = ldh;
+  P.npass = G_lo ? 3 : 1;
   P.logit_len = logit_len;
   P.target_len = target_len;
   P.de = de;
@@ -414,10 +486,54 @@ extern "C" int b200_joint_dh(const void* G, int ldg, const void* w_bf16, const v
   }
   cudaStream_t st = (cudaStream_t)stream;
   switch (best) {
-    case 2: return launch_dh<2>(wmap, G, ldg, P, ctas, st);
-    case 4: return launch_dh<4>(wmap, G, ldg, P, ctas, st);
-    case 8: return launch_dh<8>(wmap, G, ldg, P, ctas, st);
-    case 16: return launch_dh<16>(wmap, G, ldg, P, ctas, st);
-    default: return launch_dh<32>(wmap, G, ldg, P, ctas, st);
+    case 2: return launch_dh<2, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+    case 4: return launch_dh<4, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+    case 8: return launch_dh<8, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+    case 16: return launch_dh<16, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+    default: return launch_dh<32, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
   }
+}
+
+}  // namespace
+
+extern "C" int b200_joint_dh(const void* G, int ldg, const void* w_bf16, const void* H, int ldh, int nb, int T,
+                             int U1, int V, int J, const int32_t* logit_len, const int32_t* target_len,
+                             float* de, float* dp, int max_ctas, b200_stream_t stream) {
+  return joint_dh_impl(G, nullptr, ldg, w_bf16, nullptr, H, nullptr, ldh, nb, T, U1, V, J, logit_len, target_len,
+                       de, dp, max_ctas, stream);
+}
+
+extern "C" int b200_joint_dh_split(const void* G_hi, const void* G_lo, int ldg, const void* w_hi,
+                                   const void* w_lo, const void* H_hi, const void* H_lo, int ldh, int nb, int T,
+                                   int U1, int V, int J, const int32_t* logit_len, const int32_t* target_len,
+                                   float* de, float* dp, int max_ctas, b200_stream_t stream) {
+  B200_CHECK_ARG(G_lo && w_lo && H_lo, "b200_joint_dh_split: null pointer");
+  return joint_dh_impl(G_hi, G_lo, ldg, w_hi, w_lo, H_hi, H_lo, ldh, nb, T, U1, V, J, logit_len, target_len, de,
+                       dp, max_ctas, stream);
+}
+
+extern "C" int b200_split_gemm_nn(const void* G_hi, const void* G_lo, int ldg, const void* w_hi, const void* w_lo,
+                                  long long rows, int V, int J, float* out, int max_ctas, b200_stream_t stream) {
+  B200_CHECK_ARG(G_hi && w_hi && out, "b200_split_gemm_nn: null pointer");
+  B200_CHECK_ARG(rows > 0 && V > 0, "b200_split_gemm_nn: bad shape rows=%lld V=%d", rows, V);
+  B200_CHECK_ARG(J == 256 || J == 512, "b200_split_gemm_nn: output width J=%d must be 256 or 512", J);
+  B200_CHECK_ARG(ldg >= V && ldg % 8 == 0 && ((uintptr_t)G_hi & 15) == 0 && ((uintptr_t)G_lo & 15) == 0,
+                 "b200_split_gemm_nn: ldg=%d must be >= V and a multiple of 8, G 16-byte aligned", ldg);
+  B200_CHECK_ARG(((uintptr_t)w_hi & 15) == 0 && ((uintptr_t)w_lo & 15) == 0,
+                 "b200_split_gemm_nn: W must be 16-byte aligned");
+  B200_CHECK_ARG((G_lo == nullptr) == (w_lo == nullptr), "b200_split_gemm_nn: G_lo and W_lo go together");
+  CUtensorMap wmap, wmap_lo;
+  if (int rc = encode_w(&wmap, w_hi, V, J)) return rc;
+  wmap_lo = wmap;
+  if (w_lo)
+    if (int rc = encode_w(&wmap_lo, w_lo, V, J)) return rc;
+  dh::Params P{};
+  P.T = P.U1 = 1;
+  P.V = V;
+  P.J = J;
+  P.kblocks = (V + dh::kBlockK - 1) / dh::kBlockK;
+  P.npass = G_lo ? 3 : 1;
+  P.rows = rows;
+  P.out = out;
+  return launch_dh<16, true>(wmap, wmap_lo, G_hi, G_lo, ldg, P, dh_ctas(max_ctas), (cudaStream_t)stream);
 }

@@ -41,6 +41,7 @@ struct Params {
   int kblocks;        // ceil(n / 64)
   int nvt;            // V tiles of 256
   int nsplit;         // K splits
+  int npass;          // 1: G.H   3: split operands, G_hi.H_hi + G_lo.H_hi + G_hi.H_lo (fp32-accurate mode)
   float* dW;          // [V, J] fp32, accumulated
 };
 
@@ -67,6 +68,7 @@ using namespace pair;
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     joint_dw_kernel(const __grid_constant__ CUtensorMap gmap, const __grid_constant__ CUtensorMap hmap,
+                    const __grid_constant__ CUtensorMap gmap_lo, const __grid_constant__ CUtensorMap hmap_lo,
                     const Params P) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * kStages + 2];
@@ -120,28 +122,32 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
       const int kb0 = (int)((long long)P.kblocks * ks / P.nsplit);
       const int kb1 = (int)((long long)P.kblocks * (ks + 1) / P.nsplit);
       const int v0 = vt * kTileV + (int)rank * 128;
-      for (int kb = kb0; kb < kb1; ++kb, ++it) {
-        const int s = (int)(it % kStages);
-        const uint32_t ph = (uint32_t)((it / kStages) & 1);
-        ptx::mbar_wait(empty_bar(s), ph ^ 1u);
-        if (ptx::elect_one()) {
-          if (rank == 0) ptx::mbar_arrive_expect_tx(full_bar(s), 2u * (uint32_t)sbytes);
-          const uint32_t bar = leader_full0 + 8u * s;
-          const uint32_t dst = smem_base + (uint32_t)s * sbytes;
-          const int c = kb * kBlockK;
-          // A: G^T rows v0 .. v0+127 (two boxes of 64 v); read exactly once: evict first
-          tma_load_2d_pair(dst, &gmap, bar, v0, c, pol_stream);
-          tma_load_2d_pair(dst + kBoxBytes, &gmap, bar, v0 + 64, c, pol_stream);
-          // B: this CTA's half of each accumulator's J range; shared by all V tiles: keep in L2
-          uint32_t bdst = dst + 2 * kBoxBytes;
-          for (int a = 0; a < nacc; ++a) {
-            const int Na = min(256, J - 256 * a);
-            const int j0 = 256 * a + (int)rank * (Na / 2);
-            for (int i = 0; i < Na / 128; ++i, bdst += kBoxBytes)
-              tma_load_2d_pair(bdst, &hmap, bar, j0 + 64 * i, c, pol_keep);
+      for (int pass = 0; pass < P.npass; ++pass) {
+        const CUtensorMap* gm = pass == 1 ? &gmap_lo : &gmap;
+        const CUtensorMap* hm = pass == 2 ? &hmap_lo : &hmap;
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+          const int s = (int)(it % kStages);
+          const uint32_t ph = (uint32_t)((it / kStages) & 1);
+          ptx::mbar_wait(empty_bar(s), ph ^ 1u);
+          if (ptx::elect_one()) {
+            if (rank == 0) ptx::mbar_arrive_expect_tx(full_bar(s), 2u * (uint32_t)sbytes);
+            const uint32_t bar = leader_full0 + 8u * s;
+            const uint32_t dst = smem_base + (uint32_t)s * sbytes;
+            const int c = kb * kBlockK;
+            // A: G^T rows v0 .. v0+127 (two boxes of 64 v); read exactly once: evict first
+            tma_load_2d_pair(dst, gm, bar, v0, c, pol_stream);
+            tma_load_2d_pair(dst + kBoxBytes, gm, bar, v0 + 64, c, pol_stream);
+            // B: this CTA's half of each accumulator's J range; shared by all V tiles: keep in L2
+            uint32_t bdst = dst + 2 * kBoxBytes;
+            for (int a = 0; a < nacc; ++a) {
+              const int Na = min(256, J - 256 * a);
+              const int j0 = 256 * a + (int)rank * (Na / 2);
+              for (int i = 0; i < Na / 128; ++i, bdst += kBoxBytes)
+                tma_load_2d_pair(bdst, hm, bar, j0 + 64 * i, c, pol_keep);
+            }
           }
+          __syncwarp();
         }
-        __syncwarp();
       }
     }
   } else if (warp == 1) {
@@ -158,30 +164,31 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         ptx::mbar_wait(acc_empty, (uint32_t)((nu & 1) ^ 1));
         ++nu;
         ptx::tc_fence_after();
-        for (int kb = kb0; kb < kb1; ++kb, ++it) {
-          const int s = (int)(it % kStages);
-          const uint32_t ph = (uint32_t)((it / kStages) & 1);
-          ptx::mbar_wait(full_bar(s), ph);
-          ptx::tc_fence_after();
-          if (ptx::elect_one()) {
-            const uint32_t sa = smem_base + (uint32_t)s * sbytes;
+        for (int pass = 0; pass < P.npass; ++pass)
+          for (int kb = kb0; kb < kb1; ++kb, ++it) {
+            const int s = (int)(it % kStages);
+            const uint32_t ph = (uint32_t)((it / kStages) & 1);
+            ptx::mbar_wait(full_bar(s), ph);
+            ptx::tc_fence_after();
+            if (ptx::elect_one()) {
+              const uint32_t sa = smem_base + (uint32_t)s * sbytes;
 #pragma unroll
-            for (int k = 0; k < kBlockK / 16; ++k) {
-              const uint64_t adesc = make_sw128_mnmajor_desc(sa + k * 2048);
-              uint32_t sb = sa + 2 * kBoxBytes;
-              for (int a = 0; a < nacc; ++a) {
-                const int Na = min(256, J - 256 * a);
-                const uint64_t bdesc = make_sw128_mnmajor_desc(sb + k * 2048);
-                umma_bf16_pair(tmem_base + 256u * a, adesc, bdesc, make_idesc_mn(256, Na),
-                               (kb > kb0 || k > 0) ? 1u : 0u);
-                sb += (Na / 128) * kBoxBytes;
+              for (int k = 0; k < kBlockK / 16; ++k) {
+                const uint64_t adesc = make_sw128_mnmajor_desc(sa + k * 2048);
+                uint32_t sb = sa + 2 * kBoxBytes;
+                for (int a = 0; a < nacc; ++a) {
+                  const int Na = min(256, J - 256 * a);
+                  const uint64_t bdesc = make_sw128_mnmajor_desc(sb + k * 2048);
+                  umma_bf16_pair(tmem_base + 256u * a, adesc, bdesc, make_idesc_mn(256, Na),
+                                 (pass > 0 || kb > kb0 || k > 0) ? 1u : 0u);
+                  sb += (Na / 128) * kBoxBytes;
+                }
               }
+              umma_commit_pair(empty_bar(s));
+              if (pass == P.npass - 1 && kb == kb1 - 1) umma_commit_pair(acc_full);
             }
-            umma_commit_pair(empty_bar(s));
-            if (kb == kb1 - 1) umma_commit_pair(acc_full);
+            __syncwarp();
           }
-          __syncwarp();
-        }
       }
     }
   } else {
@@ -270,21 +277,24 @@ int make_dw_map(CUtensorMap* map, const void* ptr, long long rows, int cols, lon
 
 }  // namespace
 
-extern "C" int b200_joint_dw(const void* G, int ldg, const void* H, int ldh, long long n, int V, int J,
-                             float* dW, int max_ctas, b200_stream_t stream) {
+static int joint_dw_impl(const void* G, const void* G_lo, int ldg, const void* H, const void* H_lo, int ldh,
+                        long long n, int V, int J, float* dW, int max_ctas, b200_stream_t stream) {
   B200_CHECK_ARG(G && H && dW, "b200_joint_dw: null pointer");
+  B200_CHECK_ARG((G_lo == nullptr) == (H_lo == nullptr), "b200_joint_dw: G_lo and H_lo go together");
   B200_CHECK_ARG(n > 0 && V > 0, "b200_joint_dw: bad shape n=%lld V=%d", n, V);
   B200_CHECK_ARG(J >= 128 && J <= dw::kMaxJ && J % 128 == 0,
                  "b200_joint_dw: join dim J=%d must be a multiple of 128 in [128, 512]", J);
-  B200_CHECK_ARG(ldg >= V && ldg % 8 == 0 && ((uintptr_t)G & 15) == 0,
+  B200_CHECK_ARG(ldg >= V && ldg % 8 == 0 && (((uintptr_t)G | (uintptr_t)G_lo) & 15) == 0,
                  "b200_joint_dw: ldg=%d must be >= V and a multiple of 8, G 16-byte aligned", ldg);
-  B200_CHECK_ARG(ldh >= J && ldh % 8 == 0 && ((uintptr_t)H & 15) == 0,
+  B200_CHECK_ARG(ldh >= J && ldh % 8 == 0 && (((uintptr_t)H | (uintptr_t)H_lo) & 15) == 0,
                  "b200_joint_dw: ldh=%d must be >= J and a multiple of 8, H 16-byte aligned", ldh);
   B200_CHECK_ARG(((uintptr_t)dW & 15) == 0, "b200_joint_dw: dW must be 16-byte aligned");
   B200_CHECK_ARG((n + dw::kBlockK - 1) / dw::kBlockK < (1ll << 31), "b200_joint_dw: n too large");
-  CUtensorMap gmap, hmap;
+  CUtensorMap gmap, hmap, gmap_lo, hmap_lo;
   if (int rc = make_dw_map(&gmap, G, n, V, (long long)ldg * 2)) return rc;
   if (int rc = make_dw_map(&hmap, H, n, J, (long long)ldh * 2)) return rc;
+  if (int rc = make_dw_map(&gmap_lo, G_lo ? G_lo : G, n, V, (long long)ldg * 2)) return rc;
+  if (int rc = make_dw_map(&hmap_lo, H_lo ? H_lo : H, n, J, (long long)ldh * 2)) return rc;
   int sms = 0, dev = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -297,6 +307,7 @@ extern "C" int b200_joint_dw(const void* G, int ldg, const void* H, int ldh, lon
   P.V = V;
   P.J = J;
   P.n = n;
+  P.npass = G_lo ? 3 : 1;
   P.kblocks = (int)((n + dw::kBlockK - 1) / dw::kBlockK);
   P.nvt = (V + dw::kTileV - 1) / dw::kTileV;
   // K splits: fill `rounds` rounds of the pairs as evenly as possible (V tile fastest), units of
@@ -323,7 +334,20 @@ extern "C" int b200_joint_dw(const void* G, int ldg, const void* H, int ldh, lon
                                        dw::kStages * dw::stage_bytes(dw::kMaxJ) + 1024));
   int grid = 2 * npairs;
   if (P.nvt * P.nsplit < npairs) grid = 2 * P.nvt * P.nsplit;
-  dw::joint_dw_kernel<<<grid, dw::kThreads, smem, (cudaStream_t)stream>>>(gmap, hmap, P);
+  dw::joint_dw_kernel<<<grid, dw::kThreads, smem, (cudaStream_t)stream>>>(gmap, hmap, gmap_lo, hmap_lo, P);
   B200_CHECK_LAUNCH("joint_dw_kernel");
   return B200_OK;
+}
+
+extern "C" int b200_joint_dw(const void* G, int ldg, const void* H, int ldh, long long n, int V, int J,
+                             float* dW, int max_ctas, b200_stream_t stream) {
+  return joint_dw_impl(G, nullptr, ldg, H, nullptr, ldh, n, V, J, dW, max_ctas, stream);
+}
+
+// fp32-accurate form: both operands split (X = X_hi + X_lo, bf16 each): G_hi.H_hi + G_lo.H_hi + G_hi.H_lo
+extern "C" int b200_joint_dw_split(const void* G_hi, const void* G_lo, int ldg, const void* H_hi, const void* H_lo,
+                                   int ldh, long long n, int V, int J, float* dW, int max_ctas,
+                                   b200_stream_t stream) {
+  B200_CHECK_ARG(G_lo && H_lo, "b200_joint_dw_split: null pointer");
+  return joint_dw_impl(G_hi, G_lo, ldg, H_hi, H_lo, ldh, n, V, J, dW, max_ctas, stream);
 }

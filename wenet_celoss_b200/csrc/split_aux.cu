@@ -1,0 +1,389 @@
+// Small kernels around the fp32-accurate (split-bf16) tensor-core path of csrc/split_gemm.cu:
+//   split_f32_kernel        x (fp32) -> x_hi = bf16(x), x_lo = bf16(x - x_hi)
+//   joint_h_split_kernel    H = tanh(e[b,t,:] + p[b,u,:]) in fp32 (joint.py:58-64) -> H_hi, H_lo
+//   joint_pick_kernel       the two logits per lattice cell the RNN-T lattice needs (blank, target), as exact
+//                           fp32 dot products -> lp_blank, lp_emit = logit - lse, and the raw logits for the fix-up
+//   ctc_lp_ext_kernel       log-probs of the blank-interleaved label states, exact fp32 dot products of
+//                           hs[b,t,:] with the gathered ctc_lo rows (ctc.py:57-60) minus lse
+//   rnnt_fixup_kernel       G[cell, blank] -= scale exp(x_b + cb), G[cell, y] -= scale exp(x_y + ce) on the
+//                           split G written by split_gemm MODE_EXP (the sparse terms of the rnnt_loss gradient)
+//   ctc_fixup_kernel        G[b,t,c] -= scale_b * posterior(c at t) for the blank and every distinct label
+//   colsum_split_kernel     d bias[c] = sum_r (G_hi + G_lo)[r, c]
+// All of them are small next to the GEMMs (gathered dot products: 2 or L+1 classes per row out of V).
+#include "common.cuh"
+
+namespace b200 {
+namespace sa {
+
+__device__ __forceinline__ void split1(float x, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+  hi = __float2bfloat16_rn(x);
+  lo = __float2bfloat16_rn(x - __bfloat162float(hi));
+}
+
+__global__ void __launch_bounds__(256)
+split_f32_kernel(const float* __restrict__ x, long long rows, int cols, long long ldx, __nv_bfloat16* __restrict__ hi,
+                 __nv_bfloat16* __restrict__ lo, long long ldo) {
+  const long long total = rows * cols;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cols;
+    const int c = (int)(i - r * cols);
+    __nv_bfloat16 h, l;
+    split1(x[r * ldx + c], h, l);
+    hi[r * ldo + c] = h;
+    lo[r * ldo + c] = l;
+  }
+}
+
+// H[cell, 0:J] for all cells of B utterances; 8 elements per thread (16-byte stores)
+__global__ void __launch_bounds__(256)
+joint_h_split_kernel(const float* __restrict__ e, const float* __restrict__ p, int T, int U1, int J, long long ncells,
+                     __nv_bfloat16* __restrict__ Hhi, __nv_bfloat16* __restrict__ Hlo, int ldh) {
+  const int g8 = J >> 3;
+  const long long total = ncells * g8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long cell = i / g8;
+    const int k0 = (int)(i - cell * g8) << 3;
+    const long long bt = cell / U1;
+    const int u = (int)(cell - bt * U1);
+    const long long b = bt / T;
+    const float4* ep = reinterpret_cast<const float4*>(e + bt * J + k0);
+    const float4* pp = reinterpret_cast<const float4*>(p + (b * U1 + u) * J + k0);
+    const float4 e0 = __ldg(ep), e1 = __ldg(ep + 1), p0 = __ldg(pp), p1 = __ldg(pp + 1);
+    const float v[8] = {tanhf(e0.x + p0.x), tanhf(e0.y + p0.y), tanhf(e0.z + p0.z), tanhf(e0.w + p0.w),
+                        tanhf(e1.x + p1.x), tanhf(e1.y + p1.y), tanhf(e1.z + p1.z), tanhf(e1.w + p1.w)};
+    __align__(16) __nv_bfloat16 h[8], l[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) split1(v[k], h[k], l[k]);
+    *reinterpret_cast<uint4*>(Hhi + cell * ldh + k0) = *reinterpret_cast<const uint4*>(h);
+    *reinterpret_cast<uint4*>(Hlo + cell * ldh + k0) = *reinterpret_cast<const uint4*>(l);
+  }
+}
+
+// one warp per lattice cell: x_blank, x_target as fp32 dot products of tanh(e + p) with two rows of W_out
+__global__ void __launch_bounds__(256)
+joint_pick_kernel(const float* __restrict__ e, const float* __restrict__ p, const float* __restrict__ W,
+                  const float* __restrict__ bias, const int32_t* __restrict__ targets,
+                  const int32_t* __restrict__ logit_len, const int32_t* __restrict__ target_len, int T, int U1, int J,
+                  int blank, long long ncells, const float* __restrict__ lse, float* __restrict__ lp_blank,
+                  float* __restrict__ lp_emit, float2* __restrict__ xbe) {
+  const long long cell = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (cell >= ncells) return;
+  const long long bt = cell / U1;
+  const int u = (int)(cell - bt * U1);
+  const int b = (int)(bt / T), t = (int)(bt - (long long)b * T);
+  if (t >= logit_len[b] || u > target_len[b]) return;
+  const int y = u < target_len[b] ? targets[(long long)b * (U1 - 1) + u] : -1;
+  const float* er = e + bt * J;
+  const float* pr = p + ((long long)b * U1 + u) * J;
+  const float* wb = W + (long long)blank * J;
+  const float* wy = W + (long long)(y >= 0 ? y : blank) * J;
+  float sb = 0.f, sy = 0.f;
+  for (int k = lane * 4; k < J; k += 128) {
+    const float4 ev = __ldg(reinterpret_cast<const float4*>(er + k));
+    const float4 pv = __ldg(reinterpret_cast<const float4*>(pr + k));
+    const float4 a = __ldg(reinterpret_cast<const float4*>(wb + k));
+    const float4 c = __ldg(reinterpret_cast<const float4*>(wy + k));
+    const float h0 = tanhf(ev.x + pv.x), h1 = tanhf(ev.y + pv.y), h2 = tanhf(ev.z + pv.z), h3 = tanhf(ev.w + pv.w);
+    sb += h0 * a.x + h1 * a.y + h2 * a.z + h3 * a.w;
+    sy += h0 * c.x + h1 * c.y + h2 * c.z + h3 * c.w;
+  }
+  sb = warp_sum(sb);
+  sy = warp_sum(sy);
+  if (lane == 0) {
+    const float l = lse[cell];
+    const float xb = sb + bias[blank];
+    const float xy = y >= 0 ? sy + bias[y] : 0.f;
+    lp_blank[cell] = xb - l;
+    lp_emit[cell] = y >= 0 ? xy - l : -INFINITY;
+    xbe[cell] = make_float2(xb, xy);
+  }
+}
+
+// one CTA per (utterance, block of 32 frames, block of 64 label slots): gathered ctc_lo rows of the blank
+// (slot 0) and the utterance's labels (slot 1 + l) in shared memory, thread (frame, slot) accumulates an
+// fp32 dot product over E
+constexpr int kLpFrames = 32;
+constexpr int kLpSlots = 64;
+__global__ void __launch_bounds__(256)
+ctc_lp_ext_kernel(const float* __restrict__ hs, const float* __restrict__ W, const float* __restrict__ bias,
+                  const long long* __restrict__ ys_pad, const int32_t* __restrict__ hlens,
+                  const int32_t* __restrict__ ys_lens, int Tm, int E, int V, int Lmax, int blank,
+                  const float* __restrict__ lse, float* __restrict__ lp_ext) {
+  extern __shared__ float sm[];
+  const int b = blockIdx.y;
+  const int t0 = blockIdx.x * kLpFrames;
+  const int Tb = hlens[b];
+  const int L = ys_lens[b];
+  const int c0 = blockIdx.z * kLpSlots;
+  if (t0 >= Tb || c0 > L) return;
+  const int ncls = min(kLpSlots, L + 1 - c0);
+  const int ldw = E + 1;   // odd pitch: conflict-free column walks
+  float* Ws = sm;                          // [kLpSlots][ldw]
+  float* hs_s = sm + (size_t)kLpSlots * ldw;  // [kLpFrames][ldw]
+  const long long* ys = ys_pad + (long long)b * Lmax;
+  auto class_of = [&](int slot) {
+    int cls = slot == 0 ? blank : (int)ys[slot - 1];
+    return cls;
+  };
+  for (int i = threadIdx.x; i < ncls * E; i += blockDim.x) {
+    const int c = i / E, k = i - c * E;
+    int cls = class_of(c0 + c);
+    if (cls < 0 || cls >= V) cls = blank;
+    Ws[c * ldw + k] = __ldg(W + (long long)cls * E + k);
+  }
+  const int nfr = min(kLpFrames, Tb - t0);
+  for (int i = threadIdx.x; i < nfr * E; i += blockDim.x) {
+    const int f = i / E, k = i - f * E;
+    hs_s[f * ldw + k] = __ldg(hs + ((long long)b * Tm + t0 + f) * E + k);
+  }
+  __syncthreads();
+  const int Smax = 2 * Lmax + 1;
+  for (int o = threadIdx.x; o < nfr * ncls; o += blockDim.x) {
+    const int f = o / ncls, c = o - f * ncls;
+    const float* wr = Ws + c * ldw;
+    const float* hr = hs_s + f * ldw;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    int k = 0;
+    for (; k + 4 <= E; k += 4) {
+      a0 = fmaf(hr[k], wr[k], a0);
+      a1 = fmaf(hr[k + 1], wr[k + 1], a1);
+      a2 = fmaf(hr[k + 2], wr[k + 2], a2);
+      a3 = fmaf(hr[k + 3], wr[k + 3], a3);
+    }
+    for (; k < E; ++k) a0 = fmaf(hr[k], wr[k], a0);
+    const long long rowi = (long long)b * Tm + t0 + f;
+    const int slot = c0 + c;
+    const int cls = class_of(slot);
+    const bool ok = cls >= 0 && cls < V;
+    const float lp = ok ? (a0 + a1) + (a2 + a3) + __ldg(bias + cls) - lse[rowi] : -INFINITY;
+    float* out = lp_ext + rowi * Smax;
+    if (slot == 0) {
+      for (int s = 0; s <= 2 * L; s += 2) out[s] = lp;  // every blank state
+    } else {
+      out[2 * slot - 1] = lp;
+    }
+  }
+}
+
+__device__ __forceinline__ float split_get(const __nv_bfloat16* hi, const __nv_bfloat16* lo, long long i) {
+  return __bfloat162float(hi[i]) + (lo ? __bfloat162float(lo[i]) : 0.f);
+}
+__device__ __forceinline__ void split_put(__nv_bfloat16* hi, __nv_bfloat16* lo, long long i, float v) {
+  __nv_bfloat16 h, l;
+  split1(v, h, l);
+  hi[i] = h;
+  if (lo) lo[i] = l;
+}
+
+// one thread per lattice cell
+__global__ void __launch_bounds__(256)
+rnnt_fixup_kernel(const float4* __restrict__ coef, const float2* __restrict__ xbe, const int32_t* __restrict__ targets,
+                  int T, int U1, int blank, long long ncells, __nv_bfloat16* __restrict__ Ghi,
+                  __nv_bfloat16* __restrict__ Glo, long long ldg) {
+  const long long cell = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (cell >= ncells) return;
+  const float4 c = coef[cell];
+  if (c.w == 0.f) return;
+  const float2 x = xbe[cell];
+  const long long bt = cell / U1;
+  const int u = (int)(cell - bt * U1);
+  const int b = (int)(bt / T);
+  // same if / else-if order as torchaudio when a target equals blank: both terms land on one class
+  float fb = c.y != -INFINITY ? c.w * expf(x.x + c.y) : 0.f;
+  int y = -1;
+  float fe = 0.f;
+  if (c.z != -INFINITY) {
+    y = targets[(long long)b * (U1 - 1) + u];
+    fe = c.w * expf(x.y + c.z);
+  }
+  const long long row = cell * ldg;
+  if (y == blank) {
+    fb += fe;
+    y = -1;
+  }
+  if (fb != 0.f) split_put(Ghi, Glo, row + blank, split_get(Ghi, Glo, row + blank) - fb);
+  if (y >= 0) split_put(Ghi, Glo, row + y, split_get(Ghi, Glo, row + y) - fe);
+}
+
+// one warp per (b, t): posteriors of the extended states, merged per class through the leader table
+__global__ void __launch_bounds__(256)
+ctc_fixup_kernel(const float* __restrict__ lp_ext, const float* __restrict__ alpha, const float* __restrict__ beta,
+                 const double* __restrict__ frame_off, const float* __restrict__ scale,
+                 const long long* __restrict__ ys_pad, const int32_t* __restrict__ hlens,
+                 const int32_t* __restrict__ ys_lens, const int32_t* __restrict__ leader, int B, int Tm, int V, int Lmax,
+                 int blank, __nv_bfloat16* __restrict__ Ghi, __nv_bfloat16* __restrict__ Glo, long long ldg) {
+  extern __shared__ float occ_all[];  // [8][Smax]
+  const long long rowi = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (rowi >= (long long)B * Tm) return;
+  const int Smax = 2 * Lmax + 1;
+  float* occ = occ_all + (threadIdx.x >> 5) * Smax;
+  const int b = (int)(rowi / Tm), t = (int)(rowi - (long long)b * Tm);
+  const float sc = scale[b];
+  if (t >= hlens[b] || sc == 0.f) return;
+  const int S = 2 * ys_lens[b] + 1;
+  const double* oa = frame_off + (long long)b * 2 * (Tm + 1);
+  const float nl = (float)(oa[t] + oa[Tm + 1 + t] - oa[Tm]);
+  const float* al = alpha + rowi * Smax;
+  const float* be = beta + rowi * Smax;
+  const float* lp = lp_ext + rowi * Smax;
+  const int32_t* ld = leader + (long long)b * Smax;
+  const long long* ys = ys_pad + (long long)b * Lmax;
+  for (int s = lane; s < S; s += 32) occ[s] = 0.f;
+  __syncwarp();
+  float occ_blank = 0.f;
+  for (int s = lane; s < S; s += 32) {
+    const float post = expf(al[s] + be[s] + nl - lp[s]);  // alpha*beta counts the emission at t twice
+    if (s & 1)
+      atomicAdd(&occ[ld[s]], post);
+    else
+      occ_blank += post;
+  }
+  occ_blank = warp_sum(occ_blank);
+  __syncwarp();
+  const long long row = rowi * ldg;
+  if (lane == 0) split_put(Ghi, Glo, row + blank, split_get(Ghi, Glo, row + blank) - sc * occ_blank);
+  for (int s = 1 + 2 * lane; s < S; s += 64) {
+    if (ld[s] != s) continue;  // the first state of each distinct label carries the class total
+    const int c = (int)ys[s >> 1];
+    if (c < 0 || c >= V || c == blank) continue;
+    split_put(Ghi, Glo, row + c, split_get(Ghi, Glo, row + c) - sc * occ[s]);
+  }
+}
+
+// grid (column blocks of 256, row slabs); thread = one column pair over a slab of rows
+__global__ void __launch_bounds__(128)
+colsum_split_kernel(const __nv_bfloat16* __restrict__ Ghi, const __nv_bfloat16* __restrict__ Glo, long long rows, int N,
+                    long long ldg, long long rows_per_slab, float* __restrict__ out) {
+  const int c = (blockIdx.x * 128 + threadIdx.x) * 2;
+  if (c >= N) return;
+  const long long r0 = blockIdx.y * rows_per_slab;
+  const long long r1 = min(rows, r0 + rows_per_slab);
+  float s0 = 0.f, s1 = 0.f;
+  const bool pair_ok = c + 1 < N;
+  for (long long r = r0; r < r1; ++r) {
+    const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(Ghi + r * ldg + c);
+    float2 v = __bfloat1622float2(h);
+    if (Glo) {
+      const float2 w = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(Glo + r * ldg + c));
+      v.x += w.x;
+      v.y += w.y;
+    }
+    s0 += v.x;
+    s1 += v.y;
+  }
+  atomicAdd(out + c, s0);
+  if (pair_ok) atomicAdd(out + c + 1, s1);
+}
+
+}  // namespace sa
+}  // namespace b200
+
+using namespace b200;
+
+static int grid_for(long long items, int per_block, int cap) {
+  long long g = (items + per_block - 1) / per_block;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+extern "C" int b200_split_f32(const float* x, long long rows, int cols, long long ldx, void* hi, void* lo,
+                              long long ldo, b200_stream_t stream) {
+  B200_CHECK_ARG(x && hi && lo && rows > 0 && cols > 0 && ldx >= cols && ldo >= cols, "b200_split_f32: bad arguments");
+  sa::split_f32_kernel<<<grid_for(rows * cols, 256, 148 * 16), 256, 0, (cudaStream_t)stream>>>(
+      x, rows, cols, ldx, reinterpret_cast<__nv_bfloat16*>(hi), reinterpret_cast<__nv_bfloat16*>(lo), ldo);
+  B200_CHECK_LAUNCH("split_f32_kernel");
+  return B200_OK;
+}
+
+extern "C" int b200_joint_h_split(const float* e, const float* p, int B, int T, int U1, int J, void* H_hi, void* H_lo,
+                                  int ldh, b200_stream_t stream) {
+  B200_CHECK_ARG(e && p && H_hi && H_lo, "b200_joint_h_split: null pointer");
+  B200_CHECK_ARG(B > 0 && T > 0 && U1 > 0 && J > 0 && J % 8 == 0 && ldh >= J && ldh % 8 == 0,
+                 "b200_joint_h_split: bad shape (J and ldh multiples of 8)");
+  B200_CHECK_ARG((((uintptr_t)e | (uintptr_t)p | (uintptr_t)H_hi | (uintptr_t)H_lo) & 15) == 0,
+                 "b200_joint_h_split: pointers must be 16-byte aligned");
+  const long long ncells = (long long)B * T * U1;
+  sa::joint_h_split_kernel<<<grid_for(ncells * (J / 8), 256, 148 * 16), 256, 0, (cudaStream_t)stream>>>(
+      e, p, T, U1, J, ncells, reinterpret_cast<__nv_bfloat16*>(H_hi), reinterpret_cast<__nv_bfloat16*>(H_lo), ldh);
+  B200_CHECK_LAUNCH("joint_h_split_kernel");
+  return B200_OK;
+}
+
+extern "C" int b200_joint_pick(const float* e, const float* p, const float* W, const float* bias,
+                               const int32_t* targets, const int32_t* logit_len, const int32_t* target_len, int B,
+                               int T, int U1, int V, int J, int blank, const float* lse, float* lp_blank,
+                               float* lp_emit, float* xbe, b200_stream_t stream) {
+  B200_CHECK_ARG(e && p && W && bias && logit_len && target_len && lse && lp_blank && lp_emit && xbe &&
+                     (U1 == 1 || targets),
+                 "b200_joint_pick: null pointer");
+  B200_CHECK_ARG(J % 4 == 0 && blank >= 0 && blank < V, "b200_joint_pick: J %% 4, blank in range");
+  B200_CHECK_ARG((((uintptr_t)e | (uintptr_t)p | (uintptr_t)W) & 15) == 0 && ((uintptr_t)xbe & 7) == 0,
+                 "b200_joint_pick: e, p, W must be 16-byte aligned");
+  const long long ncells = (long long)B * T * U1;
+  sa::joint_pick_kernel<<<(unsigned)((ncells + 7) / 8), 256, 0, (cudaStream_t)stream>>>(
+      e, p, W, bias, targets, logit_len, target_len, T, U1, J, blank, ncells, lse, lp_blank, lp_emit,
+      reinterpret_cast<float2*>(xbe));
+  B200_CHECK_LAUNCH("joint_pick_kernel");
+  return B200_OK;
+}
+
+extern "C" int b200_ctc_lp_ext(const float* hs, const float* W, const float* bias, const int64_t* ys_pad,
+                               const int32_t* hlens, const int32_t* ys_lens, int B, int T, int E, int V, int Lmax,
+                               int blank, const float* lse, float* lp_ext, b200_stream_t stream) {
+  B200_CHECK_ARG(hs && W && bias && hlens && ys_lens && lse && lp_ext && (Lmax == 0 || ys_pad),
+                 "b200_ctc_lp_ext: null pointer");
+  B200_CHECK_ARG(B > 0 && T > 0 && E > 0 && V > 0 && Lmax >= 0 && blank >= 0 && blank < V, "b200_ctc_lp_ext: bad shape");
+  const size_t smem = (size_t)(sa::kLpSlots + sa::kLpFrames) * (E + 1) * sizeof(float);
+  B200_CHECK_ARG(smem <= 200 * 1024, "b200_ctc_lp_ext: encoder dim E=%d too large (96 * (E + 1) floats of shared memory)", E);
+  B200_CHECK_CUDA(cudaFuncSetAttribute(sa::ctc_lp_ext_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  dim3 grid((T + sa::kLpFrames - 1) / sa::kLpFrames, B, (Lmax + 1 + sa::kLpSlots - 1) / sa::kLpSlots);
+  sa::ctc_lp_ext_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(hs, W, bias, reinterpret_cast<const long long*>(ys_pad),
+                                                                   hlens, ys_lens, T, E, V, Lmax, blank, lse, lp_ext);
+  B200_CHECK_LAUNCH("ctc_lp_ext_kernel");
+  return B200_OK;
+}
+
+extern "C" int b200_rnnt_fixup(const float* coef, const float* xbe, const int32_t* targets, int B, int T, int U1,
+                               int V, int blank, void* G_hi, void* G_lo, long long ldg, b200_stream_t stream) {
+  B200_CHECK_ARG(coef && xbe && G_hi && (U1 == 1 || targets), "b200_rnnt_fixup: null pointer");
+  B200_CHECK_ARG(blank >= 0 && blank < V && ldg >= V, "b200_rnnt_fixup: bad arguments");
+  const long long ncells = (long long)B * T * U1;
+  sa::rnnt_fixup_kernel<<<(unsigned)((ncells + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const float4*>(coef), reinterpret_cast<const float2*>(xbe), targets, T, U1, blank, ncells,
+      reinterpret_cast<__nv_bfloat16*>(G_hi), reinterpret_cast<__nv_bfloat16*>(G_lo), ldg);
+  B200_CHECK_LAUNCH("rnnt_fixup_kernel");
+  return B200_OK;
+}
+
+extern "C" int b200_ctc_fixup(const float* lp_ext, const float* alpha, const float* beta, const double* frame_off,
+                              const float* scale, const int64_t* ys_pad, const int32_t* hlens,
+                              const int32_t* ys_lens, const int32_t* leader, int B, int T, int V, int Lmax, int blank,
+                              void* G_hi, void* G_lo, long long ldg, b200_stream_t stream) {
+  B200_CHECK_ARG(lp_ext && alpha && beta && frame_off && scale && hlens && ys_lens && leader && G_hi,
+                 "b200_ctc_fixup: null pointer");
+  const int Smax = 2 * Lmax + 1;
+  const long long rows = (long long)B * T;
+  sa::ctc_fixup_kernel<<<(unsigned)((rows + 7) / 8), 256, 8 * Smax * sizeof(float), (cudaStream_t)stream>>>(
+      lp_ext, alpha, beta, frame_off, scale, reinterpret_cast<const long long*>(ys_pad), hlens, ys_lens, leader, B, T, V,
+      Lmax, blank, reinterpret_cast<__nv_bfloat16*>(G_hi), reinterpret_cast<__nv_bfloat16*>(G_lo), ldg);
+  B200_CHECK_LAUNCH("ctc_fixup_kernel");
+  return B200_OK;
+}
+
+extern "C" int b200_colsum_split(const void* G_hi, const void* G_lo, long long rows, int N, long long ldg, float* out,
+                                 b200_stream_t stream) {
+  B200_CHECK_ARG(G_hi && out && rows > 0 && N > 0 && ldg >= N && ldg % 2 == 0, "b200_colsum_split: bad arguments");
+  const int cblocks = (N + 255) / 256;
+  int slabs = (148 * 8 + cblocks - 1) / cblocks;
+  if (slabs > rows) slabs = (int)rows;
+  const long long per = (rows + slabs - 1) / slabs;
+  dim3 grid(cblocks, (unsigned)((rows + per - 1) / per));
+  sa::colsum_split_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(reinterpret_cast<const __nv_bfloat16*>(G_hi),
+                                                                  reinterpret_cast<const __nv_bfloat16*>(G_lo), rows, N,
+                                                                  ldg, per, out);
+  B200_CHECK_LAUNCH("colsum_split_kernel");
+  return B200_OK;
+}

@@ -179,6 +179,116 @@ class _FusedJointLossFn(torch.autograd.Function):
                 None, None, None, None, None)
 
 
+def split_f32(x: torch.Tensor):
+    """(hi, lo) bf16 pair of a 2-D fp32 tensor: hi = bf16(x), lo = bf16(x - hi)."""
+    x = x.detach().float().contiguous()
+    rows, cols = x.shape
+    hi = torch.empty(rows, cols, dtype=torch.bfloat16, device=x.device)
+    lo = torch.empty_like(hi)
+    _lib.call("b200_split_f32", ptr(x), _i64(rows), i32(cols), _i64(cols), ptr(hi), ptr(lo), _i64(cols),
+              _lib.stream_handle(x.device))
+    return hi, lo
+
+
+class _FusedJointLossFp32Fn(torch.autograd.Function):
+    """The same fusion with fp32-accurate GEMMs (split-bf16 operands, csrc/split_gemm.cu): the mode for
+    the reference's fp32 configuration (BASELINE configs[1], rtol 1e-4)."""
+
+    @staticmethod
+    @custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    def forward(ctx, e, p, w_out, b_out, targets, logit_lengths, target_lengths, blank, max_ctas=0):
+        dev = e.device
+        with torch.cuda.device(dev):
+            st = _lib.stream_handle(dev)
+            e32 = e.detach().float().contiguous()
+            p32 = p.detach().float().contiguous()
+            w32 = w_out.detach().float().contiguous()
+            b32 = b_out.detach().float().contiguous()
+            B, T, J = e32.shape
+            U1 = p32.shape[1]
+            V = w32.shape[0]
+            ncells = B * T * U1
+            w_hi, w_lo = split_f32(w32)
+            bias_pad = _pad_bias(b_out, V)
+            H_hi = torch.empty(ncells, J, dtype=torch.bfloat16, device=dev)
+            H_lo = torch.empty_like(H_hi)
+            _lib.call("b200_joint_h_split", ptr(e32), ptr(p32), i32(B), i32(T), i32(U1), i32(J), ptr(H_hi),
+                      ptr(H_lo), i32(J), st)
+            lat = torch.zeros(3, B, T, U1, dtype=torch.float32, device=dev)
+            lse, lpb, lpe = lat.unbind(0)
+            _lib.call("b200_split_gemm_lse", ptr(H_hi), ptr(H_lo), _i64(ncells), i32(J), i32(J), ptr(w_hi),
+                      ptr(w_lo), i32(V), i32(J), ptr(bias_pad), ptr(lse), i32(max_ctas), st)
+            xbe = torch.zeros(B, T, U1, 2, dtype=torch.float32, device=dev)
+            _lib.call("b200_joint_pick", ptr(e32), ptr(p32), ptr(w32), ptr(b32), ptr(targets),
+                      ptr(logit_lengths), ptr(target_lengths), i32(B), i32(T), i32(U1), i32(V), i32(J),
+                      i32(blank), ptr(lse), ptr(lpb), ptr(lpe), ptr(xbe), st)
+            alpha, beta, costs, diag_off = rnnt_lattice(lpb, lpe, logit_lengths, target_lengths)
+        ctx.save_for_backward(w32, w_hi, w_lo, bias_pad, targets, logit_lengths, target_lengths, lse, alpha,
+                              beta, diag_off, H_hi, H_lo, xbe)
+        ctx.shape = (B, T, U1, V, J)
+        ctx.blank = blank
+        ctx.max_ctas = max_ctas
+        ctx.in_dtypes = (e.dtype, p.dtype, w_out.dtype, b_out.dtype)
+        return costs
+
+    @staticmethod
+    @custom_bwd(device_type="cuda")
+    def backward(ctx, dy):
+        (w32, w_hi, w_lo, bias_pad, targets, logit_lengths, target_lengths, lse, alpha, beta, diag_off,
+         H_hi_all, H_lo_all, xbe) = ctx.saved_tensors
+        B, T, U1, V, J = ctx.shape
+        dev = w32.device
+        blank = ctx.blank
+        mc = ctx.max_ctas
+        with torch.cuda.device(dev):
+            st = _lib.stream_handle(dev)
+            dyf = dy.detach().to(torch.float32).contiguous()
+            coef = rnnt_grad_coef(lse, alpha, beta, diag_off, dyf, targets, logit_lengths,
+                                  target_lengths, blank)
+            per_utt = T * U1
+            ldg = (V + 15) // 16 * 16
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            nb = _chunk_utts(B, per_utt, 2 * ldg, sms)  # two scratch arrays (G_hi, G_lo)
+            G_hi = torch.empty(nb * per_utt, ldg, dtype=torch.bfloat16, device=dev)
+            G_lo = torch.empty_like(G_hi)
+            own = J in (256, 512)  # csrc/joint_dw.cu / joint_dh.cu tile shapes (the reference's join_dim is 512)
+            dW = torch.zeros(V, J, dtype=torch.float32, device=dev)
+            db = torch.zeros(V, dtype=torch.float32, device=dev)
+            de = torch.zeros(B, T, J, dtype=torch.float32, device=dev)
+            dp = torch.zeros(B, U1, J, dtype=torch.float32, device=dev)
+            tg = targets.view(B, -1)
+            for b0 in range(0, B, nb):
+                b1 = min(B, b0 + nb)
+                n = (b1 - b0) * per_utt
+                H_hi = H_hi_all[b0 * per_utt:b1 * per_utt]
+                H_lo = H_lo_all[b0 * per_utt:b1 * per_utt]
+                cf = coef[b0:b1]
+                # G = scale * softmax-part of d loss / d logits, then the sparse blank / target terms
+                _lib.call("b200_split_gemm_exp", ptr(H_hi), ptr(H_lo), _i64(n), i32(J), i32(J), ptr(w_hi),
+                          ptr(w_lo), i32(V), i32(J), ptr(bias_pad), ptr(cf), ptr(G_hi), ptr(G_lo), _i64(ldg),
+                          i32(mc), st)
+                _lib.call("b200_rnnt_fixup", ptr(cf), ptr(xbe[b0:b1]), ptr(tg[b0:b1]), i32(b1 - b0), i32(T),
+                          i32(U1), i32(V), i32(blank), ptr(G_hi), ptr(G_lo), _i64(ldg), st)
+                _lib.call("b200_colsum_split", ptr(G_hi), ptr(G_lo), _i64(n), i32(V), _i64(ldg), ptr(db), st)
+                if own:
+                    _lib.call("b200_joint_dw_split", ptr(G_hi), ptr(G_lo), i32(ldg), ptr(H_hi), ptr(H_lo),
+                              i32(J), _i64(n), i32(V), i32(J), ptr(dW), i32(mc), st)
+                    _lib.call("b200_joint_dh_split", ptr(G_hi), ptr(G_lo), i32(ldg), ptr(w_hi), ptr(w_lo),
+                              ptr(H_hi), ptr(H_lo), i32(J), i32(b1 - b0), i32(T), i32(U1), i32(V), i32(J),
+                              ptr(logit_lengths[b0:b1]), ptr(target_lengths[b0:b1]), ptr(de[b0:b1]),
+                              ptr(dp[b0:b1]), i32(mc), st)
+                else:  # other join dims: library GEMMs on the recombined operands
+                    Gf = G_hi[:n, :V].float() + G_lo[:n, :V].float()
+                    Hf = H_hi.float() + H_lo.float()
+                    dW += Gf.t() @ Hf
+                    dz = ((Gf @ w32) * (1 - Hf * Hf)).view(b1 - b0, T, U1, J)
+                    de[b0:b1] = dz.sum(2)
+                    dp[b0:b1] = dz.sum(1)
+                    del Gf, Hf, dz
+        dt_e, dt_p, dt_w, dt_b = ctx.in_dtypes
+        return (de.to(dt_e), dp.to(dt_p), dW.to(dt_w), db.to(dt_b), None, None, None, None, None)
+
+
 def _check_joint_module(joint) -> None:
     for name in ("enc_ffn", "pred_ffn", "ffn_out"):
         if getattr(joint, name, None) is None:
@@ -198,17 +308,24 @@ def _check_joint_module(joint) -> None:
 def fused_joint_rnnt_loss(joint, enc_out: torch.Tensor, pred_out: torch.Tensor,
                           targets: torch.Tensor, logit_lengths: torch.Tensor,
                           target_lengths: torch.Tensor, blank: int = 0,
-                          reduction: str = "mean", *, _max_ctas: int = 0,
+                          reduction: str = "mean", *, precision: str = "auto", _max_ctas: int = 0,
                           _use_bound: bool = True) -> torch.Tensor:
     """RNN-T loss of ``joint(enc_out, pred_out)`` without materialising the logits.
 
     enc_out [B,T,E], pred_out [B,U+1,P]; targets [B,U] int32 zero-padded; lengths int32
     (exactly what transducer.py:137-141 prepares for torchaudio).
 
+    ``precision``: "bf16" rounds the operands of the vocabulary GEMMs to bf16 (fp32 accumulate; the
+    reference's autocast configuration, rtol 1e-2), "fp32" feeds them as split bf16 pairs (three
+    tensor-core products per GEMM, results within rtol 1e-4 of the reference's fp32 run), "auto"
+    = "bf16" under autocast or for half-precision inputs, else "fp32".
+
     ``_max_ctas`` / ``_use_bound`` are test hooks: cap the persistent grids (so that every CTA
     walks many tiles on small shapes) and force the running-maximum epilogue."""
     if reduction not in ("none", "mean", "sum"):
         raise ValueError('reduction should be one of "none", "mean", or "sum"')
+    if precision not in ("auto", "bf16", "fp32"):
+        raise ValueError('precision should be one of "auto", "bf16", or "fp32"')
     _check_joint_module(joint)
     _lib.require_cuda(enc_out, "enc_out")
     V = joint.ffn_out.out_features
@@ -220,9 +337,16 @@ def fused_joint_rnnt_loss(joint, enc_out: torch.Tensor, pred_out: torch.Tensor,
     _validate_shapes((B, T, U1, V), targets, logit_lengths, target_lengths, blank)
     e = joint.enc_ffn(enc_out)    # [B,T,J]   library GEMM (joint.py:55)
     p = joint.pred_ffn(pred_out)  # [B,U1,J]  library GEMM (joint.py:56)
-    costs = _FusedJointLossFn.apply(e, p, joint.ffn_out.weight, joint.ffn_out.bias, targets,
-                                    logit_lengths, target_lengths, int(blank), int(_max_ctas),
-                                    bool(_use_bound))
+    if precision == "auto":
+        half = enc_out.dtype != torch.float32 or joint.ffn_out.weight.dtype != torch.float32
+        precision = "bf16" if half or torch.is_autocast_enabled("cuda") else "fp32"
+    if precision == "fp32":
+        costs = _FusedJointLossFp32Fn.apply(e, p, joint.ffn_out.weight, joint.ffn_out.bias, targets,
+                                            logit_lengths, target_lengths, int(blank), int(_max_ctas))
+    else:
+        costs = _FusedJointLossFn.apply(e, p, joint.ffn_out.weight, joint.ffn_out.bias, targets,
+                                        logit_lengths, target_lengths, int(blank), int(_max_ctas),
+                                        bool(_use_bound))
     if reduction == "mean":
         return costs.mean()
     if reduction == "sum":
