@@ -359,7 +359,8 @@ class RnntFusedWorkload:
         for p in self.params:
             p.grad = None
         loss = self.pkg.fused_joint_rnnt_loss(self.joint, self.enc, self.pred, self.targets, self.tl,
-                                              self.ul, blank=0, reduction=self.reduction)
+                                              self.ul, blank=0, reduction=self.reduction,
+                                              precision=self.cfg.get("precision", "bf16"))
         loss.backward()
         return loss
 
@@ -505,7 +506,7 @@ class RnntFusedWorkload:
         with torch.no_grad():
             j = self.joint
             fused = self.pkg.fused_joint_rnnt_loss(j, self.enc, self.pred, self.targets, self.tl, self.ul,
-                                                   blank=0, reduction="none")
+                                                   blank=0, reduction="none", precision="bf16")
             e = j.enc_ffn(self.enc[:1]).float()
             p = j.pred_ffn(self.pred[:1]).float()
             h = torch.tanh(e[:, :, None] + p[:, None]).to(torch.bfloat16)
@@ -692,9 +693,9 @@ def extra_rows(cfg, dev, pk):
     out["ctc"] = {"value": B5 / (ms * 1e-3), "unit": "utt/s", "ms": ms,
                   "loss_only_ms": ms_k, "loss_only_utts_per_sec": B5 / (ms_k * 1e-3),
                   "loss_only_frac_of_hbm_roofline": 3.0 * B5 * T5 * V * 4 / (ms_k * 1e-3) / 1e9 / pk["hbm"],
-                  "workload": "cfg5: CTC.forward+backward B=64 T=1000 V=5000 L<=100 fp32; 'ms' includes "
-                              "the fp32 ctc_lo library GEMMs, 'loss_only' is ctc_loss(logits) fwd+bwd "
-                              "(3*B*T*V*4 algorithmic bytes)"}
+                  "workload": "cfg5: CTC.forward+backward B=64 T=1000 V=5000 L<=100 fp32; 'ms' = the fused "
+                              "module (ctc_lo + log_softmax + loss in split_gemm, no logits in HBM), 'loss_only' "
+                              "is ctc_loss(logits) fwd+bwd on given logits (3*B*T*V*4 algorithmic bytes)"}
     # SURVEY 8(f) rows 2 and 4 on the cfg5 shape: CTC prefix beam search (beam 10) and forced alignment
     from wenet_celoss_b200.ctc_search import ctc_prefix_beam_search_batch, forced_align_batch
     with torch.no_grad():
@@ -727,6 +728,30 @@ def extra_rows(cfg, dev, pk):
 
 # --------------------------------------------------------------------------- GPU reference
 CFG2 = dict(B=32, T=250, U=40, V=4233, E=256, P=256, J=512)
+
+
+class RnntFusedFp32Workload(RnntFusedWorkload):
+    """BASELINE configs[1]: the same fused step in the reference's fp32 configuration (B=32 T=250 U=40
+    V=4233 J=512), vocabulary GEMMs as split-bf16 tcgen05 products (rtol 1e-4: tests/test_fp32_path_gpu.py)."""
+    name, dtype, base_cfg = "rnnt_fused_fp32", "f32", dict(CFG2, precision="fp32")
+    self_check = None
+
+    def roofline(self, pk, ms_step):
+        # the three GEMMs of joint.py:68-69 and its autograd over all cells: logits, d W_out, d H
+        c = self.cfg
+        flops = 3 * 2.0 * self.cells * c["J"] * c["V"]
+        tf = flops / (ms_step * 1e-3) / 1e12
+        return {"bound": "tensor", "kernel": "whole step (split_gemm LSE / EXP, joint_dw, joint_dh, lattice, enc/pred ffn)",
+                "achieved": tf, "peak": pk["bf16"], "unit": "TFLOP/s", "frac": tf / pk["bf16"], "traffic": None,
+                "peak_source": pk["source"], "algorithmic_flops_per_step": flops, "issued_flops_per_step": 4.0 * flops,
+                "note": "fp32-accurate mode: 3 bf16 products per GEMM (hi.hi + lo.hi + hi.lo) and the logits are "
+                        "recomputed in the backward pass, i.e. 4x the algorithmic flops are issued"}
+
+    def describe(self):
+        c = self.cfg
+        return (f"rnnt_fused_fp32: joint + RNN-T loss fwd+bwd, logits never materialised, B={c['B']} T={c['T']} "
+                f"U={c['U']} V={c['V']} J={c['J']} per GPU (cfg2), fp32-accurate split-bf16 MMA operands",
+                "L2 flushed by the step itself: each step streams 5.6 GB of split gradient scratch")
 
 
 def _eager_joint(joint, enc, pred):
@@ -762,7 +787,7 @@ def gpu_reference(cfg, dev, pk):
                    "kernels (fp32, allow_tf32=False as torch defaults); 'ours' = this package on the same inputs"}
     g = torch.Generator().manual_seed(777)
 
-    def fused_pair(c, tag, dtype_note):
+    def fused_pair(c, tag, dtype_note, precisions=("bf16",)):
         B, T, U, V, E, P, J = (c[k] for k in ("B", "T", "U", "V", "E", "P", "J"))
         torch.manual_seed(1234)
         joint = _Joint(V, E, P, J).to(dev)
@@ -800,18 +825,21 @@ def gpu_reference(cfg, dev, pk):
                            reference_peak_mem_gb=torch.cuda.max_memory_allocated() / 1e9,
                            reference_loss=float(ref_step().item()))
 
-                def our_step():
-                    enc.grad = pred.grad = None
-                    for p_ in params:
-                        p_.grad = None
-                    loss = pkg.fused_joint_rnnt_loss(joint, enc, pred, tgt[:b_ref], tl, ul, blank=0,
-                                                     reduction="mean")
-                    loss.backward()
-                    return loss
+                for k, prec in enumerate(precisions):
+                    def our_step():
+                        enc.grad = pred.grad = None
+                        for p_ in params:
+                            p_.grad = None
+                        loss = pkg.fused_joint_rnnt_loss(joint, enc, pred, tgt[:b_ref], tl, ul, blank=0,
+                                                         reduction="mean", precision=prec)
+                        loss.backward()
+                        return loss
 
-                ours_ms = _timed_cuda(our_step, reps=3)
-                row.update(ours_ms=ours_ms, ours_utts_per_sec=b_ref / (ours_ms * 1e-3),
-                           ours_loss=float(our_step().item()), speedup=ms / ours_ms)
+                    ours_ms = _timed_cuda(our_step, reps=3)
+                    sfx = "" if k == 0 else "_" + prec
+                    row.update({"ours_precision" + sfx: prec, "ours_ms" + sfx: ours_ms,
+                                "ours_utts_per_sec" + sfx: b_ref / (ours_ms * 1e-3),
+                                "ours_loss" + sfx: float(our_step().item()), "speedup" + sfx: ms / ours_ms})
                 break
             except torch.OutOfMemoryError:
                 b_ref //= 2
@@ -819,7 +847,9 @@ def gpu_reference(cfg, dev, pk):
         del joint
         torch.cuda.empty_cache()
 
-    fused_pair(CFG2, "cfg2_joint_rnnt", "reference fp32 (SIMT GEMMs); ours bf16 MMA operands")
+    fused_pair(CFG2, "cfg2_joint_rnnt", "reference fp32 (SIMT GEMMs); ours precision='fp32' = split-bf16 tcgen05 "
+               "(3 products per GEMM, rtol 1e-4: tests/test_fp32_path_gpu.py); '_bf16' keys = bf16 MMA operands",
+               precisions=("fp32", "bf16"))
     fused_pair(cfg, "cfg3_joint_rnnt", "reference fp32 (SIMT GEMMs); ours bf16 MMA operands")
 
     # (b) rnnt_loss alone on materialised logits: torchaudio CUDA vs this package, same tensor
@@ -1024,16 +1054,23 @@ class CtcWorkload:
     e2e_note = "CTC.forward API: encoder outputs, padded labels and lengths copied from pinned host memory every step"
 
     def roofline(self, pk, ms_step):
+        # fused module: no [B,T,V] logits in HBM; the step is the three GEMMs of ctc.py:57 and its autograd
+        # (logits, d ctc_lo.weight, d hs: 6*B*T*E*V flops).  Issued: 4 GEMMs (the logits are recomputed in the
+        # backward pass) x 3 bf16 products each (fp32-accurate split operands)
         c = self.cfg
-        nbytes = 3.0 * c["B"] * c["T"] * c["V"] * 4
-        return {"bound": "hbm", "kernel": "CTC.forward+backward (whole step)", "achieved": nbytes / (ms_step * 1e-3) / 1e9,
-                "peak": pk["hbm"], "unit": "GB/s", "frac": nbytes / (ms_step * 1e-3) / 1e9 / pk["hbm"], "traffic": None,
-                "peak_source": pk["source"], "algorithmic_bytes_per_step": nbytes}
+        flops = 6.0 * c["B"] * c["T"] * c["E"] * c["V"]
+        tf = flops / (ms_step * 1e-3) / 1e12
+        return {"bound": "tensor", "kernel": "CTC.forward+backward (whole step: split_gemm LSE / EXP, dW, d hs, trellis)",
+                "achieved": tf, "peak": pk["bf16"], "unit": "TFLOP/s", "frac": tf / pk["bf16"], "traffic": None,
+                "peak_source": pk["source"], "algorithmic_flops_per_step": flops,
+                "issued_flops_per_step": 4.0 * flops,
+                "note": "fp32-accurate mode issues 3 bf16 products per GEMM and recomputes the logits in the "
+                        "backward pass; the serial trellis (T dependent frames) is inside the step"}
 
     def describe(self):
         c = self.cfg
         return (f"ctc: CTC.forward+backward B={c['B']} T={c['T']} V={c['V']} L<={c['L']} per GPU (cfg5), fp32",
-                "logits (1.28 GB at B=64) larger than L2")
+                "split G scratch (2 x 0.64 GB at B=64) larger than L2")
 
 
 class SearchWorkload:
@@ -1098,7 +1135,8 @@ class BeamWorkload(SearchWorkload):
     mode = "beam"
 
 
-WORKLOADS = {"rnnt_logits": RnntLogitsWorkload, "rnnt_fused": RnntFusedWorkload, "ctc": CtcWorkload,
+WORKLOADS = {"rnnt_logits": RnntLogitsWorkload, "rnnt_fused": RnntFusedWorkload,
+             "rnnt_fused_fp32": RnntFusedFp32Workload, "ctc": CtcWorkload,
              "greedy": SearchWorkload, "beam": BeamWorkload}
 
 
@@ -1178,7 +1216,7 @@ def main():
             loss = red if red is not None else loss
         return loss
 
-    check = wl.self_check() if hasattr(wl, "self_check") else None
+    check = wl.self_check() if getattr(wl, "self_check", None) else None
     for _ in range(args.warmup):
         full_step()
     sync_all()
