@@ -1283,7 +1283,10 @@ def main():
 
     if rank == 0:
         roof = wl.roofline(pk, ms / args.steps)
-        cb = None if args.no_cpu_baseline else cpu_baseline(dict(CFG3))
+        # the CPU port of the SAME workload: the joint + rnnt_loss chain at this workload's shape (cfg3, or cfg2
+        # for the fp32 row); the secondary workloads (ctc, searches) carry their CPU ports inside `extra`
+        cb_cfg = dict(getattr(wcls, "base_cfg", CFG3)) if args.workload.startswith("rnnt") else None
+        cb = None if (args.no_cpu_baseline or cb_cfg is None) else cpu_baseline(cb_cfg)
         desc, l2 = wl.describe()
         line = {
             "metric": getattr(wl, "metric", METRIC), "value": value, "unit": UNIT, "n_gpus": world,

@@ -37,12 +37,25 @@ def _case(B, T, U, V, E, J, seed, ragged=True):
     return joint, enc, pred, tgt, tl, ul
 
 
-def _reference(joint, enc, pred, tgt, tl, ul, reduction="mean"):
+def _round_bf16_st(x):
+    """x rounded to bf16 in the forward pass, identity in the backward pass (what a bf16 MMA operand is)."""
+    return x + (x.detach().bfloat16().float() - x.detach())
+
+
+def _reference(joint, enc, pred, tgt, tl, ul, reduction="mean", bf16_operands=False):
+    """The reference chain TransducerJoint.forward + torchaudio rnnt_loss in fp32 on the host.
+    ``bf16_operands``: the same chain with the two operands of the vocabulary GEMM (tanh output and
+    ffn_out.weight) rounded to bf16, fp32 accumulation - the arithmetic the fused bf16 mode specifies."""
     j = copy.deepcopy(joint)
     enc = enc.clone().requires_grad_(True)
     pred = pred.clone().requires_grad_(True)
-    loss = torchaudio.functional.rnnt_loss(orc.joint_logits(enc, pred, j), tgt, tl, ul, blank=0,
-                                           reduction=reduction)
+    if bf16_operands:
+        h = torch.tanh(j.enc_ffn(enc)[:, :, None] + j.pred_ffn(pred)[:, None])
+        logits = _round_bf16_st(h) @ _round_bf16_st(j.ffn_out.weight).t() + j.ffn_out.bias
+    else:
+        logits = orc.joint_logits(enc, pred, j)
+    loss = torchaudio.functional.rnnt_loss(logits, tgt, tl, ul, blank=0, reduction=reduction)
+    del logits
     loss.sum().backward()
     grads = {"enc": enc.grad, "pred": pred.grad}
     grads.update({n: p.grad for n, p in j.named_parameters()})

@@ -74,15 +74,30 @@ def test_many_tiles_j256():
 @pytest.mark.parametrize("ragged", [False, True])
 def test_cfg3_slice(ragged):
     """B=2 of the headline shape: T=500, U=100, V=5000, E=P=256, J=512 (2 GB of fp32 logits on the
-    host for the reference chain).  790 tiles over 148 CTAs: 5-6 tiles per CTA, last wave partial."""
+    host for the reference chain).  790 tiles over 148 CTAs: 5-6 tiles per CTA, last wave partial.
+
+    Two references.  (1) The reference chain with the vocabulary GEMM's operands rounded to bf16 (the
+    arithmetic precision='bf16' specifies; fp32 everywhere else): every gradient within 1e-2 - this is
+    the check of the kernels.  (2) The plain fp32 chain: loss within 1e-2, gradients within 2e-2.  At
+    this lattice size the bf16 rounding of the logits (1e-3 absolute per cell) accumulates along the 600
+    steps of a path into ~1 % errors of the cell occupancies alpha*beta/Z, which every gradient inherits
+    (measured 0.8-1.3e-2 relative L2; scripts/dbg_prec.py traces it) - a property of bf16 operands at
+    T+U = 600, shared by the reference under autocast, not of these kernels."""
     case = _case(2, 500, 100, 5000, 256, 512, seed=13, ragged=ragged)
-    # everything downstream of d e / d p (d enc_out, d pred_out, enc_ffn / pred_ffn gradients): measured
-    # 0.8-1.3e-2 relative L2 at this shape.  scripts/dbg_prec.py traces it:
-    # the kernels reproduce a torch emulation of the bf16 operand roundings to 2e-5 (d p) / 3e-4 (d e); at
-    # the e / p level the gradients sit 1.8e-3 / 2.5e-3 from fp32 (W_out's bf16 rounding, coherent over the
-    # 500 frames a d p entry sums), and the pred_ffn / enc_ffn backward GEMMs amplify that: the true
-    # gradient lies mostly in directions those projections attenuate, the rounding error does not.
-    _check(case, tol_inputs=2e-2)
+    loss, g = _mine_kw(case)
+    emu_loss, emu_g = _reference(*case, reduction="none", bf16_operands=True)
+    np.testing.assert_allclose(loss.numpy(), emu_loss.numpy(), rtol=1e-3)
+    for k in emu_g:
+        _close(k, g[k], emu_g[k], tol=1e-2)
+    del emu_g
+    ref_loss, ref_g = _reference(*case, reduction="none")
+    np.testing.assert_allclose(loss.numpy(), ref_loss.numpy(), rtol=1e-2)
+    for k in ref_g:
+        _close(k, g[k], ref_g[k], tol=2e-2)
+    _, _, _, _, tl, ul = case
+    for b in range(len(tl)):
+        assert torch.count_nonzero(g["enc"][b, tl[b]:]) == 0
+        assert torch.count_nonzero(g["pred"][b, ul[b] + 1:]) == 0
 
 
 def test_cfg2_slice():
