@@ -80,6 +80,13 @@ __device__ __forceinline__ void tma_load_4d_pair(uint32_t dst, const CUtensorMap
       "l"(m), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "l"(policy)
       : "memory");
 }
+// volatile: keeps the H loads where the epilogue's software pipeline places them (ptxas otherwise hoists all
+// 256 of a tile above the accumulator wait and spills)
+__device__ __forceinline__ uint32_t ldg_u32_pinned(const void* p) {
+  uint32_t v;
+  asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
 __device__ __forceinline__ void red_add(float* p, float v) {
   asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
 }
@@ -100,7 +107,12 @@ __device__ __forceinline__ Tile decode(const Params& P, int u, int tb) {
 
 // PLAIN: the same product for a plain row-major G [rows, ldg] (2-D TMA map, tiles of 256 consecutive rows),
 // epilogue out[row, j] = (G W)[row, j] - the d hs GEMM of the CTC projection (autograd of ctc.py:57)
-template <int UB, bool PLAIN>
+// SPLIT: fp32-accurate mode (three passes over split operands, H = H_hi + H_lo read inside the epilogue).
+// !SPLIT: the tile's 256 H values of a thread are loaded into registers (packed pairs) BEFORE the wait for
+// the accumulator, i.e. under the tile's own MMA main loop: the epilogue that the tensor pipe has to wait
+// for (one accumulator set fills all of TMEM, so there is no second buffer to compute into) is then pure
+// register work - tcgen05.ld one chunk ahead, 5 instructions per cell, no memory latency on the chain.
+template <int UB, bool PLAIN, bool SPLIT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     joint_dh_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_constant__ CUtensorMap gmap,
                     const __grid_constant__ CUtensorMap wmap_lo, const __grid_constant__ CUtensorMap gmap_lo,
@@ -262,6 +274,76 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         if (lane == 0) mbar_arrive_cluster(map_to_cta(acc_empty, 0));
         continue;
       }
+      if constexpr (!SPLIT) {
+        // column c = 128 * half + UB * f + i: frame f of CTA half `half`, label i of the tile (the order the
+        // 4-D TMA box lays the G rows out); chunk ch = columns 16 ch .. 16 ch + 15.  Frames / labels beyond
+        // T / U1 have a zero accumulator: their H index is clamped, the value is irrelevant.
+        // The H values of chunks 0 .. kAhead-1 are loaded BEFORE the accumulator wait (under the tile's MMA
+        // main loop), those of chunk ch + kAhead while chunk ch is processed (168 registers per thread at
+        // 10 warps: all 256 values at once would spill)
+        // Lanes 2m / 2m+1 (j, j+1) share their loads: each fetches the 32-bit word {H[.., j], H[.., j+1]} of ONE
+        // cell of a column pair (even lane: the even column, odd lane: the odd one) and the pair is
+        // recombined by one shuffle + one byte permute at consumption - 128 loads and 128 registers per
+        // thread and tile instead of 256, and no pack instruction waiting on a load
+        constexpr int kAhead = 8;
+        const int par = lane & 1;
+        const uint16_t* Hj = reinterpret_cast<const uint16_t*>(P.H) + (j & ~1);
+        const uint32_t psel = par ? 0x3276u : 0x5410u;
+        auto load_chunk = [&](int ch, uint32_t* dst) {
+#pragma unroll
+          for (int k = 0; k < 16; k += 2) {
+            const int c = ch * 16 + k, row = c & 127;
+            const int t = min(tl.t0 + (c >> 7) * TBH + row / UB, P.T - 1);
+            const uint32_t cell = (uint32_t)((tl.b * P.T + t) * P.U1 + min(u0 + row % UB + par, P.U1 - 1));
+            dst[k >> 1] = ldg_u32_pinned(Hj + cell * (uint32_t)P.ldh);  // < 2^31 elements (host check)
+          }
+        };
+        uint32_t hreg[16][8];
+#pragma unroll
+        for (int ch = 0; ch < kAhead; ++ch) load_chunk(ch, hreg[ch]);
+        float dp_acc[UB];
+#pragma unroll
+        for (int i = 0; i < UB; ++i) dp_acc[i] = 0.f;
+        float de_run = 0.f;
+        ptx::mbar_wait(acc_full, (uint32_t)(nu & 1));
+        ++nu;
+        ptx::tc_fence_after();
+        uint32_t r[2][16];
+        uint32_t hpair = 0;
+        ptx::tmem_ld16(taddr, r[0]);
+#pragma unroll
+        for (int ch = 0; ch < 16; ++ch) {
+          if (ch + kAhead < 16) load_chunk(ch + kAhead, hreg[ch + kAhead]);
+          ptx::tmem_ld_wait();
+          if (ch + 1 < 16) ptx::tmem_ld16(taddr + (ch + 1) * 16, r[(ch + 1) & 1]);
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            const int c = ch * 16 + k;
+            uint32_t hp = 0;
+            if ((k & 1) == 0) {
+              const uint32_t x = hreg[ch][k >> 1];
+              hpair = __byte_perm(x, __shfl_xor_sync(0xffffffffu, x, 1), psel);
+            }
+            hp = hpair;
+            const float hv = __uint_as_float((k & 1) ? (hp & 0xffff0000u) : (hp << 16));
+            const float z = __uint_as_float(r[ch & 1][k]) * fmaf(-hv, hv, 1.f);
+            dp_acc[c % UB] += z;
+            de_run += z;
+            if (c % UB == UB - 1) {  // last label of a frame: flush d e
+              const int t = tl.t0 + (c >> 7) * TBH + (c & 127) / UB;
+              if (t < P.T) red_add(P.de + (long long)(tl.b * P.T + t) * J + j, de_run);
+              de_run = 0.f;
+            }
+          }
+        }
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(map_to_cta(acc_empty, 0));
+#pragma unroll
+        for (int i = 0; i < UB; ++i)
+          if (u0 + i < P.U1) red_add(P.dp + (long long)(tl.b * P.U1 + u0 + i) * J + j, dp_acc[i]);
+        continue;
+      }
       // chunk ch = columns 16ch .. 16ch+15 = rows (ch & 7) * 16 + k of CTA half ch >> 3; row r of a half is
       // frame r / UB, label r % UB of the tile (the order the 4-D TMA box lays the G rows out).  Frames /
       // labels beyond T / U1 have a zero accumulator: their H index is clamped, the value is irrelevant
@@ -372,7 +454,7 @@ int encode(CUtensorMap* map, const void* ptr, int rank, const cuuint64_t* dims, 
   return B200_OK;
 }
 
-template <int UB, bool PLAIN>
+template <int UB, bool PLAIN, bool SPLIT>
 int launch_dh(const CUtensorMap& wmap, const CUtensorMap& wmap_lo, const void* G, const void* G_lo, int ldg,
               dh::Params P, int ctas, cudaStream_t st) {
   constexpr int TBH = 128 / UB;
@@ -404,11 +486,11 @@ int launch_dh(const CUtensorMap& wmap, const CUtensorMap& wmap_lo, const void* G
     units = (long long)P.nb * P.ntb * P.nub;
   }
   const int smem = dh::kStages * dh::stage_bytes(P.J) + 1024;
-  B200_CHECK_CUDA(cudaFuncSetAttribute(dh::joint_dh_kernel<UB, PLAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  B200_CHECK_CUDA(cudaFuncSetAttribute(dh::joint_dh_kernel<UB, PLAIN, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dh::kStages * dh::stage_bytes(dh::kMaxJ) + 1024));
   int grid = ctas;
   if (units < grid / 2) grid = 2 * (int)units;
-  dh::joint_dh_kernel<UB, PLAIN><<<grid, dh::kThreads, smem, st>>>(wmap, gmap, wmap_lo, gmap_lo, P);
+  dh::joint_dh_kernel<UB, PLAIN, SPLIT><<<grid, dh::kThreads, smem, st>>>(wmap, gmap, wmap_lo, gmap_lo, P);
   B200_CHECK_LAUNCH("joint_dh_kernel");
   return B200_OK;
 }
@@ -441,7 +523,8 @@ int joint_dh_impl(const void* G, const void* G_lo, int ldg, const void* w, const
   B200_CHECK_ARG(J == 256 || J == 512, "b200_joint_dh: join dim J=%d must be 256 or 512", J);
   B200_CHECK_ARG(ldg >= V && ldg % 8 == 0 && ((uintptr_t)G & 15) == 0 && ((uintptr_t)G_lo & 15) == 0,
                  "b200_joint_dh: ldg=%d must be >= V and a multiple of 8, G 16-byte aligned", ldg);
-  B200_CHECK_ARG(ldh >= J && ((uintptr_t)H & 1) == 0, "b200_joint_dh: ldh=%d must be >= J", ldh);
+  B200_CHECK_ARG(ldh >= J && ldh % 2 == 0 && ((uintptr_t)H & 3) == 0 && ((uintptr_t)H_lo & 1) == 0,
+                 "b200_joint_dh: ldh=%d must be >= J and even, H 4-byte aligned", ldh);
   B200_CHECK_ARG(((uintptr_t)w & 15) == 0 && ((uintptr_t)w_lo & 15) == 0,
                  "b200_joint_dh: W must be 16-byte aligned");
   B200_CHECK_ARG((long long)nb * T * U1 * ldh < (1ll << 31),
@@ -485,12 +568,19 @@ int joint_dh_impl(const void* G, const void* G_lo, int ldg, const void* w, const
     }
   }
   cudaStream_t st = (cudaStream_t)stream;
+  if (G_lo) switch (best) {
+      case 2: return launch_dh<2, false, true>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+      case 4: return launch_dh<4, false, true>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+      case 8: return launch_dh<8, false, true>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+      case 16: return launch_dh<16, false, true>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+      default: return launch_dh<32, false, true>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+    }
   switch (best) {
-    case 2: return launch_dh<2, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
-    case 4: return launch_dh<4, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
-    case 8: return launch_dh<8, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
-    case 16: return launch_dh<16, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
-    default: return launch_dh<32, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+    case 2: return launch_dh<2, false, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+    case 4: return launch_dh<4, false, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+    case 8: return launch_dh<8, false, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+    case 16: return launch_dh<16, false, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
+    default: return launch_dh<32, false, false>(wmap, wmap_lo, G, G_lo, ldg, P, ctas, st);
   }
 }
 
@@ -535,5 +625,5 @@ extern "C" int b200_split_gemm_nn(const void* G_hi, const void* G_lo, int ldg, c
   P.npass = G_lo ? 3 : 1;
   P.rows = rows;
   P.out = out;
-  return launch_dh<16, true>(wmap, wmap_lo, G_hi, G_lo, ldg, P, dh_ctas(max_ctas), (cudaStream_t)stream);
+  return launch_dh<16, true, true>(wmap, wmap_lo, G_hi, G_lo, ldg, P, dh_ctas(max_ctas), (cudaStream_t)stream);
 }
