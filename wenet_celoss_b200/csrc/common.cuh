@@ -81,6 +81,38 @@ __device__ __forceinline__ float warp_sum(float v) {
 
 constexpr int kLag = 4;  // lattice steps between rescalings (power of two)
 
+// ---- log2-domain helpers of the trellis / lattice chains (ctc_loss.cu, rnnt_loss.cu) ----
+// log2(2^a + 2^b); -inf arguments allowed, both -inf -> -inf.  Maximum factored out: 1 ex2 + 1 lg2
+__device__ __forceinline__ float lae2_log2(float a, float b) {
+  const float m = fmaxf(a, b), mn = fminf(a, b);
+  const float ms = (m == -INFINITY) ? 0.f : m;
+  return m + lg2_approx(1.f + ex2_approx(mn - ms));
+}
+// log2(2^a + 2^b + 2^c): 2 ex2 + 1 lg2
+__device__ __forceinline__ float lae3_log2(float a, float b, float c) {
+  const float lo = fminf(a, b), hi = fmaxf(a, b);
+  const float m = fmaxf(hi, c);
+  const float mid = fmaxf(lo, fminf(hi, c));
+  const float mn = fminf(lo, c);
+  const float ms = (m == -INFINITY) ? 0.f : m;
+  return m + lg2_approx(1.f + ex2_approx(mid - ms) + ex2_approx(mn - ms));
+}
+// warp maximum of floats (no NaNs) through the integer redux unit: one instruction instead of 5 shuffles
+__device__ __forceinline__ float warp_max_redux(float v) {
+  int k = __float_as_int(v);
+  k = k >= 0 ? k : k ^ 0x7fffffff;
+  k = __reduce_max_sync(0xffffffffu, k);
+  k = k >= 0 ? k : k ^ 0x7fffffff;
+  return __int_as_float(k);
+}
+
+// maximum over the warps' slots of one parity of red = [2][32]; all -inf -> 0 (nothing to subtract)
+__device__ __forceinline__ float block_max_read(const float* red, int parity, int nw) {
+  float m = red[parity * 32];
+  for (int i = 1; i < nw; ++i) m = fmaxf(m, red[parity * 32 + i]);
+  return m == -INFINITY ? 0.f : m;
+}
+
 // Lagged block maximum for the rescaled lattices: at step i every warp publishes the max
 // of the values it just produced (before the step's __syncthreads); at step i+1 all
 // threads read the other parity slot.  No extra barrier.  red = [2][32] floats.

@@ -78,14 +78,191 @@ ctc_logprobs_kernel(const T* __restrict__ logits, const long long* __restrict__ 
 
 // ---------------------------------------------------------------------------
 // pass 2: trellis.  grid (B,2): y==0 alpha (+ leader table, nll), y==1 beta.
-// One thread per extended state; previous frame in shared memory (ping-pong).
+//
+// The frame step is the serial chain of the whole CTC loss (T dependent frames), so nothing but the
+// recurrence itself sits on it - no block barrier, no shared-memory round trip:
+//   * a lane owns TWO adjacent extended states (alpha: 2g, 2g+1; beta: 2g-1, 2g), kept in registers.
+//     With that pairing both updates need exactly ONE value from the neighbouring lane (its odd state):
+//     one __shfl per frame; the skip transition of the odd state reads that same value;
+//   * values live in log2 units (ex2.approx / lg2.approx directly); log-add with the maximum factored
+//     out: 5 MUFU per lane and frame;
+//   * 64 states per warp, ceil((S+1)/64) warps per direction.  Warps are NOT synchronised per frame: the
+//     one value that crosses a warp boundary travels through a 32-slot shared-memory ring of
+//     {value, frame} words (one 8-byte volatile store / load), so a warp simply runs a frame or two
+//     behind its upstream neighbour (a software pipeline over the state axis);
+//   * rescaling (alpha / beta are stored relative to a running fp64 offset per frame, so that the stored
+//     fp32 numbers stay O(10)): every 8 frames each warp publishes its maximum (one redux.sync); two
+//     blocks later all warps read all published maxima - by then present without waiting - and derive the
+//     SAME per-frame correction c from level + drift (deterministic arithmetic on identical inputs);
+//     c is folded into the emission term off the chain.  Waiting for the publications also bounds the
+//     lead of any warp to < 24 frames, which is what makes the 32-slot ring safe.
+// cfg5 (T = 1000, S <= 201): 330 us (one thread per state, block barrier + expf / logf per frame)
+// -> see profiles/README.md.
 // ---------------------------------------------------------------------------
-constexpr int kCtcPf = 4;
+constexpr int kCtcPf = 8;     // frames of lp_ext in registers ahead of the chain = frames per rescale block
+constexpr int kCtcRing = 32;  // slots of the warp-boundary ring
 
-__device__ __forceinline__ float lae3(float a, float b, float c) {
-  float m = fmaxf(a, fmaxf(b, c));
-  if (m == -INFINITY) return -INFINITY;
-  return m + logf(expf(a - m) + expf(b - m) + expf(c - m));
+__device__ __forceinline__ void st_tagged(unsigned long long* p, float v, int tag) {
+  const unsigned long long w = ((unsigned long long)(unsigned)tag << 32) | (unsigned)__float_as_int(v);
+  *reinterpret_cast<volatile unsigned long long*>(p) = w;
+}
+__device__ __forceinline__ bool ld_tagged(const unsigned long long* p, int tag, float* v) {
+  const unsigned long long w = *reinterpret_cast<const volatile unsigned long long*>(p);
+  *v = __int_as_float((int)(unsigned)w);
+  return (int)(w >> 32) == tag;
+}
+
+// One direction of the trellis for one warp.  DIR = +1: alpha (frames ascending, value from lane - 1);
+// DIR = -1: beta (frames descending, value from lane + 1).  Returns the final fp64 offset (log2 units);
+// va / vb leave holding the last frame's even / odd state (log2 units, relative to the offset).
+//
+// One warp per scheduler and a serial chain: every instruction of the frame body is paid at its full
+// issue latency (ncu on the first version of this kernel: 113 instructions per frame, 4.8 cycles per
+// instruction, 1.1 of them branch resolution).  Hence: states outside [0, S) carry an emission of -inf and
+// need no select; full blocks of 8 frames run without a bound check; the neighbour-warp test is hoisted
+// (HAS_UP); offsets are written per block by lanes 0..7; addresses are 32-bit row offsets.
+template <int DIR, bool HAS_UP>
+__device__ __forceinline__ double ctc_trellis(const float* __restrict__ lp, float* __restrict__ out,
+                                              double* __restrict__ offs, const int* lab,
+                                              unsigned long long* ring, unsigned long long* pub, int S,
+                                              int Smax, int Tb, int blank, float& va, float& vb) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const int g = threadIdx.x;
+  const int e = 2 * g, o = DIR > 0 ? 2 * g + 1 : 2 * g - 1;
+  const bool mine_e = e < S, mine_o = o >= 0 && o < S;
+  bool skip;
+  if (DIR > 0) skip = mine_o && o >= 3 && lab[o] != blank && lab[o] != lab[o - 2];
+  else skip = mine_o && o + 2 < S && lab[o + 2] != blank && lab[o + 2] != lab[o];
+  const bool has_down = warp + DIR >= 0 && warp + DIR < nw;
+  const int lane_in = DIR > 0 ? 0 : 31, lane_out = DIR > 0 ? 31 : 0;
+  const bool is_in = lane == lane_in, is_out = lane == lane_out && has_down;
+  const unsigned long long* ring_in = ring + (HAS_UP ? warp - DIR : 0) * kCtcRing;
+  unsigned long long* ring_out = ring + warp * kCtcRing;
+  const int step = DIR * Smax;                      // row offset from one processed frame to the next
+  const int row0 = (DIR > 0 ? 0 : Tb - 1) * Smax;   // row offset of processing index 0
+  const int last_row = (DIR > 0 ? Tb - 1 : 0) * Smax;
+  const float* lpe = lp + e;
+  const float* lpo = lp + o;
+  float* oute = out + e;
+  float* outo = out + o;
+  // ---- frame 0
+  {
+    const bool se = DIR > 0 ? e == 0 : e == S - 1;
+    const bool so = DIR > 0 ? o == 1 : o == S - 2;
+    va = (mine_e && se) ? lpe[row0] * kLog2e : -INFINITY;
+    vb = (mine_o && so) ? lpo[row0] * kLog2e : -INFINITY;
+    if (mine_e) oute[row0] = va * kLn2;
+    if (mine_o) outo[row0] = vb * kLn2;
+    const float wm = warp_max_redux(fmaxf(va, vb));
+    if (lane == 0) st_tagged(pub + warp * 4, wm, 0);
+    if (is_out) st_tagged(ring_out, vb, 0);
+    if (g == 0) offs[DIR > 0 ? 0 : Tb - 1] = 0.0;
+  }
+  // emissions of the next block, natural log; states outside [0, S): -inf (they then stay -inf by themselves)
+  float xe[kCtcPf], xo[kCtcPf];
+  auto load_block = [&](int i0, float* de, float* dn) {
+#pragma unroll
+    for (int k = 0; k < kCtcPf; ++k) {
+      const int r = (i0 + k < Tb) ? row0 + (i0 + k) * step : last_row;
+      de[k] = mine_e ? lpe[r] : -INFINITY;
+      dn[k] = mine_o ? lpo[r] : -INFINITY;
+    }
+  };
+  load_block(1, xe, xo);
+  // rescale controller state (identical in every warp): O = offset so far, (x_last, i_last) = the last
+  // published maximum in absolute log2 units and the frame it was measured at
+  double O = 0.0, O_pub[4] = {0.0, 0.0, 0.0, 0.0};
+  int i_pub[4] = {0, 0, 0, 0};
+  double x_last = 0.0, vel = 0.0;
+  int i_last = -1, p_last = -1;
+  int blk = 0;
+  for (int i0 = 1; i0 < Tb; i0 += kCtcPf, ++blk) {
+    float nxe[kCtcPf], nxo[kCtcPf];
+    load_block(i0 + kCtcPf, nxe, nxo);
+    // ---- per-frame correction of this block from the maxima published two blocks ago
+    const int pn = blk > 0 ? blk - 1 : 0;
+    float M;
+    for (;;) {
+      float v = -INFINITY;
+      bool ok = true;
+      if (lane < nw) ok = ld_tagged(pub + lane * 4 + (pn & 3), pn, &v);
+      if (__all_sync(0xffffffffu, ok)) {
+        M = warp_max_redux(lane < nw ? v : -INFINITY);
+        break;
+      }
+    }
+    if (pn != p_last) {
+      const double x_a = (M == -INFINITY) ? O_pub[pn & 3] : (double)M + O_pub[pn & 3];
+      const int i_a = i_pub[pn & 3];
+      if (p_last >= 0 && i_a > i_last) vel = (x_a - x_last) / (double)(i_a - i_last);
+      if (p_last < 0) vel = x_a;  // first guess of the drift per frame: what frame 0 itself contributed
+      x_last = x_a;
+      i_last = i_a;
+      p_last = pn;
+    }
+    const int i_end = i0 + kCtcPf - 1;
+    const float c = (float)((x_last + vel * (double)(i_end - i_last) - O) * (1.0 / kCtcPf));
+    // offsets of this block's frames (k + 1 corrections of c after O): lanes 0..7 of warp 0
+    if (warp == 0 && lane < kCtcPf && i0 + lane < Tb)
+      offs[DIR > 0 ? i0 + lane : Tb - 1 - i0 - lane] = (O + (double)c * (double)(lane + 1)) * 0.6931471805599453094;
+    float pe[kCtcPf], po[kCtcPf];  // emissions in log2 units minus the correction
+#pragma unroll
+    for (int k = 0; k < kCtcPf; ++k) {
+      pe[k] = fmaf(xe[k], kLog2e, -c);
+      po[k] = fmaf(xo[k], kLog2e, -c);
+    }
+    const int rowb = row0 + i0 * step;
+    auto frame_step = [&](int k) {
+      const int i = i0 + k;
+      // the one value from the neighbouring lane / warp: the odd state of frame i - 1
+      float pO = DIR > 0 ? __shfl_up_sync(0xffffffffu, vb, 1) : __shfl_down_sync(0xffffffffu, vb, 1);
+      if (HAS_UP) {
+        float bv;
+        while (!ld_tagged(ring_in + ((i - 1) & (kCtcRing - 1)), i - 1, &bv)) {
+        }
+        pO = is_in ? bv : pO;
+      } else {
+        pO = is_in ? -INFINITY : pO;
+      }
+      const float na = lae2_log2(va, pO) + pe[k];
+      const float nb = lae3_log2(vb, va, skip ? pO : -INFINITY) + po[k];
+      va = na;
+      vb = nb;
+      if (is_out) st_tagged(ring_out + (i & (kCtcRing - 1)), vb, i);
+      if (mine_e) oute[rowb + k * step] = va * kLn2;
+      if (mine_o) outo[rowb + k * step] = vb * kLn2;
+    };
+    auto publish = [&]() {  // publication blk + 1: after this block's first frame
+      const float wm = warp_max_redux(fmaxf(va, vb));
+      if (lane == 0) st_tagged(pub + warp * 4 + ((blk + 1) & 3), wm, blk + 1);
+      O_pub[(blk + 1) & 3] = O + (double)c;
+      i_pub[(blk + 1) & 3] = i0;
+    };
+    if (i0 + kCtcPf <= Tb) {  // full block: no bound checks
+      frame_step(0);
+      publish();
+#pragma unroll
+      for (int k = 1; k < kCtcPf; ++k) frame_step(k);
+      O += (double)c * (double)kCtcPf;
+    } else {
+      frame_step(0);
+      publish();
+      int n = 1;
+#pragma unroll
+      for (int k = 1; k < kCtcPf; ++k)
+        if (i0 + k < Tb) {  // warp-uniform
+          frame_step(k);
+          ++n;
+        }
+      O += (double)c * (double)n;
+    }
+#pragma unroll
+    for (int k = 0; k < kCtcPf; ++k) {
+      xe[k] = nxe[k];
+      xo[k] = nxo[k];
+    }
+  }
+  return O;
 }
 
 __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
@@ -95,37 +272,33 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
                                    float* __restrict__ alpha, float* __restrict__ beta,
                                    float* __restrict__ nll, int32_t* __restrict__ leader,
                                    double* __restrict__ frame_off) {
-  extern __shared__ float sm[];  // [2][Smax+4] floats, [2][32] lagged-max scratch, then [Smax] ints
+  extern __shared__ unsigned long long sm64[];  // ring [nw][32] | pub [nw][4] | lab [Smax] | fin [2]
   const int b = blockIdx.x;
-  const int s = threadIdx.x;
+  const int tid = threadIdx.x, nw = blockDim.x >> 5;
   const int Smax = 2 * Lmax + 1;
   const int Tb = hlens[b], L = ys_lens[b];
   const int S = 2 * L + 1;
-  const int stride = Smax + 4;
-  float* buf0 = sm + 2;  // indices -2 .. Smax+1 addressable
-  float* buf1 = sm + stride + 2;
-  float* red = sm + 2 * stride;
-  int* lab = reinterpret_cast<int*>(sm + 2 * stride + 64);
+  unsigned long long* ring = sm64;
+  unsigned long long* pub = sm64 + nw * kCtcRing;
+  int* lab = reinterpret_cast<int*>(pub + nw * 4);
+  float* fin = reinterpret_cast<float*>(lab + Smax + 1);
   double* offs = frame_off + ((long long)b * 2 + blockIdx.y) * (Tm + 1);
-  double run = 0.0;  // running offset: alpha_t(s) = alpha_hat_t(s) + off_a[t] (same for beta)
   const long long* ys = ys_pad + (long long)b * Lmax;
-  for (int i = s; i < 2 * stride; i += blockDim.x) sm[i] = -INFINITY;
-  for (int i = s; i < Smax; i += blockDim.x) lab[i] = (i < S) ? ext_label(ys, i, blank) : -1;
+  for (int i = tid; i < nw * (kCtcRing + 4); i += blockDim.x) sm64[i] = 0xffffffff00000000ull;  // tag -1
+  for (int i = tid; i < Smax; i += blockDim.x) lab[i] = (i < S) ? ext_label(ys, i, blank) : -1;
   __syncthreads();
-  const bool mine = s < S;
-  const int my = mine ? lab[s] : -1;
   const long long off = (long long)b * Tm * Smax;
   const float* lp = lp_ext + off;
 
   if (blockIdx.y == 0) {
     // leader[s] = smallest state index with the same label (blank states -> 0)
-    if (mine) {
+    for (int s = tid; s < S; s += blockDim.x) {
       int ld = s;
       if ((s & 1) == 0) {
         ld = 0;
       } else {
         for (int j = 1; j < s; j += 2)
-          if (lab[j] == my) {
+          if (lab[j] == lab[s]) {
             ld = j;
             break;
           }
@@ -133,132 +306,31 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
       leader[(long long)b * Smax + s] = ld;
     }
     if (Tb <= 0) {
-      if (s == 0) {
+      if (tid == 0) {
         nll[b] = (L == 0) ? 0.f : INFINITY;
         offs[Tm] = (L == 0) ? 0.0 : (double)-INFINITY;
       }
       return;
     }
-    float* al = alpha + off;
-    const bool skip_ok = mine && s >= 2 && my != blank && my != lab[s - 2];
-    float* prev = buf0;
-    float* cur = buf1;
-    {
-      float v = (mine && s <= 1) ? lp[s] : -INFINITY;
-      if (mine) {
-        prev[s] = v;
-        al[s] = v;
-      }
-      lagged_max_write(v, red, 0);
-    }
-    int it = kLag;
-    if (s == 0) offs[0] = 0.0;
+    float va, vb;
+    const double O = (tid >> 5) > 0
+                         ? ctc_trellis<1, true>(lp, alpha + off, offs, lab, ring, pub, S, Smax, Tb, blank, va, vb)
+                         : ctc_trellis<1, false>(lp, alpha + off, offs, lab, ring, pub, S, Smax, Tb, blank, va, vb);
+    // final frame: states S-1 (even, lane L) and S-2 (odd, lane L-1)
+    if (2 * tid == S - 1) fin[0] = va;
+    if (2 * tid + 1 == S - 2) fin[1] = vb;
+    if (S == 1 && tid == 0) fin[1] = -INFINITY;
     __syncthreads();
-    float r[kCtcPf];
-#pragma unroll
-    for (int k = 0; k < kCtcPf; ++k) r[k] = (mine && 1 + k < Tb) ? lp[(long long)(1 + k) * Smax + s] : 0.f;
-    for (int t0 = 1; t0 < Tb; t0 += kCtcPf) {
-      float nr[kCtcPf];
-#pragma unroll
-      for (int k = 0; k < kCtcPf; ++k) {
-        int t = t0 + kCtcPf + k;
-        nr[k] = (mine && t < Tb) ? lp[(long long)t * Smax + s] : 0.f;
-      }
-#pragma unroll
-      for (int k = 0; k < kCtcPf; ++k) {
-        int t = t0 + k;
-        if (t < Tb) {  // block-uniform
-          float v = -INFINITY;
-          if (mine) v = lae3(prev[s], prev[s - 1], skip_ok ? prev[s - 2] : -INFINITY) + r[k];
-          {  // pull the previous frame's maximum into the fp64 offset (no extra barrier)
-            // every kLag-th step: subtract the maximum published kLag steps ago
-            if ((it & (kLag - 1)) == 0) {
-              const float M = lagged_max_read(red, ((it / kLag) - 1) & 1);
-              v -= M;
-              run += (double)M;
-              lagged_max_write(v, red, (it / kLag) & 1);
-            }
-            ++it;
-          }
-          if (mine) {
-            cur[s] = v;
-            al[(long long)t * Smax + s] = v;
-          }
-          if (s == 0) offs[t] = run;
-          __syncthreads();
-          float* tmp = prev;
-          prev = cur;
-          cur = tmp;
-        }
-      }
-#pragma unroll
-      for (int k = 0; k < kCtcPf; ++k) r[k] = nr[k];
-    }
-    if (s == 0) {
-      double ll = (double)log_add_exp(prev[S - 1], S > 1 ? prev[S - 2] : -INFINITY) + run;
+    if (tid == 0) {
+      const double ll = ((double)lae2_log2(fin[0], fin[1]) + O) * 0.6931471805599453094;
       nll[b] = (float)(-ll);
       offs[Tm] = ll;  // [b][0][T] = log-likelihood in fp64
     }
   } else {
     if (Tb <= 0) return;
-    float* be = beta + off;
-    const bool skip_ok = mine && s + 2 < S && lab[s + 2] != blank && lab[s + 2] != my;
-    float* prev = buf0;
-    float* cur = buf1;
-    {
-      float v = (mine && s >= S - 2) ? lp[(long long)(Tb - 1) * Smax + s] : -INFINITY;
-      if (mine) {
-        prev[s] = v;
-        be[(long long)(Tb - 1) * Smax + s] = v;
-      }
-      lagged_max_write(v, red, 0);
-    }
-    int it = kLag;
-    if (s == 0) offs[Tb - 1] = 0.0;
-    __syncthreads();
-    float r[kCtcPf];
-#pragma unroll
-    for (int k = 0; k < kCtcPf; ++k) {
-      int t = Tb - 2 - k;
-      r[k] = (mine && t >= 0) ? lp[(long long)t * Smax + s] : 0.f;
-    }
-    for (int t0 = Tb - 2; t0 >= 0; t0 -= kCtcPf) {
-      float nr[kCtcPf];
-#pragma unroll
-      for (int k = 0; k < kCtcPf; ++k) {
-        int t = t0 - kCtcPf - k;
-        nr[k] = (mine && t >= 0) ? lp[(long long)t * Smax + s] : 0.f;
-      }
-#pragma unroll
-      for (int k = 0; k < kCtcPf; ++k) {
-        int t = t0 - k;
-        if (t >= 0) {  // block-uniform
-          float v = -INFINITY;
-          if (mine) v = lae3(prev[s], prev[s + 1], skip_ok ? prev[s + 2] : -INFINITY) + r[k];
-          {
-            // every kLag-th step: subtract the maximum published kLag steps ago
-            if ((it & (kLag - 1)) == 0) {
-              const float M = lagged_max_read(red, ((it / kLag) - 1) & 1);
-              v -= M;
-              run += (double)M;
-              lagged_max_write(v, red, (it / kLag) & 1);
-            }
-            ++it;
-          }
-          if (mine) {
-            cur[s] = v;
-            be[(long long)t * Smax + s] = v;
-          }
-          if (s == 0) offs[t] = run;
-          __syncthreads();
-          float* tmp = prev;
-          prev = cur;
-          cur = tmp;
-        }
-      }
-#pragma unroll
-      for (int k = 0; k < kCtcPf; ++k) r[k] = nr[k];
-    }
+    float va, vb;
+    if ((tid >> 5) + 1 < nw) ctc_trellis<-1, true>(lp, beta + off, offs, lab, ring, pub, S, Smax, Tb, blank, va, vb);
+    else ctc_trellis<-1, false>(lp, beta + off, offs, lab, ring, pub, S, Smax, Tb, blank, va, vb);
   }
 }
 
@@ -430,9 +502,9 @@ extern "C" int b200_ctc_lattice(const float* lp_ext, const int64_t* ys_pad, cons
                      (Lmax == 0 || ys_pad),
                  "b200_ctc_lattice: null pointer");
   const int Smax = 2 * Lmax + 1;
-  const int threads = ((Smax + 31) / 32) * 32;
-  const size_t smem = (2 * (size_t)(Smax + 4) + 64) * sizeof(float) + (size_t)Smax * sizeof(int);
-  ctc_lattice_kernel<<<dim3(B, 2), threads, smem, (cudaStream_t)stream>>>(
+  const int nw = (Smax + 1 + 63) / 64;  // 64 states per warp (two per lane); beta's pairing starts at state -1
+  const size_t smem = (size_t)nw * (kCtcRing + 4) * 8 + ((size_t)Smax + 1) * sizeof(int) + 2 * sizeof(float);
+  ctc_lattice_kernel<<<dim3(B, 2), nw * 32, smem, (cudaStream_t)stream>>>(
       lp_ext, reinterpret_cast<const long long*>(ys_pad), hlens, ys_lens, T, Lmax, blank, alpha,
       beta, nll, leader, frame_off);
   B200_CHECK_LAUNCH("ctc_lattice_kernel");

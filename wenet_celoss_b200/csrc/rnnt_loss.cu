@@ -55,17 +55,20 @@ rnnt_logprobs_kernel(const T* __restrict__ logits, const int32_t* __restrict__ t
 // pass 2: anti-diagonal wavefront.  grid (B, 2): y==0 alpha, y==1 beta.
 // One thread per u; the previous diagonal lives in shared memory (ping-pong),
 // one __syncthreads per diagonal; log-prob loads run kPf diagonals ahead.
+// The diagonal step is the serial chain of the loss (T + U dependent steps): values are kept in log2
+// units so that the step is LDS -> 2 FADD -> FMNMX x2 -> ex2 -> lg2 -> STS -> barrier (2 MUFU, no
+// expf / logf range code on the chain); alpha / beta leave in natural-log units.
 //
 // Rescaling: every path crosses each anti-diagonal exactly once, so a per-diagonal
-// offset can be pulled out of alpha and beta without changing any posterior.  On every
-// diagonal the block subtracts the previous diagonal's maximum (published through shared
-// memory one step earlier, so no extra barrier) and adds it to a running fp64 offset:  alpha(t,u) = alpha_hat(t,u) + off_a[t+u]  (same for beta).
+// offset can be pulled out of alpha and beta without changing any posterior.  Every kPf = 8
+// diagonals the block subtracts the maximum it published 8 diagonals earlier (one redux.sync per
+// warp into shared memory, so no extra barrier) and adds it to a running fp64 offset:  alpha(t,u) = alpha_hat(t,u) + off_a[t+u]  (same for beta).
 // The stored fp32 values stay O(10) in magnitude, which removes the cost-sized
 // cancellation alpha+beta-cost that limits plain fp32 log-space to ~cost*2^-23.
 // diag_off layout: [B][2][T+U1] fp64; [b][0][d] alpha offsets, [b][1][d] beta offsets,
 // [b][0][T+U1-1] = log-likelihood of utterance b.
 // ---------------------------------------------------------------------------
-constexpr int kPf = 4;
+constexpr int kPf = 8;  // diagonals of log-probs in registers ahead of the chain == diagonals between rescalings
 
 __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
                                     const float* __restrict__ lp_emit,
@@ -100,7 +103,9 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
   }
   __syncthreads();
   const bool mine = (u <= Ub);
-  double run = 0.0;  // running offset, tracked identically by every thread
+  double run = 0.0;  // running offset (log2 units inside the loop), tracked identically by every thread
+  constexpr double kLn2d = 0.6931471805599453094;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = (blockDim.x + 31) >> 5;
 
   if (blockIdx.y == 0) {
     // ---------------- alpha: d ascending ----------------
@@ -110,48 +115,47 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
       al[0] = 0.f;
       offs[0] = 0.0;
     }
-    lagged_max_write(u == 0 ? 0.f : -INFINITY, red, 0);
-    int it = kLag;
+    {
+      const float wm = warp_max_redux(u == 0 ? 0.f : -INFINITY);
+      if (lane == 0) red[warp] = wm;
+    }
     __syncthreads();
     float* prev = buf0;
     float* cur = buf1;
     float rb[kPf], re[kPf];
-    auto fetch = [&](int d, float& vb, float& ve) {
+    auto fetch = [&](int d, float& vb, float& ve) {  // log2 units
       vb = -INFINITY;
       ve = -INFINITY;
       int t = d - u;
       if (mine && d < D && t >= 0 && t < Tb) {
-        if (t > 0) vb = lpb[(long long)(t - 1) * U1 + u];
-        if (u > 0) ve = lpe[(long long)t * U1 + u - 1];
+        if (t > 0) vb = lpb[(long long)(t - 1) * U1 + u] * kLog2e;
+        if (u > 0) ve = lpe[(long long)t * U1 + u - 1] * kLog2e;
       }
     };
 #pragma unroll
     for (int k = 0; k < kPf; ++k) fetch(1 + k, rb[k], re[k]);
-    for (int d0 = 1; d0 < D; d0 += kPf) {
+    int blk = 0;
+    for (int d0 = 1; d0 < D; d0 += kPf, ++blk) {
       float nb[kPf], ne[kPf];
 #pragma unroll
       for (int k = 0; k < kPf; ++k) fetch(d0 + kPf + k, nb[k], ne[k]);
+      const float M = block_max_read(red, blk & 1, nw);  // published one block (kPf diagonals) ago
 #pragma unroll
       for (int k = 0; k < kPf; ++k) {
         int d = d0 + k;
         if (d < D) {  // block-uniform
           int t = d - u;
           const bool live = mine && t >= 0 && t < Tb;
-          float v = -INFINITY;
-          if (live) v = log_add_exp(prev[u] + rb[k], prev[u - 1] + re[k]);
-          {
-            // every kLag-th step: subtract the maximum published kLag steps ago
-            if ((it & (kLag - 1)) == 0) {
-              const float M = lagged_max_read(red, ((it / kLag) - 1) & 1);
-              v -= M;
-              run += (double)M;
-              lagged_max_write(v, red, (it / kLag) & 1);
-            }
-            ++it;
+          float v = live ? lae2_log2(prev[u] + rb[k], prev[u - 1] + re[k]) : -INFINITY;
+          if (k == 0) {  // first diagonal of a block: subtract the maximum published kPf diagonals ago
+            v -= M;
+            run += (double)M;
+            const float wm = warp_max_redux(v);
+            if (lane == 0) red[((blk & 1) ^ 1) * 32 + warp] = wm;
           }
           if (mine) cur[u] = v;
-          if (live) al[(long long)t * U1 + u] = v;
-          if (u == 0) offs[d] = run;
+          if (live) al[(long long)t * U1 + u] = v * kLn2;
+          if (u == 0) offs[d] = run * kLn2d;
           __syncthreads();
           float* tmp = prev;
           prev = cur;
@@ -171,7 +175,7 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
     float* cur = buf1;
     if (u == Ub) {
       float v = lpb[(long long)(Tb - 1) * U1 + Ub];
-      buf0[Ub] = v;
+      buf0[Ub] = v * kLog2e;
       be[(long long)(Tb - 1) * U1 + Ub] = v;
       offs[D - 1] = 0.0;
       if (D == 1) {
@@ -179,53 +183,52 @@ __global__ void rnnt_lattice_kernel(const float* __restrict__ lp_blank,
         diag_off[(long long)b * 2 * nd + nd - 1] = (double)v;
       }
     }
-    lagged_max_write(u == Ub ? lpb[(long long)(Tb - 1) * U1 + Ub] : -INFINITY, red, 0);
-    int it = kLag;
+    {
+      const float wm = warp_max_redux(u == Ub ? lpb[(long long)(Tb - 1) * U1 + Ub] * kLog2e : -INFINITY);
+      if (lane == 0) red[warp] = wm;
+    }
     __syncthreads();
     float rb[kPf], re[kPf];
-    auto fetch = [&](int d, float& vb, float& ve) {
+    auto fetch = [&](int d, float& vb, float& ve) {  // log2 units
       vb = -INFINITY;
       ve = -INFINITY;
       int t = d - u;
       if (mine && d >= 0 && t >= 0 && t < Tb) {
-        if (t + 1 < Tb) vb = lpb[(long long)t * U1 + u];
-        if (u < Ub) ve = lpe[(long long)t * U1 + u];
+        if (t + 1 < Tb) vb = lpb[(long long)t * U1 + u] * kLog2e;
+        if (u < Ub) ve = lpe[(long long)t * U1 + u] * kLog2e;
       }
     };
 #pragma unroll
     for (int k = 0; k < kPf; ++k) fetch(D - 2 - k, rb[k], re[k]);
-    for (int d0 = D - 2; d0 >= 0; d0 -= kPf) {
+    int blk = 0;
+    for (int d0 = D - 2; d0 >= 0; d0 -= kPf, ++blk) {
       float nb[kPf], ne[kPf];
 #pragma unroll
       for (int k = 0; k < kPf; ++k) fetch(d0 - kPf - k, nb[k], ne[k]);
+      const float M = block_max_read(red, blk & 1, nw);
 #pragma unroll
       for (int k = 0; k < kPf; ++k) {
         int d = d0 - k;
         if (d >= 0) {  // block-uniform
           int t = d - u;
           const bool live = mine && t >= 0 && t < Tb;
-          float v = -INFINITY;
-          if (live) v = log_add_exp(prev[u] + rb[k], prev[u + 1] + re[k]);
-          {
-            // every kLag-th step: subtract the maximum published kLag steps ago
-            if ((it & (kLag - 1)) == 0) {
-              const float M = lagged_max_read(red, ((it / kLag) - 1) & 1);
-              v -= M;
-              run += (double)M;
-              lagged_max_write(v, red, (it / kLag) & 1);
-            }
-            ++it;
+          float v = live ? lae2_log2(prev[u] + rb[k], prev[u + 1] + re[k]) : -INFINITY;
+          if (k == 0) {
+            v -= M;
+            run += (double)M;
+            const float wm = warp_max_redux(v);
+            if (lane == 0) red[((blk & 1) ^ 1) * 32 + warp] = wm;
           }
           if (mine) cur[u] = v;
           if (live) {
-            be[(long long)t * U1 + u] = v;
+            be[(long long)t * U1 + u] = v * kLn2;
             if (d == 0) {
-              double ll = (double)v + run;
+              double ll = ((double)v + run) * kLn2d;
               costs[b] = (float)(-ll);
               diag_off[(long long)b * 2 * nd + nd - 1] = ll;
             }
           }
-          if (u == 0) offs[d] = run;
+          if (u == 0) offs[d] = run * kLn2d;
           __syncthreads();
           float* tmp = prev;
           prev = cur;
