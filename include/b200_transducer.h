@@ -164,6 +164,28 @@ int b200_joint_fwd_h(const float* e, const float* p, const void* w_bf16, const f
                      float* lse, float* lp_blank, float* lp_emit, const float* logit_bound,
                      void* H, int ldh, int max_ctas, b200_stream_t stream);
 
+/* training forward of the NO-RECOMPUTE backward: as b200_joint_fwd_h (H [B*T*U1, ldh] bf16 is written
+ * first, by a kernel of its own, and read back through TMA), and the epilogue also stores
+ * Pt [B*T*U1, ldg] bf16 = exp(logit) (ldg >= V, ldg % 16 == 0; columns >= V are written as zero).
+ * Requires the logit bound (b200_joint_logit_bound) and bound * log2(e) < 100; callers should stay
+ * below 60 so that rowscale * Pt keeps its relative precision.  The backward pass is then
+ * b200_rnnt_grad_coef -> b200_joint_rowscale -> b200_joint_dw_db + b200_joint_dh_scaled: the logits
+ * GEMM of joint.py:68-69 runs once, not twice. */
+int b200_joint_fwd_p(const float* e, const float* p, const void* w_bf16, const float* bias_pad,
+                     const int32_t* targets, const int32_t* logit_len, const int32_t* target_len,
+                     int B, int T, int U1, int V, int J, int blank,
+                     float* lse, float* lp_blank, float* lp_emit, const float* logit_bound,
+                     void* H, int ldh, void* Pt, int ldg, int max_ctas, b200_stream_t stream);
+
+/* d loss / d logits = rowscale[c] * Pt'[c, v]: writes rowscale [B*T*U1] fp32 (= scale * exp(c0) of the
+ * coefficients of b200_rnnt_grad_coef), overwrites the blank and target entries of every row of Pt with
+ * exp(x) - exp(x + cb - c0) / exp(x) - exp(x + ce - c0) (x from lse + lp_blank / lp_emit), and writes
+ * Hs [B*T*U1, ldh] bf16 = rowscale * H (the second operand of the weight-gradient GEMM). */
+int b200_joint_rowscale(const float* coef, const float* lse, const float* lp_blank,
+                        const float* lp_emit, const int32_t* targets, int B, int T, int U1, int V,
+                        int J, int blank, void* Pt, int ldg, const void* H, int ldh, void* Hs,
+                        float* rowscale, b200_stream_t stream);
+
 /* backward, one chunk of cells [cell0, cell0+ncells) (cell = (b*T+t)*U1+u): recompute the
  * logits tile and write G = d loss / d logits (bf16, [ncells, ldg], ldg % 16 == 0) from the
  * coefficients of b200_rnnt_grad_coef.  H [ncells, ldh] bf16 (ldh >= J, ldh % 8 == 0) is a
@@ -199,6 +221,19 @@ int b200_joint_dz_reduce(const float* dH, const void* H, int ldh, int nb, int T,
  * be a multiple of 128 in [128, 512]; dW must be zeroed before the first chunk. */
 int b200_joint_dw(const void* G, int ldg, const void* H, int ldh, long long n, int V, int J,
                   float* dW, int max_ctas, b200_stream_t stream);
+
+/* b200_joint_dw with the bias gradient: db [V] fp32 += sum over cells of rowscale[c] * G[c, v], computed
+ * by the kernel's otherwise idle epilogue warps from the G boxes already staged in shared memory
+ * (G = Pt' of b200_joint_rowscale, H = Hs).  db must be zeroed before the first call. */
+int b200_joint_dw_db(const void* G, int ldg, const void* H, int ldh, long long n, int V, int J,
+                     float* dW, const float* rowscale, float* db, int max_ctas, b200_stream_t stream);
+
+/* b200_joint_dh with a per-cell factor: dH = rowscale[c] * (G W_out)[c, :] (G = Pt' of
+ * b200_joint_rowscale; rowscale [nb*T*U1] fp32). */
+int b200_joint_dh_scaled(const void* G, int ldg, const void* w_bf16, const void* H, int ldh,
+                         const float* rowscale, int nb, int T, int U1, int V, int J,
+                         const int32_t* logit_len, const int32_t* target_len, float* de, float* dp,
+                         int max_ctas, b200_stream_t stream);
 
 /* hidden-side gradient of the fused joint for one chunk of nb whole utterances, in ONE kernel:
  * dH = G W_out (autograd of ffn_out, joint.py:68-69), dZ = dH * (1 - H^2) (tanh, joint.py:63-64),

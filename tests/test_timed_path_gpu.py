@@ -10,6 +10,10 @@ shapes of test_joint_gpu.py never make a CTA process a second tile.  Here:
   * the running-maximum epilogue (taken when max_v(|W_v|_1 + |b_v|) * log2(e) >= 100, or when no
     bound is supplied) is forced;
   * the multi-chunk backward loop is forced through a small SCRATCH_BYTES;
+  * BOTH backward variants run on every shape: the no-recompute path (the forward kernel keeps
+    exp(logit) in bf16; default when the scratch fits and the logit bound is small - what bench.py
+    times) and the recompute path (``_no_recompute=False``; also the fallback for large bounds and
+    chunked scratch);
   * greedy and beam-10 decode bench.py's own cfg4 model (V=5000, T=500) against the oracle.
 
 Tolerance: bf16 MMA operands -> north_star's bf16 bar, rtol 1e-2 (relative L2 and max-abs
@@ -44,17 +48,27 @@ def _mine_kw(case, reduction="none", **kw):
     return loss.detach().cpu(), grads
 
 
-def _check(case, tol_inputs=1e-2, **kw):
+def _check(case, tol_inputs=1e-2, expect_nr=True, **kw):
+    """Both backward variants against the fp32 reference chain (``expect_nr``: the default variant
+    must really have been the no-recompute one)."""
+    from wenet_celoss_b200 import joint as jmod
     ref_loss, ref_g = _reference(*case, reduction="none")
-    loss, g = _mine_kw(case, **kw)
-    np.testing.assert_allclose(loss.numpy(), ref_loss.numpy(), rtol=1e-2)
-    for k in ref_g:
-        _close(k, g[k], ref_g[k], tol=1e-2 if k.startswith("ffn_out") else tol_inputs)
-    _, _, _, _, tl, ul = case
-    for b in range(len(tl)):  # padded frames / labels receive exactly zero gradient
-        assert torch.count_nonzero(g["enc"][b, tl[b]:]) == 0
-        assert torch.count_nonzero(g["pred"][b, ul[b] + 1:]) == 0
-    return loss, g
+    out = None
+    for nr in (None, False):
+        loss, g = _mine_kw(case, _no_recompute=nr, **kw)
+        want_path = "no_recompute" if (nr is None and expect_nr) else "recompute"
+        assert jmod.LAST_BACKWARD_PATH == want_path, (nr, jmod.LAST_BACKWARD_PATH)
+        np.testing.assert_allclose(loss.numpy(), ref_loss.numpy(), rtol=1e-2)
+        for k in ref_g:
+            _close(k, g[k], ref_g[k], tol=1e-2 if k.startswith("ffn_out") else tol_inputs)
+        _, _, _, _, tl, ul = case
+        for b in range(len(tl)):  # padded frames / labels receive exactly zero gradient
+            assert torch.count_nonzero(g["enc"][b, tl[b]:]) == 0
+            assert torch.count_nonzero(g["pred"][b, ul[b] + 1:]) == 0
+        out = out or (loss, g)
+        if not expect_nr:
+            break
+    return out
 
 
 @pytest.mark.parametrize("max_ctas", [2, 4])
@@ -83,21 +97,27 @@ def test_cfg3_slice(ragged):
     steps of a path into ~1 % errors of the cell occupancies alpha*beta/Z, which every gradient inherits
     (measured 0.8-1.3e-2 relative L2; scripts/dbg_prec.py traces it) - a property of bf16 operands at
     T+U = 600, shared by the reference under autocast, not of these kernels."""
+    from wenet_celoss_b200 import joint as jmod
     case = _case(2, 500, 100, 5000, 256, 512, seed=13, ragged=ragged)
     loss, g = _mine_kw(case)
+    assert jmod.LAST_BACKWARD_PATH == "no_recompute"
+    loss_rc, g_rc = _mine_kw(case, _no_recompute=False)
+    assert jmod.LAST_BACKWARD_PATH == "recompute"
     emu_loss, emu_g = _reference(*case, reduction="none", bf16_operands=True)
-    np.testing.assert_allclose(loss.numpy(), emu_loss.numpy(), rtol=1e-3)
-    for k in emu_g:
-        _close(k, g[k], emu_g[k], tol=1e-2)
+    for l_, g_ in ((loss, g), (loss_rc, g_rc)):
+        np.testing.assert_allclose(l_.numpy(), emu_loss.numpy(), rtol=1e-3)
+        for k in emu_g:
+            _close(k, g_[k], emu_g[k], tol=1e-2)
     del emu_g
     ref_loss, ref_g = _reference(*case, reduction="none")
-    np.testing.assert_allclose(loss.numpy(), ref_loss.numpy(), rtol=1e-2)
-    for k in ref_g:
-        _close(k, g[k], ref_g[k], tol=2e-2)
     _, _, _, _, tl, ul = case
-    for b in range(len(tl)):
-        assert torch.count_nonzero(g["enc"][b, tl[b]:]) == 0
-        assert torch.count_nonzero(g["pred"][b, ul[b] + 1:]) == 0
+    for l_, g_ in ((loss, g), (loss_rc, g_rc)):
+        np.testing.assert_allclose(l_.numpy(), ref_loss.numpy(), rtol=1e-2)
+        for k in ref_g:
+            _close(k, g_[k], ref_g[k], tol=2e-2)
+        for b in range(len(tl)):
+            assert torch.count_nonzero(g_["enc"][b, tl[b]:]) == 0
+            assert torch.count_nonzero(g_["pred"][b, ul[b] + 1:]) == 0
 
 
 def test_cfg2_slice():
@@ -117,15 +137,15 @@ def test_running_max_epilogue_large_weights():
     w = joint.ffn_out.weight.to(DEV).to(torch.bfloat16).contiguous()
     bound = joint_logit_bound(w, _pad_bias(joint.ffn_out.bias.to(DEV), 700), 700)
     assert float(bound) * 1.4427 > 100.0, float(bound)
-    _check(case)
-    _check(case, _max_ctas=3)
+    _check(case, expect_nr=False)  # large bound: the recompute path is chosen by itself
+    _check(case, expect_nr=False, _max_ctas=3)
 
 
 def test_running_max_epilogue_no_bound():
     """use_bound=False: same inputs as the fast path, results must agree with it and the reference."""
     case = _case(3, 30, 10, 700, 64, 512, seed=16, ragged=True)
-    slow, gs = _check(case, _use_bound=False)
-    fast, gf = _mine_kw(case)
+    slow, gs = _check(case, expect_nr=False, _use_bound=False)
+    fast, gf = _mine_kw(case, _no_recompute=False)  # same backward kernels, bounded-logit forward epilogue
     np.testing.assert_allclose(slow.numpy(), fast.numpy(), rtol=1e-5)
     for k in gs:
         _close(k, gs[k], gf[k], tol=1e-3)
@@ -139,8 +159,8 @@ def test_multi_chunk_backward(monkeypatch):
     per_utt, ldg = 24 * 10, 704
     monkeypatch.setattr(jmod, "SCRATCH_BYTES", 2 * per_utt * ldg * 2 + 64)
     assert jmod._chunk_utts(5, per_utt, ldg, 148) <= 2
-    _check(case)
-    _check(case, _max_ctas=2)
+    _check(case, expect_nr=False)  # scratch too small for exp(logit) of the whole batch
+    _check(case, expect_nr=False, _max_ctas=2)
 
 
 # ----------------------------------------------------------------------------- cfg4 searches

@@ -50,6 +50,7 @@ struct Params {
   float* out;            // PLAIN: [rows, J] fp32 = G.W, written (no tanh', no sums)
   const int32_t* logit_len;   // optional [nb]: tiles beyond T_b / U_b are skipped (their G is zero)
   const int32_t* target_len;
+  const float* rowscale; // optional [nb*T*U1]: dH = rowscale[cell] * (G W) (no-recompute backward, joint_nr.cu)
   float* de;             // [nb, T, J]  accumulated (zero it first)
   float* dp;             // [nb, U1, J] accumulated
 };
@@ -122,6 +123,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * kStages + 2];
   __shared__ uint32_t tmem_holder;
+  __shared__ __align__(16) float rs_s[2][kTileN];  // per-cell factors of the tile (1 without P.rowscale)
 
   const uint32_t rank = cluster_ctarank();
   const int warp = threadIdx.x >> 5;
@@ -301,6 +303,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         uint32_t hreg[16][8];
 #pragma unroll
         for (int ch = 0; ch < kAhead; ++ch) load_chunk(ch, hreg[ch]);
+        // per-cell factors of the tile's 256 columns -> shared memory (double-buffered over tiles: the
+        // barrier of the next tile orders this tile's reads before the buffer's reuse)
+        float* const rs_t = rs_s[nu & 1];
+        for (int c = (warp - kEpiWarp0) * 32 + lane; c < kTileN; c += 4 * nacc * 32) {
+          float w = 1.f;
+          if (P.rowscale != nullptr) {
+            const int row = c & 127;
+            const int t = min(tl.t0 + (c >> 7) * TBH + row / UB, P.T - 1);
+            const long long cell = (long long)(tl.b * P.T + t) * P.U1 + min(u0 + row % UB, P.U1 - 1);
+            w = __ldg(P.rowscale + cell);
+          }
+          rs_t[c] = w;
+        }
+        asm volatile("bar.sync 1, %0;" ::"r"(4 * nacc * 32) : "memory");
         float dp_acc[UB];
 #pragma unroll
         for (int i = 0; i < UB; ++i) dp_acc[i] = 0.f;
@@ -316,9 +332,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
           if (ch + kAhead < 16) load_chunk(ch + kAhead, hreg[ch + kAhead]);
           ptx::tmem_ld_wait();
           if (ch + 1 < 16) ptx::tmem_ld16(taddr + (ch + 1) * 16, r[(ch + 1) & 1]);
+          float4 w4[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) w4[k] = reinterpret_cast<const float4*>(rs_t)[ch * 4 + k];
 #pragma unroll
           for (int k = 0; k < 16; ++k) {
             const int c = ch * 16 + k;
+            const float4 wq = w4[k >> 2];
+            const float wk = (k & 3) == 0 ? wq.x : ((k & 3) == 1 ? wq.y : ((k & 3) == 2 ? wq.z : wq.w));
             uint32_t hp = 0;
             if ((k & 1) == 0) {
               const uint32_t x = hreg[ch][k >> 1];
@@ -326,7 +347,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
             }
             hp = hpair;
             const float hv = __uint_as_float((k & 1) ? (hp & 0xffff0000u) : (hp << 16));
-            const float z = __uint_as_float(r[ch & 1][k]) * fmaf(-hv, hv, 1.f);
+            const float z = (__uint_as_float(r[ch & 1][k]) * wk) * fmaf(-hv, hv, 1.f);
             dp_acc[c % UB] += z;
             de_run += z;
             if (c % UB == UB - 1) {  // last label of a frame: flush d e
@@ -515,8 +536,10 @@ int dh_ctas(int max_ctas) {
 }
 
 int joint_dh_impl(const void* G, const void* G_lo, int ldg, const void* w, const void* w_lo, const void* H,
-                  const void* H_lo, int ldh, int nb, int T, int U1, int V, int J, const int32_t* logit_len,
-                  const int32_t* target_len, float* de, float* dp, int max_ctas, b200_stream_t stream) {
+                  const void* H_lo, int ldh, const float* rowscale, int nb, int T, int U1, int V, int J,
+                  const int32_t* logit_len, const int32_t* target_len, float* de, float* dp, int max_ctas,
+                  b200_stream_t stream) {
+  B200_CHECK_ARG(!(rowscale && G_lo), "b200_joint_dh: rowscale is for single-pass operands only");
   B200_CHECK_ARG(G && w && H && de && dp, "b200_joint_dh: null pointer");
   B200_CHECK_ARG(nb > 0 && T > 0 && U1 > 0 && V > 0, "b200_joint_dh: bad shape nb=%d T=%d U1=%d V=%d", nb, T,
                  U1, V);
@@ -551,6 +574,7 @@ int joint_dh_impl(const void* G, const void* G_lo, int ldg, const void* w, const
   P.npass = G_lo ? 3 : 1;
   P.logit_len = logit_len;
   P.target_len = target_len;
+  P.rowscale = rowscale;
   P.de = de;
   P.dp = dp;
   // label-block size: the power of two that wastes the fewest padded cells (ties: closest to 16,
@@ -589,8 +613,18 @@ int joint_dh_impl(const void* G, const void* G_lo, int ldg, const void* w, const
 extern "C" int b200_joint_dh(const void* G, int ldg, const void* w_bf16, const void* H, int ldh, int nb, int T,
                              int U1, int V, int J, const int32_t* logit_len, const int32_t* target_len,
                              float* de, float* dp, int max_ctas, b200_stream_t stream) {
-  return joint_dh_impl(G, nullptr, ldg, w_bf16, nullptr, H, nullptr, ldh, nb, T, U1, V, J, logit_len, target_len,
-                       de, dp, max_ctas, stream);
+  return joint_dh_impl(G, nullptr, ldg, w_bf16, nullptr, H, nullptr, ldh, nullptr, nb, T, U1, V, J, logit_len,
+                       target_len, de, dp, max_ctas, stream);
+}
+
+// with a per-cell factor on dH (no-recompute backward: G = Pt', factor = rowscale of b200_joint_rowscale)
+extern "C" int b200_joint_dh_scaled(const void* G, int ldg, const void* w_bf16, const void* H, int ldh,
+                                    const float* rowscale, int nb, int T, int U1, int V, int J,
+                                    const int32_t* logit_len, const int32_t* target_len, float* de, float* dp,
+                                    int max_ctas, b200_stream_t stream) {
+  B200_CHECK_ARG(rowscale, "b200_joint_dh_scaled: null pointer");
+  return joint_dh_impl(G, nullptr, ldg, w_bf16, nullptr, H, nullptr, ldh, rowscale, nb, T, U1, V, J, logit_len,
+                       target_len, de, dp, max_ctas, stream);
 }
 
 extern "C" int b200_joint_dh_split(const void* G_hi, const void* G_lo, int ldg, const void* w_hi,
@@ -598,8 +632,8 @@ extern "C" int b200_joint_dh_split(const void* G_hi, const void* G_lo, int ldg, 
                                    int U1, int V, int J, const int32_t* logit_len, const int32_t* target_len,
                                    float* de, float* dp, int max_ctas, b200_stream_t stream) {
   B200_CHECK_ARG(G_lo && w_lo && H_lo, "b200_joint_dh_split: null pointer");
-  return joint_dh_impl(G_hi, G_lo, ldg, w_hi, w_lo, H_hi, H_lo, ldh, nb, T, U1, V, J, logit_len, target_len, de,
-                       dp, max_ctas, stream);
+  return joint_dh_impl(G_hi, G_lo, ldg, w_hi, w_lo, H_hi, H_lo, ldh, nullptr, nb, T, U1, V, J, logit_len,
+                       target_len, de, dp, max_ctas, stream);
 }
 
 extern "C" int b200_split_gemm_nn(const void* G_hi, const void* G_lo, int ldg, const void* w_hi, const void* w_lo,

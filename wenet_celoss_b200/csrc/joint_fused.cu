@@ -57,6 +57,8 @@ constexpr int kOperandBytes = 224 * 1024;  // A staging + W ring (+ G staging), 
 //   MODE_FWD : 512 threads: 8 epilogue warps (64 columns each) + 4 A-builder warps
 //   MODE_GRAD: 640 threads: 16 epilogue warps (32 columns each; its epilogue is the longer one:
 //              FADD + bf16 packing + staging stores on top of FFMA / MUFU)
+//   MODE_FWDP: the MODE_GRAD layout (A by TMA from a precomputed H, 16 epilogue warps, staging + TMA
+//              stores) with the forward statistics: see below
 template <int MODE> struct Cfg {
   static constexpr int kEpiWarps = MODE == 0 ? 8 : 16;
   static constexpr int kEpiThreads = kEpiWarps * 32;
@@ -93,7 +95,12 @@ static_assert(Cfg<0>::kABytes + Cfg<0>::kStages * (2 * kTileN * kBlockK * 2) + C
               "operand area");
 static_assert(kTmemA0 + kMaxKB * kBlockK / 2 <= kTmemCols, "tensor memory budget");
 
-enum { MODE_FWD = 0, MODE_GRAD = 1 };
+// MODE_FWDP ("forward + probabilities"): the training forward of the no-recompute backward.  Besides
+// lse / lp_blank / lp_emit its epilogue stores Pt = 2^(logit * log2 e) = exp(logit) in bf16 (the
+// unnormalised softmax numerator; only taken when the logit bound keeps 2^(+-bound) inside fp32 / bf16
+// range).  d loss / d logits is then rowscale[c] * Pt[c, v] with two patched entries per row
+// (joint_nr.cu), so the backward pass runs dW and dH straight from Pt: the logits GEMM is NOT recomputed.
+enum { MODE_FWD = 0, MODE_GRAD = 1, MODE_FWDP = 2 };
 
 struct Params {
   const float* e;       // [B*T, J]
@@ -183,7 +190,7 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
     ptx::mbar_init(ptx::smem_u32(&bars->a_done), 1);
     ptx::fence_barrier_init();
     ptx::prefetch_tensormap(&w_map);
-    if (MODE == MODE_GRAD) {
+    if (MODE != MODE_FWD) {
       ptx::prefetch_tensormap(&h_map);
       ptx::prefetch_tensormap(&g_map);
     }
@@ -291,8 +298,8 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
       }
     }
     __syncwarp();
-  } else if (MODE == MODE_GRAD && warp == 3) {
-    // ===================== A producer (MODE_GRAD): TMA ring fed from the bf16 H scratch =====================
+  } else if (MODE != MODE_FWD && warp == 3) {
+    // ===================== A producer (MODE_GRAD / MODE_FWDP): TMA ring fed from the bf16 H scratch =====================
     const bool leader = ptx::elect_one();
     const uint64_t h_policy = ptx::l2_policy_evict_first();  // each H tile is read once here
     int aslot = 0, aph = 0;

@@ -14,11 +14,15 @@ parameters, whose names are untouched so checkpoints keep loading.
 
 Forward : enc_ffn / pred_ffn (library GEMMs, joint.py:55-56) -> tcgen05 joint kernel with a
           streaming log-softmax epilogue (lse, lp_blank, lp_emit per cell) -> lattice kernel.
-Backward: per chunk of whole utterances, the same tcgen05 mainloop recomputes the logits
-          tile and its epilogue writes G = d loss / d logits (bf16) into a bounded scratch;
-          dW = G^T H is the 2-CTA tcgen05 kernel of csrc/joint_dw.cu (both operands MN-major,
-          split over cells), dH = G W a plain library GEMM on that scratch; the
-          tanh' / sum-over-u / sum-over-t reduction gives d e and d p.
+Backward, no-recompute path (default when a gradient is needed, the bf16 scratch fits and the logit
+          bound is small): the forward epilogue also stored Pt = exp(logit) (bf16, a backward-only
+          scratch); d loss / d logits = rowscale[cell] * Pt with two patched entries per row
+          (csrc/joint_nr.cu), so dW = Pt^T (rowscale H) and d b (csrc/joint_dw.cu, 2-CTA tcgen05) and
+          dH = rowscale (Pt W) with tanh' and the sums over u / t in its epilogue (csrc/joint_dh.cu)
+          run without a second logits GEMM: three vocabulary GEMMs per step instead of four.
+Backward, recompute path (large logit bounds, scratch above SCRATCH_BYTES): per chunk of whole
+          utterances the tcgen05 mainloop recomputes the logits tile and its epilogue writes
+          G = d loss / d logits (bf16) into a bounded scratch, then the same dW / dH kernels.
 Operands of the big GEMMs are bf16 (fp32 accumulate); tolerance vs the fp32 reference is
 rtol 1e-2 (north_star's bf16 bar).
 """
@@ -36,6 +40,11 @@ _TILE_N = 256
 _TILE_M = 128
 _FORCE_LIBRARY_DH = False  # debugging aid: compare joint_dh_kernel with torch.mm + joint_dz_reduce
 SCRATCH_BYTES = 20 << 30  # bound on the bf16 G scratch of the backward pass (cfg3: 16.2 GB, one chunk)
+NO_RECOMPUTE = True       # keep exp(logit) from the forward pass when it fits SCRATCH_BYTES (see module doc)
+# The no-recompute path stores exp(logit) itself: |logit| * log2(e) must stay below this for rowscale * Pt
+# to keep bf16's relative precision over the whole row (the running-maximum-free forward needs < 100).
+NR_MAX_LOG2_BOUND = 60.0
+LAST_BACKWARD_PATH = None
 
 
 def _chunk_utts(B: int, per_utt: int, ldg: int, sms: int) -> int:
@@ -98,25 +107,52 @@ class _FusedJointLossFn(torch.autograd.Function):
     @staticmethod
     @custom_fwd(device_type="cuda", cast_inputs=torch.float32)
     def forward(ctx, e, p, w_out, b_out, targets, logit_lengths, target_lengths, blank,
-                max_ctas=0, use_bound=True):
+                max_ctas=0, use_bound=True, no_recompute=None):
         dev = e.device
         with torch.cuda.device(dev):
             e32 = e.detach().float().contiguous()
             p32 = p.detach().float().contiguous()
             V, J = w_out.shape
+            B, T = e32.shape[:2]
+            U1 = p32.shape[1]
+            cells = B * T * U1
             w_bf16 = w_out.detach().to(torch.bfloat16).contiguous()
             bias_pad = _pad_bias(b_out, V)
             # when a gradient will be asked for, the forward kernel keeps H = tanh(e + p) (bf16,
             # J / (2 V) of the logits' size: 1.65 GB at cfg3) for the backward kernels
             need_grad = any(ctx.needs_input_grad[:4])
-            H = (torch.empty(e32.shape[0] * e32.shape[1] * p32.shape[1], J, dtype=torch.bfloat16, device=dev)
-                 if need_grad else None)
-            lse, lpb, lpe = joint_logprobs(e32, p32, w_bf16, bias_pad, targets, logit_lengths,
-                                           target_lengths, V, blank, max_ctas=max_ctas,
-                                           use_bound=use_bound, H=H)
+            H = torch.empty(cells, J, dtype=torch.bfloat16, device=dev) if need_grad else None
+            ldg = (V + 15) // 16 * 16
+            nr = NO_RECOMPUTE if no_recompute is None else bool(no_recompute)
+            nr = (nr and need_grad and use_bound and J in (256, 512) and cells * ldg * 2 <= SCRATCH_BYTES
+                  and cells * ldg < (1 << 62))
+            bound = None
+            if nr:  # one 4-byte read: the path is chosen on the host
+                bound = joint_logit_bound(w_bf16, bias_pad, V)
+                nr = float(bound.item()) * 1.4426950408889634 < NR_MAX_LOG2_BOUND
+            Pt = None
+            if nr:
+                Pt = torch.empty(cells, ldg, dtype=torch.bfloat16, device=dev)
+                lat = torch.empty(3, B, T, U1, dtype=torch.float32, device=dev)
+                lse, lpb, lpe = lat.unbind(0)
+                _lib.call("b200_joint_fwd_p", ptr(e32), ptr(p32), ptr(w_bf16), ptr(bias_pad), ptr(targets),
+                          ptr(logit_lengths), ptr(target_lengths), i32(B), i32(T), i32(U1), i32(V), i32(J),
+                          i32(blank), ptr(lse), ptr(lpb), ptr(lpe), ptr(bound), ptr(H), i32(J), ptr(Pt),
+                          i32(ldg), i32(max_ctas), _lib.stream_handle(dev))
+            else:
+                lse, lpb, lpe = joint_logprobs(e32, p32, w_bf16, bias_pad, targets, logit_lengths,
+                                               target_lengths, V, blank, max_ctas=max_ctas,
+                                               use_bound=use_bound, H=H)
             alpha, beta, costs, diag_off = rnnt_lattice(lpb, lpe, logit_lengths, target_lengths)
-        ctx.save_for_backward(e32, p32, w_bf16, bias_pad, targets, logit_lengths, target_lengths,
-                              lse, alpha, beta, diag_off, H)
+        if nr:
+            ctx.save_for_backward(e32, p32, w_bf16, bias_pad, targets, logit_lengths, target_lengths,
+                                  lse, alpha, beta, diag_off, H, Pt, lpb, lpe)
+        else:
+            ctx.save_for_backward(e32, p32, w_bf16, bias_pad, targets, logit_lengths, target_lengths,
+                                  lse, alpha, beta, diag_off, H)
+        ctx.nr = nr
+        global LAST_BACKWARD_PATH
+        LAST_BACKWARD_PATH = "no_recompute" if nr else "recompute"  # read by the tests / bench
         ctx.blank = blank
         ctx.max_ctas = max_ctas  # tests only: fewer persistent CTAs -> more tiles per CTA
         ctx.in_dtypes = (e.dtype, p.dtype, w_out.dtype, b_out.dtype)
@@ -125,6 +161,8 @@ class _FusedJointLossFn(torch.autograd.Function):
     @staticmethod
     @custom_bwd(device_type="cuda")
     def backward(ctx, dy):
+        if ctx.nr:
+            return _FusedJointLossFn._backward_nr(ctx, dy)
         (e32, p32, w_bf16, bias_pad, targets, logit_lengths, target_lengths, lse, alpha, beta,
          diag_off, H_all) = ctx.saved_tensors
         B, T, J = e32.shape
@@ -176,7 +214,43 @@ class _FusedJointLossFn(torch.autograd.Function):
                               i32(U1), i32(J), ptr(de[b0:b1]), ptr(dp[b0:b1]), st)
         dt_e, dt_p, dt_w, dt_b = ctx.in_dtypes
         return (de.to(dt_e), dp.to(dt_p), dW.to(dt_w), db_part.sum(0)[:V].to(dt_b), None,
-                None, None, None, None, None)
+                None, None, None, None, None, None)
+
+    @staticmethod
+    def _backward_nr(ctx, dy):
+        """No-recompute backward: G = rowscale * Pt' (csrc/joint_nr.cu), then dW / d b and dH."""
+        (e32, p32, w_bf16, bias_pad, targets, logit_lengths, target_lengths, lse, alpha, beta,
+         diag_off, H, Pt, lpb, lpe) = ctx.saved_tensors
+        B, T, J = e32.shape
+        U1 = p32.shape[1]
+        V = w_bf16.shape[0]
+        dev = e32.device
+        blank = ctx.blank
+        cells = B * T * U1
+        ldg = Pt.stride(0)
+        with torch.cuda.device(dev):
+            st = _lib.stream_handle(dev)
+            dyf = dy.detach().to(torch.float32).contiguous()
+            coef = rnnt_grad_coef(lse, alpha, beta, diag_off, dyf, targets, logit_lengths,
+                                  target_lengths, blank)
+            rowscale = torch.empty(cells, dtype=torch.float32, device=dev)
+            Hs = torch.empty_like(H)
+            # (patching Pt in place is idempotent: the two entries are recomputed from fp32 statistics)
+            _lib.call("b200_joint_rowscale", ptr(coef), ptr(lse), ptr(lpb), ptr(lpe), ptr(targets), i32(B),
+                      i32(T), i32(U1), i32(V), i32(J), i32(blank), ptr(Pt), i32(ldg), ptr(H), i32(J), ptr(Hs),
+                      ptr(rowscale), st)
+            dW = torch.zeros(V, J, dtype=torch.float32, device=dev)
+            db = torch.zeros(V, dtype=torch.float32, device=dev)
+            de = torch.zeros(B, T, J, dtype=torch.float32, device=dev)
+            dp = torch.zeros(B, U1, J, dtype=torch.float32, device=dev)
+            _lib.call("b200_joint_dw_db", ptr(Pt), i32(ldg), ptr(Hs), i32(J), _i64(cells), i32(V), i32(J),
+                      ptr(dW), ptr(rowscale), ptr(db), i32(ctx.max_ctas), st)
+            _lib.call("b200_joint_dh_scaled", ptr(Pt), i32(ldg), ptr(w_bf16), ptr(H), i32(J), ptr(rowscale),
+                      i32(B), i32(T), i32(U1), i32(V), i32(J), ptr(logit_lengths), ptr(target_lengths),
+                      ptr(de), ptr(dp), i32(ctx.max_ctas), st)
+        dt_e, dt_p, dt_w, dt_b = ctx.in_dtypes
+        return (de.to(dt_e), dp.to(dt_p), dW.to(dt_w), db.to(dt_b), None, None, None, None, None, None,
+                None)
 
 
 def split_f32(x: torch.Tensor):
@@ -309,7 +383,7 @@ def fused_joint_rnnt_loss(joint, enc_out: torch.Tensor, pred_out: torch.Tensor,
                           targets: torch.Tensor, logit_lengths: torch.Tensor,
                           target_lengths: torch.Tensor, blank: int = 0,
                           reduction: str = "mean", *, precision: str = "auto", _max_ctas: int = 0,
-                          _use_bound: bool = True) -> torch.Tensor:
+                          _use_bound: bool = True, _no_recompute=None) -> torch.Tensor:
     """RNN-T loss of ``joint(enc_out, pred_out)`` without materialising the logits.
 
     enc_out [B,T,E], pred_out [B,U+1,P]; targets [B,U] int32 zero-padded; lengths int32
@@ -320,8 +394,9 @@ def fused_joint_rnnt_loss(joint, enc_out: torch.Tensor, pred_out: torch.Tensor,
     tensor-core products per GEMM, results within rtol 1e-4 of the reference's fp32 run), "auto"
     = "bf16" under autocast or for half-precision inputs, else "fp32".
 
-    ``_max_ctas`` / ``_use_bound`` are test hooks: cap the persistent grids (so that every CTA
-    walks many tiles on small shapes) and force the running-maximum epilogue."""
+    ``_max_ctas`` / ``_use_bound`` / ``_no_recompute`` are test hooks: cap the persistent grids (so
+    that every CTA walks many tiles on small shapes), force the running-maximum epilogue, and pick the
+    backward variant (None = the module default ``NO_RECOMPUTE``, False = recompute path)."""
     if reduction not in ("none", "mean", "sum"):
         raise ValueError('reduction should be one of "none", "mean", or "sum"')
     if precision not in ("auto", "bf16", "fp32"):
@@ -346,7 +421,7 @@ def fused_joint_rnnt_loss(joint, enc_out: torch.Tensor, pred_out: torch.Tensor,
     else:
         costs = _FusedJointLossFn.apply(e, p, joint.ffn_out.weight, joint.ffn_out.bias, targets,
                                         logit_lengths, target_lengths, int(blank), int(_max_ctas),
-                                        bool(_use_bound))
+                                        bool(_use_bound), _no_recompute)
     if reduction == "mean":
         return costs.mean()
     if reduction == "sum":
