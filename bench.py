@@ -448,14 +448,50 @@ class RnntFusedWorkload:
             _lib.call("b200_joint_dh", ptr(G), i32(ldg), ptr(w), ptr(H_all), i32(J), i32(B), i32(T), i32(U1),
                       i32(V), i32(J), ptr(self.tl), ptr(self.ul), ptr(de), ptr(dp), i32(0), st)
 
+        # the no-recompute backward (what the step runs when the logit bound allows: joint.py)
+        from wenet_celoss_b200 import joint as jmod
+        from wenet_celoss_b200.joint import joint_logit_bound
+        nr = jmod.LAST_BACKWARD_PATH == "no_recompute"
+        bound = joint_logit_bound(w, bias, V)
+        rowscale = torch.empty(B * per_utt, device=self.dev)
+        Hs = torch.empty_like(H_all) if nr else None
+        db = torch.zeros(V, device=self.dev)
+
+        def k_fwdp():  # joint_h_kernel + joint_kernel<FWDP>: statistics and Pt = exp(logit) (bf16) into G
+            lat = torch.empty(3, B, T, U1, device=self.dev)
+            _lib.call("b200_joint_fwd_p", ptr(e), ptr(p), ptr(w), ptr(bias), ptr(self.targets), ptr(self.tl),
+                      ptr(self.ul), i32(B), i32(T), i32(U1), i32(V), i32(J), i32(0), ptr(lat[0]), ptr(lat[1]),
+                      ptr(lat[2]), ptr(bound), ptr(H_all), i32(J), ptr(G), i32(ldg), i32(0), st)
+            box["lat"] = lat.unbind(0)
+
+        def k_rowscale():
+            _lib.call("b200_joint_rowscale", ptr(box["coef"]), ptr(box["lat"][0]), ptr(box["lat"][1]),
+                      ptr(box["lat"][2]), ptr(self.targets), i32(B), i32(T), i32(U1), i32(V), i32(J), i32(0),
+                      ptr(G), i32(ldg), ptr(H_all), i32(J), ptr(Hs), ptr(rowscale), st)
+
+        def k_dw_db():
+            _lib.call("b200_joint_dw_db", ptr(G), i32(ldg), ptr(Hs), i32(J), _i64(B * per_utt), i32(V), i32(J),
+                      ptr(dW8), ptr(rowscale), ptr(db), i32(0), st)
+
+        def k_dh_scaled():
+            de.zero_(); dp.zero_()
+            _lib.call("b200_joint_dh_scaled", ptr(G), i32(ldg), ptr(w), ptr(H_all), i32(J), ptr(rowscale), i32(B),
+                      i32(T), i32(U1), i32(V), i32(J), ptr(self.tl), ptr(self.ul), ptr(de), ptr(dp), i32(0), st)
+
         out = {}
-        k_fwd(); k_lat()
+        (k_fwdp if nr else k_fwd)(); k_lat()
         alpha, beta, costs, doff = box["ab"]
         box["coef"] = rnnt_grad_coef(box["lat"][0], alpha, beta, doff, dy, self.targets, self.tl, self.ul, 0)
-        for name, fn in (("joint_kernel<FWD> (all cells)", k_fwd), ("rnnt_lattice_kernel", k_lat),
-                         ("joint_kernel<GRAD> (all cells, one chunk)", k_grad),
-                         ("joint_dw_kernel (all cells)", k_dw),
-                         ("joint_dh_kernel (all cells)", k_dh)):
+        if nr:
+            plan = (("joint_kernel<FWDP> (all cells, with joint_h_kernel)", k_fwdp), ("rnnt_lattice_kernel", k_lat),
+                    ("joint_rowscale_kernel", k_rowscale), ("joint_dw_kernel (all cells, with d b)", k_dw_db),
+                    ("joint_dh_kernel (all cells)", k_dh_scaled))
+        else:
+            plan = (("joint_kernel<FWD> (all cells)", k_fwd), ("rnnt_lattice_kernel", k_lat),
+                    ("joint_kernel<GRAD> (all cells, one chunk)", k_grad),
+                    ("joint_dw_kernel (all cells)", k_dw), ("joint_dh_kernel (all cells)", k_dh))
+        out["backward_path"] = jmod.LAST_BACKWARD_PATH
+        for name, fn in plan:
             ts = []
             for _ in range(iters + 1):
                 e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
@@ -475,6 +511,7 @@ class RnntFusedWorkload:
         kb = self.kernel_breakdown()
         cfg = self.cfg
         flops = 2.0 * self.cells * cfg["J"] * cfg["V"]  # per GEMM-shaped launch (2*cells*J*V)
+        path = kb.pop("backward_path", None)
         tensor_kernels = {k: v for k, v in kb.items()
                           if k.startswith(("joint_kernel", "joint_dw_kernel", "joint_dh_kernel"))}
         dom = max(tensor_kernels, key=tensor_kernels.get)
@@ -492,7 +529,7 @@ class RnntFusedWorkload:
                 "unit": "TFLOP/s", "frac": ach[dom] / pk["bf16"], "traffic": traffic,
                 "traffic_source": traffic_src,
                 "peak_source": pk["source"] + " (burst: kernel timed alone)",
-                "algorithmic_flops_per_launch": flops, "kernel_ms": kb,
+                "algorithmic_flops_per_launch": flops, "kernel_ms": kb, "backward_path": path,
                 "other": {k: {"achieved": a, "frac": a / pk["bf16"]} for k, a in ach.items() if k != dom},
                 "step_frac_of_tensor_roofline":
                     counted / (ms_step * 1e-3) / 1e12 / pk["bf16_sustained"],

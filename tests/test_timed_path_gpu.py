@@ -141,6 +141,22 @@ def test_running_max_epilogue_large_weights():
     _check(case, expect_nr=False, _max_ctas=3)
 
 
+def test_bound_between_no_recompute_and_running_max():
+    """60 <= bound * log2(e) < 100: the training forward kernel (joint_kernel<FWDP>) keeps the
+    maximum-free statistics but must NOT hand exp(logit) to the backward pass - the recompute
+    variant is chosen (on the device and, through the asynchronous flag, on the host)."""
+    from wenet_celoss_b200.joint import _pad_bias, joint_logit_bound
+    case = _case(3, 30, 10, 700, 64, 512, seed=18, ragged=True)
+    joint = case[0]
+    with torch.no_grad():
+        joint.ffn_out.weight.mul_(2.2)  # x2 in _case (bound * log2 e ~ 35) -> ~ 78
+    w = joint.ffn_out.weight.to(DEV).to(torch.bfloat16).contiguous()
+    bound = joint_logit_bound(w, _pad_bias(joint.ffn_out.bias.to(DEV), 700), 700)
+    assert 60.0 < float(bound) * 1.4427 < 100.0, float(bound) * 1.4427
+    _check(case, expect_nr=False)
+    _check(case, expect_nr=False, _max_ctas=3)
+
+
 def test_running_max_epilogue_no_bound():
     """use_bound=False: same inputs as the fast path, results must agree with it and the reference."""
     case = _case(3, 30, 10, 700, 64, 512, seed=16, ragged=True)

@@ -82,6 +82,7 @@ template <int MODE> struct Cfg {
 };
 constexpr int kWBlockBytes = kTileN * kBlockK * 2;      // 16 KB per k-block
 constexpr int kWStageBytes = 2 * kWBlockBytes;          // 32 KB
+constexpr float kNrMaxLog2Bound = 60.f;  // MODE_FWDP keeps exp(logit) only below this bound * log2(e)
 constexpr int kTmemCols = 512;
 constexpr int kTmemA0 = 2 * kTileN;  // TMEM columns [256,512): A, 2 bf16 per 32-bit column
 constexpr int kBarBytes = 512;
@@ -400,29 +401,45 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
 // H[cell - cell0, 0:J] = bf16(tanh(e[b,t,:] + p[b,u,:])) for one chunk of cells: the A operand of
 // the backward joint kernel (read back through TMA while still in L2) and of the dW GEMM.
 // Same arithmetic as the forward builders (tanh.approx.f32, round-to-nearest bf16).
+// Block = (256 / (J/8)) cell rows x J/8 threads of 8 elements; 32-bit index arithmetic only (the host
+// checks cells, B*T*J, B*U1*J < 2^31): the 64-bit divisions of the first version cost more than the
+// tanh.  Two rows per thread and iteration keep 8 independent 16-byte loads in flight.
 __global__ void __launch_bounds__(256)
 joint_h_kernel(const float* __restrict__ e, const float* __restrict__ p, int T, int U1, int J,
                long long cell0, long long ncells, __nv_bfloat16* __restrict__ H, int ldh) {
-  const int g8 = J >> 3;  // 8-element groups per row
-  const long long total = ncells * g8;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const long long local = i / g8;
-    const int k0 = (int)(i - local * g8) << 3;
-    const long long cell = cell0 + local;
-    const long long bt = cell / U1;
-    const int u = (int)(cell - bt * U1);
-    const long long b = bt / T;
-    const float4* ep = reinterpret_cast<const float4*>(e + bt * J + k0);
-    const float4* pp = reinterpret_cast<const float4*>(p + (b * U1 + u) * J + k0);
+  const int g8 = J >> 3;                      // 16-byte groups per row
+  const int rows = blockDim.x / g8;           // cell rows per block and pass
+  const int r = threadIdx.x / g8;
+  const int k0 = (threadIdx.x - r * g8) << 3;
+  if (r >= rows) return;
+  const unsigned n = (unsigned)ncells, c0 = (unsigned)cell0;
+  const unsigned stride = (unsigned)gridDim.x * rows;
+  auto compute = [&](unsigned local, uint4& h) {
+    const unsigned cell = c0 + local;
+    const unsigned bt = cell / (unsigned)U1;
+    const unsigned u = cell - bt * (unsigned)U1;
+    const unsigned b = bt / (unsigned)T;
+    const float4* ep = reinterpret_cast<const float4*>(e + (size_t)bt * J + k0);
+    const float4* pp = reinterpret_cast<const float4*>(p + (size_t)(b * U1 + u) * J + k0);
     const float4 e0 = __ldg(ep), e1 = __ldg(ep + 1);
     const float4 p0 = __ldg(pp), p1 = __ldg(pp + 1);
-    uint4 h;
     h.x = pack_bf16x2(tanh_approx(e0.x + p0.x), tanh_approx(e0.y + p0.y));
     h.y = pack_bf16x2(tanh_approx(e0.z + p0.z), tanh_approx(e0.w + p0.w));
     h.z = pack_bf16x2(tanh_approx(e1.x + p1.x), tanh_approx(e1.y + p1.y));
     h.w = pack_bf16x2(tanh_approx(e1.z + p1.z), tanh_approx(e1.w + p1.w));
-    *reinterpret_cast<uint4*>(H + local * ldh + k0) = h;
+  };
+  unsigned local = blockIdx.x * rows + r;
+  for (; local + stride < n; local += 2 * stride) {
+    uint4 h0, h1;
+    compute(local, h0);
+    compute(local + stride, h1);
+    *reinterpret_cast<uint4*>(H + (size_t)local * ldh + k0) = h0;
+    *reinterpret_cast<uint4*>(H + (size_t)(local + stride) * ldh + k0) = h1;
+  }
+  if (local < n) {
+    uint4 h0;
+    compute(local, h0);
+    *reinterpret_cast<uint4*>(H + (size_t)local * ldh + k0) = h0;
   }
 }
 

@@ -18,6 +18,7 @@
 namespace b200 {
 namespace nr {
 
+// Block = (256 / (J/8)) cell rows x J/8 threads of 8 elements, 32-bit index arithmetic (cells < 2^31).
 __global__ void __launch_bounds__(256)
 joint_rowscale_kernel(const float4* __restrict__ coef, const float* __restrict__ lse,
                       const float* __restrict__ lp_blank, const float* __restrict__ lp_emit,
@@ -25,14 +26,13 @@ joint_rowscale_kernel(const float4* __restrict__ coef, const float* __restrict__
                       __nv_bfloat16* __restrict__ Pt, long long ldg, const __nv_bfloat16* __restrict__ H,
                       long long ldh, __nv_bfloat16* __restrict__ Hs, float* __restrict__ rowscale) {
   const int g8 = J >> 3;  // 16-byte groups per row
-  const long long total = cells * g8;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const long long cell = i / g8;
-    const int k0 = (int)(i - cell * g8) << 3;
-    const float4 c = __ldg(coef + cell);
-    const float rs = c.x == -INFINITY ? 0.f : c.w * __expf(c.x);
-    const uint4 h = __ldg(reinterpret_cast<const uint4*>(H + cell * ldh + k0));
+  const int rows = blockDim.x / g8;
+  const int r = threadIdx.x / g8;
+  const int k0 = (threadIdx.x - r * g8) << 3;
+  if (r >= rows) return;
+  const unsigned n = (unsigned)cells;
+  const unsigned stride = (unsigned)gridDim.x * rows;
+  auto scale_row = [&](unsigned cell, float rs, uint4 h) {
     uint4 o;
     const uint32_t* hi = &h.x;
     uint32_t* oo = &o.x;
@@ -43,32 +43,52 @@ joint_rowscale_kernel(const float4* __restrict__ coef, const float* __restrict__
       const __nv_bfloat162 v = __floats2bfloat162_rn(lo, up);
       oo[k] = *reinterpret_cast<const uint32_t*>(&v);
     }
-    *reinterpret_cast<uint4*>(Hs + cell * ldh + k0) = o;
-    if (k0 == 0) {
-      rowscale[cell] = rs;
-      if (rs != 0.f) {
-        const float ls = lse[cell];
-        const bool has_b = c.y != -INFINITY, has_e = c.z != -INFINITY;
-        int y = -1;
-        if (has_e) {
-          const long long bt = cell / U1;
-          const int u = (int)(cell - bt * U1);
-          const int b = (int)(bt / T);
-          y = targets[(long long)b * (U1 - 1) + u];
-        }
-        // exp(x + (cb - c0)) <= exp(lse): lp + beta_next <= beta (the lattice recursion)
-        if (has_b) {
-          const float xb = lp_blank[cell] + ls;
-          float v = __expf(xb) - __expf(xb + (c.y - c.x));
-          if (y == blank) v -= __expf(xb + (c.z - c.x));
-          Pt[cell * ldg + blank] = __float2bfloat16_rn(v);
-        }
-        if (has_e && !(y == blank && has_b)) {
-          const float xe = lp_emit[cell] + ls;
-          Pt[cell * ldg + y] = __float2bfloat16_rn(__expf(xe) - __expf(xe + (c.z - c.x)));
-        }
-      }
+    *reinterpret_cast<uint4*>(Hs + (size_t)cell * ldh + k0) = o;
+  };
+  auto patch = [&](unsigned cell, const float4 c, float rs) {
+    rowscale[cell] = rs;
+    if (rs == 0.f) return;
+    const float ls = lse[cell];
+    const bool has_b = c.y != -INFINITY, has_e = c.z != -INFINITY;
+    int y = -1;
+    if (has_e) {
+      const unsigned bt = cell / (unsigned)U1;
+      const unsigned u = cell - bt * (unsigned)U1;
+      const unsigned b = bt / (unsigned)T;
+      y = targets[(size_t)b * (U1 - 1) + u];
     }
+    // exp(x + (cb - c0)) <= exp(lse): lp + beta_next <= beta (the lattice recursion)
+    if (has_b) {
+      const float xb = lp_blank[cell] + ls;
+      float v = __expf(xb) - __expf(xb + (c.y - c.x));
+      if (y == blank) v -= __expf(xb + (c.z - c.x));
+      Pt[(size_t)cell * ldg + blank] = __float2bfloat16_rn(v);
+    }
+    if (has_e && !(y == blank && has_b)) {
+      const float xe = lp_emit[cell] + ls;
+      Pt[(size_t)cell * ldg + y] = __float2bfloat16_rn(__expf(xe) - __expf(xe + (c.z - c.x)));
+    }
+  };
+  unsigned cell = blockIdx.x * rows + r;
+  for (; cell + stride < n; cell += 2 * stride) {  // two rows per pass: four 16-byte loads in flight
+    const float4 c0 = __ldg(coef + cell), c1 = __ldg(coef + cell + stride);
+    const uint4 h0 = __ldg(reinterpret_cast<const uint4*>(H + (size_t)cell * ldh + k0));
+    const uint4 h1 = __ldg(reinterpret_cast<const uint4*>(H + (size_t)(cell + stride) * ldh + k0));
+    const float r0 = c0.x == -INFINITY ? 0.f : c0.w * __expf(c0.x);
+    const float r1 = c1.x == -INFINITY ? 0.f : c1.w * __expf(c1.x);
+    scale_row(cell, r0, h0);
+    scale_row(cell + stride, r1, h1);
+    if (k0 == 0) {
+      patch(cell, c0, r0);
+      patch(cell + stride, c1, r1);
+    }
+  }
+  if (cell < n) {
+    const float4 c0 = __ldg(coef + cell);
+    const uint4 h0 = __ldg(reinterpret_cast<const uint4*>(H + (size_t)cell * ldh + k0));
+    const float r0 = c0.x == -INFINITY ? 0.f : c0.w * __expf(c0.x);
+    scale_row(cell, r0, h0);
+    if (k0 == 0) patch(cell, c0, r0);
   }
 }
 
@@ -92,14 +112,15 @@ extern "C" int b200_joint_rowscale(const float* coef, const float* lse, const fl
   B200_CHECK_ARG((((uintptr_t)coef | (uintptr_t)H | (uintptr_t)Hs) & 15) == 0,
                  "b200_joint_rowscale: coef, H, Hs must be 16-byte aligned");
   const long long cells = (long long)B * T * U1;
-  const long long groups = cells * (J / 8);
+  B200_CHECK_ARG(cells < (1ll << 31) && J <= 2048, "b200_joint_rowscale: more than 2^31 cells or J > 2048");
   int sms = 0, dev = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (sms <= 0) sms = 148;
-  long long blocks = (groups + 255) / 256;
+  const int g8 = J / 8, rows = 256 / g8;
+  long long blocks = (cells + rows - 1) / rows;
   if (blocks > 16ll * sms) blocks = 16ll * sms;
-  nr::joint_rowscale_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(
+  nr::joint_rowscale_kernel<<<(int)blocks, rows * g8, 0, (cudaStream_t)stream>>>(
       reinterpret_cast<const float4*>(coef), lse, lp_blank, lp_emit, targets, T, U1, J, blank, cells,
       reinterpret_cast<__nv_bfloat16*>(Pt), ldg, reinterpret_cast<const __nv_bfloat16*>(H), ldh,
       reinterpret_cast<__nv_bfloat16*>(Hs), rowscale);

@@ -43,8 +43,31 @@ SCRATCH_BYTES = 20 << 30  # bound on the bf16 G scratch of the backward pass (cf
 NO_RECOMPUTE = True       # keep exp(logit) from the forward pass when it fits SCRATCH_BYTES (see module doc)
 # The no-recompute path stores exp(logit) itself: |logit| * log2(e) must stay below this for rowscale * Pt
 # to keep bf16's relative precision over the whole row (the running-maximum-free forward needs < 100).
-NR_MAX_LOG2_BOUND = 60.0
+# jf::kNrMaxLog2Bound (csrc/joint_fused.cu) is 60: the kernel keeps exp(logit) below it; the host takes the
+# no-recompute backward only a margin below, so that rounding can never make the two tests disagree
+NR_MAX_LOG2_BOUND = 59.99
 LAST_BACKWARD_PATH = None
+_LOG2E = 1.4426950408889634
+
+# The forward kernel decides ON THE DEVICE (from the logit-bound scalar) whether it keeps exp(logit); the
+# host learns the decision through a 1-byte pinned buffer + event and reads it in backward(), long after
+# the copy has completed: no host synchronisation between enc_ffn and the forward joint kernel.
+_FLAG_RING: list = []   # [pinned bool tensor, generation]
+_flag_next = -1
+
+
+def _flag_slot():
+    """(slot, generation): slots are reused round-robin; backward() checks the generation and repeats
+    the test synchronously if 64 other forwards have run since its own."""
+    global _flag_next
+    if len(_FLAG_RING) < 64:
+        _FLAG_RING.append([torch.empty(1, dtype=torch.bool).pin_memory(), 0])
+        _flag_next = len(_FLAG_RING) - 1
+    else:
+        _flag_next = (_flag_next + 1) % len(_FLAG_RING)
+    slot = _FLAG_RING[_flag_next]
+    slot[1] += 1
+    return slot, slot[1]
 
 
 def _chunk_utts(B: int, per_utt: int, ldg: int, sms: int) -> int:
@@ -124,14 +147,17 @@ class _FusedJointLossFn(torch.autograd.Function):
             H = torch.empty(cells, J, dtype=torch.bfloat16, device=dev) if need_grad else None
             ldg = (V + 15) // 16 * 16
             nr = NO_RECOMPUTE if no_recompute is None else bool(no_recompute)
-            nr = (nr and need_grad and use_bound and J in (256, 512) and cells * ldg * 2 <= SCRATCH_BYTES
-                  and cells * ldg < (1 << 62))
-            bound = None
-            if nr:  # one 4-byte read: the path is chosen on the host
-                bound = joint_logit_bound(w_bf16, bias_pad, V)
-                nr = float(bound.item()) * 1.4426950408889634 < NR_MAX_LOG2_BOUND
+            nr = nr and need_grad and use_bound and J in (256, 512) and cells * ldg * 2 <= SCRATCH_BYTES
             Pt = None
+            nr_flag = nr_event = None
             if nr:
+                # eligible: the kernel keeps exp(logit) iff bound * log2(e) < NR_MAX_LOG2_BOUND; the same
+                # test goes to the host asynchronously and picks the backward variant
+                bound = joint_logit_bound(w_bf16, bias_pad, V)
+                nr_flag = _flag_slot()
+                nr_flag[0][0].copy_(bound * _LOG2E < NR_MAX_LOG2_BOUND, non_blocking=True)
+                nr_event = torch.cuda.Event()
+                nr_event.record(torch.cuda.current_stream(dev))
                 Pt = torch.empty(cells, ldg, dtype=torch.bfloat16, device=dev)
                 lat = torch.empty(3, B, T, U1, dtype=torch.float32, device=dev)
                 lse, lpb, lpe = lat.unbind(0)
@@ -151,8 +177,7 @@ class _FusedJointLossFn(torch.autograd.Function):
             ctx.save_for_backward(e32, p32, w_bf16, bias_pad, targets, logit_lengths, target_lengths,
                                   lse, alpha, beta, diag_off, H)
         ctx.nr = nr
-        global LAST_BACKWARD_PATH
-        LAST_BACKWARD_PATH = "no_recompute" if nr else "recompute"  # read by the tests / bench
+        ctx.nr_flag, ctx.nr_event = nr_flag, nr_event
         ctx.blank = blank
         ctx.max_ctas = max_ctas  # tests only: fewer persistent CTAs -> more tiles per CTA
         ctx.in_dtypes = (e.dtype, p.dtype, w_out.dtype, b_out.dtype)
@@ -161,10 +186,22 @@ class _FusedJointLossFn(torch.autograd.Function):
     @staticmethod
     @custom_bwd(device_type="cuda")
     def backward(ctx, dy):
+        global LAST_BACKWARD_PATH
         if ctx.nr:
-            return _FusedJointLossFn._backward_nr(ctx, dy)
+            ctx.nr_event.synchronize()  # recorded before the forward joint kernel: complete long ago
+            (slot, gen) = ctx.nr_flag
+            if slot[1] == gen:
+                take_nr = bool(slot[0][0])
+            else:  # slot reused since: same deterministic test, synchronously
+                w_bf16, bias_pad = ctx.saved_tensors[2:4]
+                take_nr = float(joint_logit_bound(w_bf16, bias_pad, w_bf16.shape[0]).item()) * _LOG2E \
+                    < NR_MAX_LOG2_BOUND
+            if take_nr:
+                LAST_BACKWARD_PATH = "no_recompute"  # read by the tests / bench
+                return _FusedJointLossFn._backward_nr(ctx, dy)
+        LAST_BACKWARD_PATH = "recompute"
         (e32, p32, w_bf16, bias_pad, targets, logit_lengths, target_lengths, lse, alpha, beta,
-         diag_off, H_all) = ctx.saved_tensors
+         diag_off, H_all) = ctx.saved_tensors[:12]
         B, T, J = e32.shape
         U1 = p32.shape[1]
         V = w_bf16.shape[0]
@@ -445,8 +482,21 @@ def _validate_shapes(shape, targets, logit_lengths, target_lengths, blank):
         raise RuntimeError("batch dimension mismatch between logits and targets")
     if not (0 <= blank < V):
         raise RuntimeError("blank must be within [0, logits.shape[-1])")
-    mx = torch.stack([logit_lengths.max(), target_lengths.max()]).tolist()
+    # torchaudio's contract (max lengths == tensor sizes) needs the lengths on the host: one small
+    # device-to-host read per NEW pair of length tensors - the result is remembered for the same
+    # (storage, version) so that re-using a batch does not synchronise the stream again
+    key = (logit_lengths.data_ptr(), logit_lengths._version, target_lengths.data_ptr(),
+           target_lengths._version, B)
+    mx = _LEN_CACHE.get(key)
+    if mx is None:
+        mx = torch.stack([logit_lengths.max(), target_lengths.max()]).tolist()
+        if len(_LEN_CACHE) >= 16:
+            _LEN_CACHE.clear()
+        _LEN_CACHE[key] = mx
     if mx[0] != T:
         raise RuntimeError("input length mismatch")
     if mx[1] != targets.size(1) or U1 != targets.size(1) + 1:
         raise RuntimeError("output length mismatch")
+
+
+_LEN_CACHE: dict = {}
