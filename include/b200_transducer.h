@@ -462,6 +462,22 @@ int b200_ce_loss_bwd(const float* logits, const int64_t* labels, int B, int C, i
                      long long ignore_index, const float* dy, const float* count, float* grad,
                      b200_stream_t stream);
 
+/* ---- n-best rescoring --------------------------------------------
+ * The score-combine step of Transducer.transducer_attention_rescoring (transducer.py:459-513) over the
+ * attention decoder's logits (_cal_attn_score, transducer.py:304-330): per hypothesis i
+ *   attn_i = sum_j log_softmax(dec[i, j])[w_ij] + log_softmax(dec[i, len_i])[eos]   (and the right-to-left
+ *   analogue on rdec, rows len_i - 1 - j, mixed with reverse_weight when it is > 0),
+ *   scores[i] = attn_i * attn_weight + beam_score[i] * ctc_weight + td_score[i] * transducer_weight,
+ *   best = first index of the maximum.
+ * dec / rdec [N, L1, V] fp32 (L1 >= Lmax + 1), hyps_pad [N, Lmax] int64 (entries beyond hyps_lens ignored),
+ * beam_score [N] fp64, td_score [N] fp32 (= -rnnt_loss per hypothesis), scores [N] fp64,
+ * attn_scores optional [N] fp64 (the attention part alone), best [1] int32. */
+int b200_attn_rescore(const float* dec, const float* rdec, const int64_t* hyps_pad,
+                      const int32_t* hyps_lens, int N, int L1, int Lmax, int V, int eos,
+                      double reverse_weight, double attn_weight, const double* beam_score,
+                      double ctc_weight, const float* td_score, double transducer_weight,
+                      double* scores, double* attn_scores, int32_t* best, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -560,3 +560,29 @@ def hw_ce_loss(hw_output, labels, ignore_index: int = -100):
     np.put_along_axis(onehot, ysafe[:, None, :], 1.0, axis=1)
     grad = (np.exp(logp) - onehot) * valid[:, None, :] / max(n, 1)
     return loss, grad.astype(np.float32)
+
+
+# --------------------------------------------------------------------------- n-best rescoring
+def attention_rescoring(hyps, beam_score, td_score, decoder_logp, r_decoder_logp, eos: int,
+                        reverse_weight: float, attn_weight: float, ctc_weight: float,
+                        transducer_weight: float):
+    """The score-combine loop of Transducer.transducer_attention_rescoring (transducer.py:487-511):
+    ``decoder_logp`` / ``r_decoder_logp`` [N, L+1, V] log-softmax outputs of the attention decoder (numpy),
+    ``td_score`` = _cal_transducer_score.  Returns (best index, best score, attention part per hypothesis)."""
+    best_score, best_index, attn = -float("inf"), 0, []
+    for i, hyp in enumerate(hyps):
+        score = 0.0
+        for j, w in enumerate(hyp):
+            score += float(decoder_logp[i][j][w])
+        score += float(decoder_logp[i][len(hyp)][eos])
+        if reverse_weight > 0:
+            r_score = 0.0
+            for j, w in enumerate(hyp):
+                r_score += float(r_decoder_logp[i][len(hyp) - j - 1][w])
+            r_score += float(r_decoder_logp[i][len(hyp)][eos])
+            score = score * (1 - reverse_weight) + r_score * reverse_weight
+        attn.append(score)
+        score = score * attn_weight + beam_score[i] * ctc_weight + float(td_score[i]) * transducer_weight
+        if score > best_score:
+            best_score, best_index = score, i
+    return best_index, best_score, attn

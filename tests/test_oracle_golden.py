@@ -231,3 +231,27 @@ def test_hw_ce_loss_matches_reference(golden):
         loss, grad = orc.hw_ce_loss(d[f"{mode}.hw_output"], d[f"{mode}.labels"])
         np.testing.assert_allclose(loss, float(d[f"{mode}.hw_loss"]), rtol=1e-6)
         np.testing.assert_allclose(grad, d[f"{mode}.grad"], atol=1e-7)
+
+
+def test_attention_rescoring_oracle_vs_reference(golden):
+    """oracle.reference.attention_rescoring reproduces what the real transducer_attention_rescoring
+    (transducer.py:487-511) chose and scored (oracle/gen_golden_rescore.py)."""
+    d = golden("rescore")
+    eos = int(d["sos_eos"][1])
+    for ci in range(int(d["ncases"])):
+        pre = f"c{ci}."
+        beam, rw, cw, aw, tw, _, _ = (float(x) for x in d[pre + "params"])
+        hyps = [row[:n] for row, n in zip(d[pre + "hyps_pad"].tolist(), d[pre + "hyps_lens"].tolist())]
+        dlp = torch.log_softmax(torch.from_numpy(d[pre + "dec"]), -1).numpy()
+        rlp = torch.log_softmax(torch.from_numpy(d[pre + "rdec"]), -1).numpy() if pre + "rdec" in d.files else None
+        bi, bs, attn = orc.attention_rescoring(hyps, d[pre + "beam_score"].tolist(), d[pre + "td_score"].tolist(),
+                                               dlp, rlp, eos, rw, aw, cw, tw)
+        assert bi == int(d[pre + "best_index"]) and hyps[bi] == d[pre + "best_hyp"].tolist()
+        np.testing.assert_allclose(bs, float(d[pre + "best_score"]), rtol=1e-5)
+        np.testing.assert_allclose(attn, d[pre + "attn"], rtol=1e-12)
+        om = load_oracle_model(d)
+        T = d[pre + "speech"].shape[1]
+        N = len(hyps)
+        td = orc.transducer_score(om, torch.from_numpy(d[pre + "speech"]).repeat(N, 1, 1), torch.full((N,), T),
+                                  torch.from_numpy(d[pre + "hyps_pad"]), torch.from_numpy(d[pre + "hyps_lens"]))
+        np.testing.assert_allclose(td.detach().numpy(), d[pre + "td_score"], rtol=1e-5, atol=1e-5)

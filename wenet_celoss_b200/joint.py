@@ -443,12 +443,12 @@ def fused_joint_rnnt_loss(joint, enc_out: torch.Tensor, pred_out: torch.Tensor,
     V = joint.ffn_out.out_features
     if blank < 0:
         blank = V + blank
-    B, T = enc_out.shape[:2]
+    e = joint.enc_ffn(enc_out)    # [B,T,J]   library GEMM (joint.py:55); may be a broadcast view over B
+    p = joint.pred_ffn(pred_out)  # [B,U1,J]  library GEMM (joint.py:56)
+    B, T = e.shape[:2]
     U1 = pred_out.shape[1]
     # same validation (and messages) as the materialised path
     _validate_shapes((B, T, U1, V), targets, logit_lengths, target_lengths, blank)
-    e = joint.enc_ffn(enc_out)    # [B,T,J]   library GEMM (joint.py:55)
-    p = joint.pred_ffn(pred_out)  # [B,U1,J]  library GEMM (joint.py:56)
     if precision == "auto":
         half = enc_out.dtype != torch.float32 or joint.ffn_out.weight.dtype != torch.float32
         precision = "bf16" if half or torch.is_autocast_enabled("cuda") else "fp32"

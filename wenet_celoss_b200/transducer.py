@@ -172,6 +172,133 @@ def transducer_beam_search(self, speech: torch.Tensor, speech_lengths: torch.Ten
     return out[0] if len(out) == 1 else out
 
 
+def _add_sos_eos_in(hyps, sos: int, eos: int, device) -> torch.Tensor:
+    """``ys_in`` of add_sos_eos (wenet/utils/common.py:122-163): <sos> + tokens, padded with <eos>."""
+    L = max(len(h) for h in hyps) + 1
+    out = torch.full((len(hyps), L), eos, dtype=torch.long)
+    for i, h in enumerate(hyps):
+        out[i, 0] = sos
+        if h:
+            out[i, 1:1 + len(h)] = torch.tensor(h, dtype=torch.long)
+    return out.to(device)
+
+
+@torch.no_grad()
+def transducer_attention_rescoring(self, speech: torch.Tensor, speech_lengths: torch.Tensor,
+                                   beam_size: int, decoding_chunk_size: int = -1,
+                                   num_decoding_left_chunks: int = -1, simulate_streaming: bool = False,
+                                   reverse_weight: float = 0.0, ctc_weight: float = 0.0,
+                                   attn_weight: float = 0.0, transducer_weight: float = 0.0,
+                                   search_ctc_weight: float = 1.0, search_transducer_weight: float = 0.0,
+                                   beam_search_type: str = "transducer"):
+    """``Transducer.transducer_attention_rescoring`` (transducer.py:378-513), same arguments and return
+    ``(best hypothesis, best score)``.
+
+    n-best search on the device (RNN-T or CTC prefix beam search), then one rescoring step:
+    transducer score of every hypothesis through the fused joint + RNN-T loss kernels with ONE encoder
+    projection shared by the beam (the reference ``repeat``s encoder_out beam_size times, :467, and
+    materialises [beam, T, U+1, V] logits), the attention decoder (a library module of the model, called
+    as the reference calls it), and the score combine + argmax in ``b200_attn_rescore`` instead of a
+    ``.cpu().numpy()`` round trip and Python loops (:487-511)."""
+    import ctypes
+
+    from . import _lib
+    from ._lib import i32, ptr
+    from .joint import fused_joint_rnnt_loss as _fused
+
+    assert speech.shape[0] == speech_lengths.shape[0]
+    assert decoding_chunk_size != 0
+    if reverse_weight > 0.0:
+        assert hasattr(self.decoder, "right_decoder")
+    assert speech.shape[0] == 1  # as the reference: attention rescoring is per utterance
+    dev = speech.device
+    _lib.require_cuda(speech, "speech")
+    if beam_search_type == "transducer":
+        encoder_out, encoder_mask = self.encoder(speech, speech_lengths, decoding_chunk_size,
+                                                 num_decoding_left_chunks)
+        lens = encoder_mask.squeeze(1).sum(1)
+        beam = prefix_beam_search_batch(self, encoder_out, lens, beam_size, search_ctc_weight,
+                                        search_transducer_weight)[0]
+        beam_score = [s.score for s in beam]
+        hyps = [list(s.hyp[1:]) for s in beam]
+    elif beam_search_type == "ctc":
+        nbest, encoder_out = self._ctc_prefix_beam_search(
+            speech, speech_lengths, beam_size=beam_size, decoding_chunk_size=decoding_chunk_size,
+            num_decoding_left_chunks=num_decoding_left_chunks, simulate_streaming=simulate_streaming)
+        beam_score = [h[1] for h in nbest]
+        hyps = [list(h[0]) for h in nbest]
+    else:
+        raise ValueError("beam_search_type must be 'transducer' or 'ctc'")
+    assert len(hyps) == beam_size
+    N, T = beam_size, encoder_out.size(1)
+    ignore_id = getattr(self, "ignore_id", IGNORE_ID)
+    Lmax = max(len(h) for h in hyps)
+    hyps_pad = torch.full((N, max(Lmax, 1)), ignore_id, dtype=torch.long)
+    for i, h in enumerate(hyps):
+        if h:
+            hyps_pad[i, :len(h)] = torch.tensor(h, dtype=torch.long)
+    hyps_pad = hyps_pad[:, :Lmax].contiguous().to(dev)
+    hyps_lens = torch.tensor([len(h) for h in hyps], dtype=torch.long, device=dev)
+
+    # 2.1 transducer score: predictor over the n-best, ONE encoder projection for the whole beam
+    td_score = transducer_score_shared(self, encoder_out, hyps_lens, hyps_pad)
+
+    # 2.2 attention decoder (model module; encoder_out broadcast as a stride-0 view, not a copy)
+    enc_rep = encoder_out.expand(N, -1, -1)
+    enc_mask = torch.ones(N, 1, T, dtype=torch.bool, device=dev)
+    ys_in = _add_sos_eos_in(hyps, self.sos, self.eos, dev)
+    r_hyps = [list(reversed(h)) for h in hyps]
+    r_ys_in = _add_sos_eos_in(r_hyps, self.sos, self.eos, dev)
+    decoder_out, r_decoder_out, _ = self.decoder(enc_rep, enc_mask, ys_in, hyps_lens + 1, r_ys_in,
+                                                 reverse_weight)
+    dec = decoder_out.float().contiguous()
+    use_r = reverse_weight > 0.0 and torch.is_tensor(r_decoder_out) and r_decoder_out.dim() == 3
+    rdec = r_decoder_out.float().contiguous() if use_r else None
+    L1, V = dec.size(1), dec.size(2)
+    with torch.cuda.device(dev):
+        scores = torch.empty(N, dtype=torch.float64, device=dev)
+        best = torch.empty(1, dtype=torch.int32, device=dev)
+        bs = torch.tensor(beam_score, dtype=torch.float64, device=dev)
+        _lib.call("b200_attn_rescore", ptr(dec), ptr(rdec), ptr(hyps_pad), ptr(hyps_lens.int().contiguous()),
+                  i32(N), i32(L1), i32(Lmax), i32(V), i32(self.eos), ctypes.c_double(reverse_weight),
+                  ctypes.c_double(attn_weight), ptr(bs), ctypes.c_double(ctc_weight),
+                  ptr(td_score.float().contiguous()), ctypes.c_double(transducer_weight), ptr(scores),
+                  ptr(None), ptr(best), _lib.stream_handle(dev))
+        bi = int(best.item())
+    return hyps[bi], float(scores[bi].item())
+
+
+@torch.no_grad()
+def transducer_score_shared(self, encoder_out: torch.Tensor, hyps_lens: torch.Tensor,
+                            hyps_pad: torch.Tensor) -> torch.Tensor:
+    """``_cal_transducer_score`` (transducer.py:277-302) for N hypotheses of ONE utterance:
+    ``encoder_out`` is ``[1, T, E]`` - the encoder projection runs once and is shared by the beam."""
+    ignore_id = getattr(self, "ignore_id", IGNORE_ID)
+    N, T = hyps_pad.size(0), encoder_out.size(1)
+    hyps_pad_blank = add_blank(hyps_pad, self.blank, ignore_id)
+    predictor_out = self.predictor(hyps_pad_blank)
+    xs_in_lens = torch.full((N,), T, dtype=torch.int32, device=encoder_out.device)
+    rnnt_text, xs32, hl32 = rnnt_targets(hyps_pad, hyps_lens, xs_in_lens, ignore_id)
+    cost = fused_joint_rnnt_loss(_SharedEncJoint(self.joint, N), encoder_out, predictor_out, rnnt_text, xs32,
+                                 hl32, blank=self.blank, reduction="none")
+    return cost * -1
+
+
+class _SharedEncJoint:
+    """The model's joint with ``enc_ffn`` evaluated on the single utterance and broadcast over the
+    n-best: [1,T,E] -> one GEMM -> [N,T,J] view (what fused_joint_rnnt_loss consumes)."""
+
+    def __init__(self, joint, n):
+        self._joint, self._n = joint, n
+        self.pred_ffn, self.ffn_out = joint.pred_ffn, joint.ffn_out
+        for name in ("postjoin_linear", "post_ffn", "activatoin"):
+            if hasattr(joint, name):
+                setattr(self, name, getattr(joint, name))
+
+    def enc_ffn(self, x):
+        return self._joint.enc_ffn(x).expand(self._n, -1, -1)
+
+
 def patch_transducer(model: torch.nn.Module) -> torch.nn.Module:
     """Rebind the hot-path methods of a reference ``Transducer`` instance in place."""
     for attr in ("encoder", "predictor", "joint", "blank"):
@@ -187,4 +314,6 @@ def patch_transducer(model: torch.nn.Module) -> torch.nn.Module:
     model._cal_transducer_score = types.MethodType(transducer_score, model)
     model.greedy_search = types.MethodType(transducer_greedy_search, model)
     model.beam_search = types.MethodType(transducer_beam_search, model)
+    if getattr(model, "decoder", None) is not None and hasattr(model, "sos"):
+        model.transducer_attention_rescoring = types.MethodType(transducer_attention_rescoring, model)
     return model
