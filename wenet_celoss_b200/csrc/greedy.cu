@@ -341,8 +341,9 @@ __global__ void __launch_bounds__(1024) update_kernel(Model M, State S, int roun
   }
 }
 
-#include "greedy_persistent.inc"
 #include "greedy_bias.inc"
+#include "greedy_gate_cluster.inc"
+#include "greedy_persistent.inc"
 
 }  // namespace gs
 }  // namespace b200
