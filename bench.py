@@ -686,7 +686,8 @@ def extra_rows(cfg, dev, pk):
         "symbols_per_frame": sum(len(h) for h in hyps_g) / (B4 * T4),
         "decisions": sum(len(d) for d in dec_g), "decision0_share": n0 / max(1, sum(len(d) for d in dec_g)),
         "workload": "cfg4 shape, context_filter_state='on' (the fork's default greedy): 100 phrase vectors, "
-                    "gate head + predictor bias per predictor call, go-back re-decodes; per-round kernels"}
+                    "gate head + predictor bias per predictor call, go-back re-decodes; one cooperative launch "
+                    "(greedy_persistent_kernel<GATED>, gate chain per flagged utterance on a cluster of 8 CTAs)"}
     del model.context_bias
     with torch.no_grad():
         model.joint.ffn_out.bias[0] += 2.0

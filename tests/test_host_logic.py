@@ -85,3 +85,25 @@ def test_wrappers_refuse_cpu_tensors():
     m = orc.OracleModel(20, 8, 8, 64, 8, 8, 1)
     with pytest.raises(RuntimeError, match="CUDA"):
         pkg.greedy_search_batch(m, torch.randn(1, 4, 8), torch.tensor([4]))
+
+
+def test_cached_host_read_identity_and_version():
+    """Length-validation reads are remembered per tensor OBJECT and version: an in-place update or a new
+    tensor (even one reusing the same storage address) reads again."""
+    from wenet_celoss_b200 import _lib
+    a, b = torch.tensor([3, 4]), torch.tensor([1, 2])
+    calls = []
+
+    def read():
+        calls.append(1)
+        return [int(a.max()), int(b.max())]
+
+    assert _lib.cached_host_read((a, b), read) == [4, 2]
+    assert _lib.cached_host_read((a, b), read) == [4, 2] and len(calls) == 1
+    a.add_(1)
+    assert _lib.cached_host_read((a, b), read) == [5, 2] and len(calls) == 2
+    ptr = a.data_ptr()
+    del a
+    a = torch.tensor([7, 1])  # may land on the freed address: must not hit
+    assert _lib.cached_host_read((a, b), read) == [7, 2] and len(calls) == 3
+    _ = ptr

@@ -157,6 +157,18 @@ def test_bound_between_no_recompute_and_running_max():
     _check(case, expect_nr=False, _max_ctas=3)
 
 
+def test_target_symbol_equal_to_blank():
+    """Labels equal to the blank index: the emit and blank terms of d loss / d logits fall on the same
+    column (torchaudio's if / else-if order, rnnt_loss.cu); both backward variants patch it once."""
+    case = list(_case(3, 26, 9, 700, 64, 512, seed=19, ragged=True))
+    tgt = case[3].clone()
+    tgt[0, 2] = 0
+    tgt[1, 0] = 0
+    tgt[2, 5] = 0
+    case[3] = tgt
+    _check(tuple(case))
+
+
 def test_running_max_epilogue_no_bound():
     """use_bound=False: same inputs as the fast path, results must agree with it and the reference."""
     case = _case(3, 30, 10, 700, 64, 512, seed=16, ragged=True)

@@ -401,45 +401,50 @@ joint_kernel(const __grid_constant__ CUtensorMap w_map, const __grid_constant__ 
 // H[cell - cell0, 0:J] = bf16(tanh(e[b,t,:] + p[b,u,:])) for one chunk of cells: the A operand of
 // the backward joint kernel (read back through TMA while still in L2) and of the dW GEMM.
 // Same arithmetic as the forward builders (tanh.approx.f32, round-to-nearest bf16).
-// Block = (256 / (J/8)) cell rows x J/8 threads of 8 elements; 32-bit index arithmetic only (the host
-// checks cells, B*T*J, B*U1*J < 2^31): the 64-bit divisions of the first version cost more than the
-// tanh.  Two rows per thread and iteration keep 8 independent 16-byte loads in flight.
+// Block = J/8 threads x (256 / (J/8)) frame slots: a thread owns 8 consecutive k of one (b, t) frame, keeps
+// that frame's e values in registers and walks the U1 labels (the fp32 e row was re-read through L1 for
+// every cell before: 0.42 of HBM peak, issue-bound).  Two labels per pass keep four 16-byte p loads in
+// flight; 32-bit index arithmetic only (the host checks cells, B*T*J, B*U1*J < 2^31).  Chunks that do
+// not start / end on a frame boundary are handled by clamping the label range of the edge frames.
 __global__ void __launch_bounds__(256)
 joint_h_kernel(const float* __restrict__ e, const float* __restrict__ p, int T, int U1, int J,
                long long cell0, long long ncells, __nv_bfloat16* __restrict__ H, int ldh) {
   const int g8 = J >> 3;                      // 16-byte groups per row
-  const int rows = blockDim.x / g8;           // cell rows per block and pass
+  const int rows = blockDim.x / g8;           // frames per block and pass
   const int r = threadIdx.x / g8;
   const int k0 = (threadIdx.x - r * g8) << 3;
   if (r >= rows) return;
-  const unsigned n = (unsigned)ncells, c0 = (unsigned)cell0;
-  const unsigned stride = (unsigned)gridDim.x * rows;
-  auto compute = [&](unsigned local, uint4& h) {
-    const unsigned cell = c0 + local;
-    const unsigned bt = cell / (unsigned)U1;
-    const unsigned u = cell - bt * (unsigned)U1;
+  const unsigned c0 = (unsigned)cell0, c1 = (unsigned)(cell0 + ncells);  // cells [c0, c1)
+  const unsigned bt0 = c0 / (unsigned)U1, bt1 = (c1 + U1 - 1) / (unsigned)U1;  // frames touched
+  for (unsigned bt = bt0 + blockIdx.x * rows + r; bt < bt1; bt += gridDim.x * rows) {
     const unsigned b = bt / (unsigned)T;
     const float4* ep = reinterpret_cast<const float4*>(e + (size_t)bt * J + k0);
-    const float4* pp = reinterpret_cast<const float4*>(p + (size_t)(b * U1 + u) * J + k0);
     const float4 e0 = __ldg(ep), e1 = __ldg(ep + 1);
-    const float4 p0 = __ldg(pp), p1 = __ldg(pp + 1);
-    h.x = pack_bf16x2(tanh_approx(e0.x + p0.x), tanh_approx(e0.y + p0.y));
-    h.y = pack_bf16x2(tanh_approx(e0.z + p0.z), tanh_approx(e0.w + p0.w));
-    h.z = pack_bf16x2(tanh_approx(e1.x + p1.x), tanh_approx(e1.y + p1.y));
-    h.w = pack_bf16x2(tanh_approx(e1.z + p1.z), tanh_approx(e1.w + p1.w));
-  };
-  unsigned local = blockIdx.x * rows + r;
-  for (; local + stride < n; local += 2 * stride) {
-    uint4 h0, h1;
-    compute(local, h0);
-    compute(local + stride, h1);
-    *reinterpret_cast<uint4*>(H + (size_t)local * ldh + k0) = h0;
-    *reinterpret_cast<uint4*>(H + (size_t)(local + stride) * ldh + k0) = h1;
-  }
-  if (local < n) {
-    uint4 h0;
-    compute(local, h0);
-    *reinterpret_cast<uint4*>(H + (size_t)local * ldh + k0) = h0;
+    const unsigned first = bt * (unsigned)U1;
+    const int ua = first >= c0 ? 0 : (int)(c0 - first);
+    const int ub = first + U1 <= c1 ? U1 : (int)(c1 - first);
+    const float* pb = p + (size_t)b * U1 * J + k0;
+    __nv_bfloat16* hb = H + ((size_t)first - c0) * ldh + k0;
+    auto one = [&](const float4 p0, const float4 p1) {
+      uint4 h;
+      h.x = pack_bf16x2(tanh_approx(e0.x + p0.x), tanh_approx(e0.y + p0.y));
+      h.y = pack_bf16x2(tanh_approx(e0.z + p0.z), tanh_approx(e0.w + p0.w));
+      h.z = pack_bf16x2(tanh_approx(e1.x + p1.x), tanh_approx(e1.y + p1.y));
+      h.w = pack_bf16x2(tanh_approx(e1.z + p1.z), tanh_approx(e1.w + p1.w));
+      return h;
+    };
+    int u = ua;
+    for (; u + 1 < ub; u += 2) {
+      const float4* pa = reinterpret_cast<const float4*>(pb + (size_t)u * J);
+      const float4* pc = reinterpret_cast<const float4*>(pb + (size_t)(u + 1) * J);
+      const float4 a0 = __ldg(pa), a1 = __ldg(pa + 1), b0 = __ldg(pc), b1 = __ldg(pc + 1);
+      *reinterpret_cast<uint4*>(hb + (ptrdiff_t)u * ldh) = one(a0, a1);
+      *reinterpret_cast<uint4*>(hb + (ptrdiff_t)(u + 1) * ldh) = one(b0, b1);
+    }
+    if (u < ub) {
+      const float4* pa = reinterpret_cast<const float4*>(pb + (size_t)u * J);
+      *reinterpret_cast<uint4*>(hb + (ptrdiff_t)u * ldh) = one(__ldg(pa), __ldg(pa + 1));
+    }
   }
 }
 

@@ -149,7 +149,7 @@ def _fusable(E: int) -> bool:
 
 def _check_lengths(hl, yl, T, Lmax):
     # lengths beyond the tensors would run the trellis kernels out of bounds; torch.nn.CTCLoss raises too
-    mx = torch.stack([hl.max(), yl.max(), -hl.min(), -yl.min()]).tolist()
+    mx = _lib.cached_host_read((hl, yl), lambda: torch.stack([hl.max(), yl.max(), -hl.min(), -yl.min()]).tolist())
     if mx[0] > T or mx[2] > 0:
         raise RuntimeError(f"Expected input_lengths to have value at most {T}, but got value "
                            f"{mx[0] if mx[0] > T else -mx[2]} (while checking arguments for ctc_loss)")

@@ -483,20 +483,11 @@ def _validate_shapes(shape, targets, logit_lengths, target_lengths, blank):
     if not (0 <= blank < V):
         raise RuntimeError("blank must be within [0, logits.shape[-1])")
     # torchaudio's contract (max lengths == tensor sizes) needs the lengths on the host: one small
-    # device-to-host read per NEW pair of length tensors - the result is remembered for the same
-    # (storage, version) so that re-using a batch does not synchronise the stream again
-    key = (logit_lengths.data_ptr(), logit_lengths._version, target_lengths.data_ptr(),
-           target_lengths._version, B)
-    mx = _LEN_CACHE.get(key)
-    if mx is None:
-        mx = torch.stack([logit_lengths.max(), target_lengths.max()]).tolist()
-        if len(_LEN_CACHE) >= 16:
-            _LEN_CACHE.clear()
-        _LEN_CACHE[key] = mx
+    # device-to-host read per NEW pair of length tensors (_lib.cached_host_read)
+    mx = _lib.cached_host_read((logit_lengths, target_lengths),
+                               lambda: torch.stack([logit_lengths.max(), target_lengths.max()]).tolist())
     if mx[0] != T:
         raise RuntimeError("input length mismatch")
     if mx[1] != targets.size(1) or U1 != targets.size(1) + 1:
         raise RuntimeError("output length mismatch")
 
-
-_LEN_CACHE: dict = {}

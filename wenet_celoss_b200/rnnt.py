@@ -58,7 +58,8 @@ def _validate(logits, targets, logit_lengths, target_lengths, blank):
                     ("target_lengths", target_lengths)):
         _lib.require_cuda(t, name)
     # one small D2H read, as torchaudio does for the same two checks
-    mx = torch.stack([logit_lengths.max(), target_lengths.max()]).tolist()
+    mx = _lib.cached_host_read((logit_lengths, target_lengths),
+                               lambda: torch.stack([logit_lengths.max(), target_lengths.max()]).tolist())
     if mx[0] != logits.size(1):
         raise RuntimeError("input length mismatch")
     if mx[1] != targets.size(1) or logits.size(2) != targets.size(1) + 1:
