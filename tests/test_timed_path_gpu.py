@@ -157,6 +157,15 @@ def test_bound_between_no_recompute_and_running_max():
     _check(case, expect_nr=False, _max_ctas=3)
 
 
+@pytest.mark.parametrize("shape", [(2, 9, 0, 300, 32, 256), (3, 1, 4, 300, 32, 512), (1, 130, 1, 129, 32, 256)])
+def test_edge_shapes_both_backward_variants(shape):
+    """No labels at all (U = 0: the lattice is one column of blanks), a single frame, a vocabulary of one
+    tile + 1 class, on the join dims the no-recompute backward covers."""
+    B, T, U, V, E, J = shape
+    case = _case(B, T, U, V, E, J, seed=T + V, ragged=U > 1)
+    _check(case)
+
+
 def test_target_symbol_equal_to_blank():
     """Labels equal to the blank index: the emit and blank terms of d loss / d logits fall on the same
     column (torchaudio's if / else-if order, rnnt_loss.cu); both backward variants patch it once."""

@@ -147,9 +147,11 @@ def _fusable(E: int) -> bool:
     return E in (256, 512)  # tile shapes of csrc/joint_dw.cu / joint_dh.cu
 
 
-def _check_lengths(hl, yl, T, Lmax):
-    # lengths beyond the tensors would run the trellis kernels out of bounds; torch.nn.CTCLoss raises too
-    mx = _lib.cached_host_read((hl, yl), lambda: torch.stack([hl.max(), yl.max(), -hl.min(), -yl.min()]).tolist())
+def _check_lengths(hl, yl, T, Lmax, key=None):
+    # lengths beyond the tensors would run the trellis kernels out of bounds; torch.nn.CTCLoss raises too.
+    # `key`: the caller's own length tensors (hl / yl may be fresh int32 copies of them)
+    mx = _lib.cached_host_read(key or (hl, yl),
+                               lambda: torch.stack([hl.max(), yl.max(), -hl.min(), -yl.min()]).tolist())
     if mx[0] > T or mx[2] > 0:
         raise RuntimeError(f"Expected input_lengths to have value at most {T}, but got value "
                            f"{mx[0] if mx[0] > T else -mx[2]} (while checking arguments for ctc_loss)")
@@ -179,7 +181,7 @@ def ctc_loss(logits: torch.Tensor, ys_pad: torch.Tensor, hlens: torch.Tensor, ys
     ys = ys_pad.to(device=dev, dtype=torch.int64).contiguous()
     hl = hlens.to(device=dev, dtype=torch.int32).contiguous()
     yl = ys_lens.to(device=dev, dtype=torch.int32).contiguous()
-    _check_lengths(hl, yl, logits.size(1), ys.size(1))
+    _check_lengths(hl, yl, logits.size(1), ys.size(1), key=(hlens, ys_lens))
     nll = _CtcLossFn.apply(logits, ys, hl, yl, int(blank))
     if reduction == "sum":
         return nll.sum()
@@ -203,7 +205,7 @@ def _ctc_forward(self, hs_pad: torch.Tensor, hlens: torch.Tensor, ys_pad: torch.
         ys = ys_pad.to(device=dev, dtype=torch.int64).contiguous()
         hl = hlens.to(device=dev, dtype=torch.int32).contiguous()
         yl = ys_lens.to(device=dev, dtype=torch.int32).contiguous()
-        _check_lengths(hl, yl, T, ys.size(1))
+        _check_lengths(hl, yl, T, ys.size(1), key=(hlens, ys_lens))
         nll = _FusedCtcFn.apply(hs, self.ctc_lo.weight, self.ctc_lo.bias, ys, hl, yl, 0)
         return (nll.sum() if reduce else nll) / B
     ys_hat = self.ctc_lo(hs)  # [B,T,V], library GEMM
