@@ -166,6 +166,33 @@ def test_edge_shapes_both_backward_variants(shape):
     _check(case)
 
 
+def test_weighted_costs_negative_and_zero_upstream_gradient():
+    """d loss / d cost_b = w_b with a negative, a zero and a large weight: the per-cell factor of the
+    no-recompute backward (rowscale = w_b * exp(c0)) carries sign and zero; the recompute kernel's
+    'all factors positive' shortcut must not be taken."""
+    from wenet_celoss_b200 import fused_joint_rnnt_loss
+    from wenet_celoss_b200 import joint as jmod
+    case = _case(4, 28, 9, 700, 64, 512, seed=21, ragged=True)
+    joint, enc, pred, tgt, tl, ul = case
+    w = torch.tensor([1.5, -0.75, 0.0, 3.0])
+    j = copy.deepcopy(joint)
+    er, pr = enc.clone().requires_grad_(True), pred.clone().requires_grad_(True)
+    ref = torchaudio.functional.rnnt_loss(orc.joint_logits(er, pr, j), tgt, tl, ul, blank=0, reduction="none")
+    (ref * w).sum().backward()
+    ref_g = {"enc": er.grad, "pred": pr.grad, **{n: p.grad for n, p in j.named_parameters()}}
+    for nr in (None, False):
+        jd = copy.deepcopy(joint).to(DEV)
+        ed, pd = enc.to(DEV).requires_grad_(True), pred.to(DEV).requires_grad_(True)
+        costs = fused_joint_rnnt_loss(jd, ed, pd, tgt.to(DEV), tl.to(DEV), ul.to(DEV), blank=0, reduction="none",
+                                      precision="bf16", _no_recompute=nr)
+        (costs * w.to(DEV)).sum().backward()
+        assert jmod.LAST_BACKWARD_PATH == ("no_recompute" if nr is None else "recompute")
+        g = {"enc": ed.grad.cpu(), "pred": pd.grad.cpu(), **{n: p.grad.cpu() for n, p in jd.named_parameters()}}
+        for k in ref_g:
+            _close(k, g[k], ref_g[k], tol=1e-2)
+        assert torch.count_nonzero(g["enc"][2]) == 0 and torch.count_nonzero(g["pred"][2]) == 0  # w = 0
+
+
 def test_target_symbol_equal_to_blank():
     """Labels equal to the blank index: the emit and blank terms of d loss / d logits fall on the same
     column (torchaudio's if / else-if order, rnnt_loss.cu); both backward variants patch it once."""
