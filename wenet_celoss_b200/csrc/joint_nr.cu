@@ -18,13 +18,11 @@
 namespace b200 {
 namespace nr {
 
-// Block = (256 / (J/8)) cell rows x J/8 threads of 8 elements, 32-bit index arithmetic (cells < 2^31).
+// Hs = bf16(rowscale * H), streaming.  Block = (256 / (J/8)) cell rows x J/8 threads of 8 elements,
+// 32-bit index arithmetic (cells < 2^31).
 __global__ void __launch_bounds__(256)
-joint_rowscale_kernel(const float4* __restrict__ coef, const float* __restrict__ lse,
-                      const float* __restrict__ lp_blank, const float* __restrict__ lp_emit,
-                      const int32_t* __restrict__ targets, int T, int U1, int J, int blank, long long cells,
-                      __nv_bfloat16* __restrict__ Pt, long long ldg, const __nv_bfloat16* __restrict__ H,
-                      long long ldh, __nv_bfloat16* __restrict__ Hs, float* __restrict__ rowscale) {
+joint_rowscale_kernel(const float4* __restrict__ coef, int J, long long cells,
+                      const __nv_bfloat16* __restrict__ H, long long ldh, __nv_bfloat16* __restrict__ Hs) {
   const int g8 = J >> 3;  // 16-byte groups per row
   const int rows = blockDim.x / g8;
   const int r = threadIdx.x / g8;
@@ -45,30 +43,6 @@ joint_rowscale_kernel(const float4* __restrict__ coef, const float* __restrict__
     }
     *reinterpret_cast<uint4*>(Hs + (size_t)cell * ldh + k0) = o;
   };
-  auto patch = [&](unsigned cell, const float4 c, float rs) {
-    rowscale[cell] = rs;
-    if (rs == 0.f) return;
-    const float ls = lse[cell];
-    const bool has_b = c.y != -INFINITY, has_e = c.z != -INFINITY;
-    int y = -1;
-    if (has_e) {
-      const unsigned bt = cell / (unsigned)U1;
-      const unsigned u = cell - bt * (unsigned)U1;
-      const unsigned b = bt / (unsigned)T;
-      y = targets[(size_t)b * (U1 - 1) + u];
-    }
-    // exp(x + (cb - c0)) <= exp(lse): lp + beta_next <= beta (the lattice recursion)
-    if (has_b) {
-      const float xb = lp_blank[cell] + ls;
-      float v = __expf(xb) - __expf(xb + (c.y - c.x));
-      if (y == blank) v -= __expf(xb + (c.z - c.x));
-      Pt[(size_t)cell * ldg + blank] = __float2bfloat16_rn(v);
-    }
-    if (has_e && !(y == blank && has_b)) {
-      const float xe = lp_emit[cell] + ls;
-      Pt[(size_t)cell * ldg + y] = __float2bfloat16_rn(__expf(xe) - __expf(xe + (c.z - c.x)));
-    }
-  };
   unsigned cell = blockIdx.x * rows + r;
   for (; cell + stride < n; cell += 2 * stride) {  // two rows per pass: four 16-byte loads in flight
     const float4 c0 = __ldg(coef + cell), c1 = __ldg(coef + cell + stride);
@@ -78,17 +52,48 @@ joint_rowscale_kernel(const float4* __restrict__ coef, const float* __restrict__
     const float r1 = c1.x == -INFINITY ? 0.f : c1.w * __expf(c1.x);
     scale_row(cell, r0, h0);
     scale_row(cell + stride, r1, h1);
-    if (k0 == 0) {
-      patch(cell, c0, r0);
-      patch(cell + stride, c1, r1);
-    }
   }
   if (cell < n) {
     const float4 c0 = __ldg(coef + cell);
     const uint4 h0 = __ldg(reinterpret_cast<const uint4*>(H + (size_t)cell * ldh + k0));
     const float r0 = c0.x == -INFINITY ? 0.f : c0.w * __expf(c0.x);
     scale_row(cell, r0, h0);
-    if (k0 == 0) patch(cell, c0, r0);
+  }
+}
+
+// one thread per cell: rowscale[c] and the two patched entries of the row of Pt (kept apart from the
+// streaming kernel above: one diverged lane per row cost it a fifth of its bandwidth)
+__global__ void __launch_bounds__(256)
+joint_patch_kernel(const float4* __restrict__ coef, const float* __restrict__ lse,
+                   const float* __restrict__ lp_blank, const float* __restrict__ lp_emit,
+                   const int32_t* __restrict__ targets, int T, int U1, int blank, long long cells,
+                   __nv_bfloat16* __restrict__ Pt, long long ldg, float* __restrict__ rowscale) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= cells) return;
+  const unsigned cell = (unsigned)i;
+  const float4 c = __ldg(coef + cell);
+  const float rs = c.x == -INFINITY ? 0.f : c.w * __expf(c.x);
+  rowscale[cell] = rs;
+  if (rs == 0.f) return;
+  const float ls = lse[cell];
+  const bool has_b = c.y != -INFINITY, has_e = c.z != -INFINITY;
+  int y = -1;
+  if (has_e) {
+    const unsigned bt = cell / (unsigned)U1;
+    const unsigned u = cell - bt * (unsigned)U1;
+    const unsigned b = bt / (unsigned)T;
+    y = targets[(size_t)b * (U1 - 1) + u];
+  }
+  // exp(x + (cb - c0)) <= exp(lse): lp + beta_next <= beta (the lattice recursion)
+  if (has_b) {
+    const float xb = lp_blank[cell] + ls;
+    float v = __expf(xb) - __expf(xb + (c.y - c.x));
+    if (y == blank) v -= __expf(xb + (c.z - c.x));
+    Pt[(size_t)cell * ldg + blank] = __float2bfloat16_rn(v);
+  }
+  if (has_e && !(y == blank && has_b)) {
+    const float xe = lp_emit[cell] + ls;
+    Pt[(size_t)cell * ldg + y] = __float2bfloat16_rn(__expf(xe) - __expf(xe + (c.z - c.x)));
   }
 }
 
@@ -120,10 +125,13 @@ extern "C" int b200_joint_rowscale(const float* coef, const float* lse, const fl
   const int g8 = J / 8, rows = 256 / g8;
   long long blocks = (cells + rows - 1) / rows;
   if (blocks > 16ll * sms) blocks = 16ll * sms;
+  nr::joint_patch_kernel<<<(unsigned)((cells + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const float4*>(coef), lse, lp_blank, lp_emit, targets, T, U1, blank, cells,
+      reinterpret_cast<__nv_bfloat16*>(Pt), ldg, rowscale);
+  B200_CHECK_LAUNCH("joint_patch_kernel");
   nr::joint_rowscale_kernel<<<(int)blocks, rows * g8, 0, (cudaStream_t)stream>>>(
-      reinterpret_cast<const float4*>(coef), lse, lp_blank, lp_emit, targets, T, U1, J, blank, cells,
-      reinterpret_cast<__nv_bfloat16*>(Pt), ldg, reinterpret_cast<const __nv_bfloat16*>(H), ldh,
-      reinterpret_cast<__nv_bfloat16*>(Hs), rowscale);
+      reinterpret_cast<const float4*>(coef), J, cells, reinterpret_cast<const __nv_bfloat16*>(H), ldh,
+      reinterpret_cast<__nv_bfloat16*>(Hs));
   B200_CHECK_LAUNCH("joint_rowscale_kernel");
   return B200_OK;
 }
