@@ -158,7 +158,11 @@ class _FusedJointLossFn(torch.autograd.Function):
                 nr_flag[0][0].copy_(bound * _LOG2E < NR_MAX_LOG2_BOUND, non_blocking=True)
                 nr_event = torch.cuda.Event()
                 nr_event.record(torch.cuda.current_stream(dev))
-                Pt = torch.empty(cells, ldg, dtype=torch.bfloat16, device=dev)
+                try:
+                    Pt = torch.empty(cells, ldg, dtype=torch.bfloat16, device=dev)
+                except torch.cuda.OutOfMemoryError:  # no room for the scratch: recompute path, chunked
+                    nr, Pt = False, None
+            if nr:
                 lat = torch.empty(3, B, T, U1, dtype=torch.float32, device=dev)
                 lse, lpb, lpe = lat.unbind(0)
                 _lib.call("b200_joint_fwd_p", ptr(e32), ptr(p32), ptr(w_bf16), ptr(bias_pad), ptr(targets),
