@@ -457,9 +457,12 @@ class RnntFusedWorkload:
         Hs = torch.empty_like(H_all) if nr else None
         db = torch.zeros(V, device=self.dev)
 
-        def k_fwdp():  # joint_h_kernel + joint_kernel<FWDP>: statistics and Pt = exp(logit) (bf16) into G
+        def k_h():  # H = tanh(e + p) (bf16): the A operand of the forward kernel and of the backward GEMMs
+            _lib.call("b200_joint_h", ptr(e), ptr(p), i32(B), i32(T), i32(U1), i32(J), ptr(H_all), i32(J), st)
+
+        def k_fwdp():  # joint_kernel<FWDP> on the ready H: statistics and Pt = exp(logit) (bf16) into G
             lat = torch.empty(3, B, T, U1, device=self.dev)
-            _lib.call("b200_joint_fwd_p", ptr(e), ptr(p), ptr(w), ptr(bias), ptr(self.targets), ptr(self.tl),
+            _lib.call("b200_joint_fwd_p_h", ptr(e), ptr(p), ptr(w), ptr(bias), ptr(self.targets), ptr(self.tl),
                       ptr(self.ul), i32(B), i32(T), i32(U1), i32(V), i32(J), i32(0), ptr(lat[0]), ptr(lat[1]),
                       ptr(lat[2]), ptr(bound), ptr(H_all), i32(J), ptr(G), i32(ldg), i32(0), st)
             box["lat"] = lat.unbind(0)
@@ -479,11 +482,13 @@ class RnntFusedWorkload:
                       i32(T), i32(U1), i32(V), i32(J), ptr(self.tl), ptr(self.ul), ptr(de), ptr(dp), i32(0), st)
 
         out = {}
+        if nr:
+            k_h()
         (k_fwdp if nr else k_fwd)(); k_lat()
         alpha, beta, costs, doff = box["ab"]
         box["coef"] = rnnt_grad_coef(box["lat"][0], alpha, beta, doff, dy, self.targets, self.tl, self.ul, 0)
         if nr:
-            plan = (("joint_kernel<FWDP> (all cells, with joint_h_kernel)", k_fwdp), ("rnnt_lattice_kernel", k_lat),
+            plan = (("joint_h_kernel", k_h), ("joint_kernel<FWDP> (all cells)", k_fwdp), ("rnnt_lattice_kernel", k_lat),
                     ("joint_rowscale_kernel", k_rowscale), ("joint_dw_kernel (all cells, with d b)", k_dw_db),
                     ("joint_dh_kernel (all cells)", k_dh_scaled))
         else:

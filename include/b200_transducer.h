@@ -177,6 +177,15 @@ int b200_joint_fwd_p(const float* e, const float* p, const void* w_bf16, const f
                      float* lse, float* lp_blank, float* lp_emit, const float* logit_bound,
                      void* H, int ldh, void* Pt, int ldg, int max_ctas, b200_stream_t stream);
 
+/* b200_joint_fwd_p split in its two launches: H = tanh(e + p) alone, and the tensor-core kernel on a ready H */
+int b200_joint_h(const float* e, const float* p, int B, int T, int U1, int J, void* H, int ldh,
+                 b200_stream_t stream);
+int b200_joint_fwd_p_h(const float* e, const float* p, const void* w_bf16, const float* bias_pad,
+                       const int32_t* targets, const int32_t* logit_len, const int32_t* target_len,
+                       int B, int T, int U1, int V, int J, int blank,
+                       float* lse, float* lp_blank, float* lp_emit, const float* logit_bound,
+                       const void* H, int ldh, void* Pt, int ldg, int max_ctas, b200_stream_t stream);
+
 /* d loss / d logits = rowscale[c] * Pt'[c, v]: writes rowscale [B*T*U1] fp32 (= scale * exp(c0) of the
  * coefficients of b200_rnnt_grad_coef), overwrites the blank and target entries of every row of Pt with
  * exp(x) - exp(x + cb - c0) / exp(x) - exp(x + ce - c0) (x from lse + lp_blank / lp_emit), and writes
@@ -319,6 +328,30 @@ int b200_ctc_fixup(const float* lp_ext, const float* alpha, const float* beta,
 /* out[c] += sum_r (G_hi + G_lo)[r, c] (the bias gradient); out must be zeroed first */
 int b200_colsum_split(const void* G_hi, const void* G_lo, long long rows, int N, long long ldg,
                       float* out, b200_stream_t stream);
+
+/* ---- no-recompute backward in fp32 mode (cf. b200_joint_fwd_p / b200_joint_rowscale for bf16) ----
+ * b200_split_gemm_explse: lse [rows] AND Pt = exp(x) as a split pair (p_hi, p_lo [rows, ldp]) from ONE pass
+ * over split operands; logit_bound = the device scalar of b200_joint_logit_bound: with
+ * bound * log2(e) >= 60 the kernel only computes lse (running maximum) and stores nothing.
+ * b200_joint_rowscale_split: rowscale [cells], the blank / target entries of the split Pt replaced by
+ * exp(x) - exp(x + c_b - c_0) (x = the exact fp32 logits xbe of b200_joint_pick), Hs = rowscale * H split again.
+ * b200_colsum_split_w: out[c] += sum_r w[r] (G_hi + G_lo)[r, c].   b200_joint_dh_split_scaled: b200_joint_dh_split
+ * with dH = rowscale[cell] * (G W). */
+int b200_split_gemm_explse(const void* a_hi, const void* a_lo, long long rows, int K, int lda,
+                           const void* b_hi, const void* b_lo, int N, int ldb, const float* bias_pad,
+                           const float* logit_bound, float* lse, void* p_hi, void* p_lo, long long ldp,
+                           int max_ctas, b200_stream_t stream);
+int b200_joint_rowscale_split(const float* coef, const float* xbe, const int32_t* targets, int B, int T,
+                              int U1, int V, int J, int blank, void* P_hi, void* P_lo, long long ldg,
+                              const void* H_hi, const void* H_lo, int ldh, void* Hs_hi, void* Hs_lo,
+                              float* rowscale, b200_stream_t stream);
+int b200_colsum_split_w(const void* G_hi, const void* G_lo, long long rows, int N, long long ldg,
+                        const float* w, float* out, b200_stream_t stream);
+int b200_joint_dh_split_scaled(const void* G_hi, const void* G_lo, int ldg, const void* w_hi,
+                               const void* w_lo, const void* H_hi, const void* H_lo, int ldh,
+                               const float* rowscale, int nb, int T, int U1, int V, int J,
+                               const int32_t* logit_len, const int32_t* target_len, float* de, float* dp,
+                               int max_ctas, b200_stream_t stream);
 
 /* b200_joint_dw / b200_joint_dh on split operands (three products each) */
 int b200_joint_dw_split(const void* G_hi, const void* G_lo, int ldg, const void* H_hi,

@@ -1,5 +1,5 @@
 """Fused step with the no-recompute backward vs the recompute backward, same process, interleaved:
-python scripts/ab_nr.py [cfg3|cfg2] [reps]"""
+python scripts/ab_nr.py [cfg3|cfg2] [reps] [bf16|fp32]"""
 import sys; sys.path.insert(0, '.')
 import torch
 import bench
@@ -7,6 +7,8 @@ from wenet_celoss_b200 import joint as jm
 torch.cuda.set_device(0)
 cfg = dict(bench.CFG2 if (len(sys.argv) > 1 and sys.argv[1] == "cfg2") else bench.CFG3)
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+if len(sys.argv) > 3:
+    cfg["precision"] = sys.argv[3]  # bf16 | fp32
 wl = bench.RnntFusedWorkload(cfg, 0)
 def run(nr, n=10):
     jm.NO_RECOMPUTE = nr

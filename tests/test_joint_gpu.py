@@ -62,13 +62,13 @@ def _reference(joint, enc, pred, tgt, tl, ul, reduction="mean", bf16_operands=Fa
     return loss.detach(), grads
 
 
-def _mine(joint, enc, pred, tgt, tl, ul, reduction="mean", precision="bf16"):
+def _mine(joint, enc, pred, tgt, tl, ul, reduction="mean", precision="bf16", **kw):
     from wenet_celoss_b200 import fused_joint_rnnt_loss
     j = copy.deepcopy(joint).to(DEV)
     enc = enc.to(DEV).requires_grad_(True)
     pred = pred.to(DEV).requires_grad_(True)
     loss = fused_joint_rnnt_loss(j, enc, pred, tgt.to(DEV), tl.to(DEV), ul.to(DEV), blank=0,
-                                 reduction=reduction, precision=precision)
+                                 reduction=reduction, precision=precision, **kw)
     loss.sum().backward()
     grads = {"enc": enc.grad.cpu(), "pred": pred.grad.cpu()}
     grads.update({n: p.grad.cpu() for n, p in j.named_parameters()})

@@ -276,6 +276,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         if (lane == 0) mbar_arrive_cluster(map_to_cta(acc_empty, 0));
         continue;
       }
+      // per-cell factors of the tile's 256 columns -> shared memory (double-buffered over tiles: the
+      // barrier of the next tile orders this tile's reads before the buffer's reuse)
+      auto stage_rowscale = [&](int tile_no) {
+        float* const rs_t = rs_s[tile_no & 1];
+        for (int c = (warp - kEpiWarp0) * 32 + lane; c < kTileN; c += 4 * nacc * 32) {
+          float w = 1.f;
+          if (P.rowscale != nullptr) {
+            const int row = c & 127;
+            const int t = min(tl.t0 + (c >> 7) * TBH + row / UB, P.T - 1);
+            const long long cell = (long long)(tl.b * P.T + t) * P.U1 + min(u0 + row % UB, P.U1 - 1);
+            w = __ldg(P.rowscale + cell);
+          }
+          rs_t[c] = w;
+        }
+        asm volatile("bar.sync 1, %0;" ::"r"(4 * nacc * 32) : "memory");
+        return rs_t;
+      };
       if constexpr (!SPLIT) {
         // column c = 128 * half + UB * f + i: frame f of CTA half `half`, label i of the tile (the order the
         // 4-D TMA box lays the G rows out); chunk ch = columns 16 ch .. 16 ch + 15.  Frames / labels beyond
@@ -303,20 +320,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         uint32_t hreg[16][8];
 #pragma unroll
         for (int ch = 0; ch < kAhead; ++ch) load_chunk(ch, hreg[ch]);
-        // per-cell factors of the tile's 256 columns -> shared memory (double-buffered over tiles: the
-        // barrier of the next tile orders this tile's reads before the buffer's reuse)
-        float* const rs_t = rs_s[nu & 1];
-        for (int c = (warp - kEpiWarp0) * 32 + lane; c < kTileN; c += 4 * nacc * 32) {
-          float w = 1.f;
-          if (P.rowscale != nullptr) {
-            const int row = c & 127;
-            const int t = min(tl.t0 + (c >> 7) * TBH + row / UB, P.T - 1);
-            const long long cell = (long long)(tl.b * P.T + t) * P.U1 + min(u0 + row % UB, P.U1 - 1);
-            w = __ldg(P.rowscale + cell);
-          }
-          rs_t[c] = w;
-        }
-        asm volatile("bar.sync 1, %0;" ::"r"(4 * nacc * 32) : "memory");
+        float* const rs_t = stage_rowscale(nu);
         float dp_acc[UB];
 #pragma unroll
         for (int i = 0; i < UB; ++i) dp_acc[i] = 0.f;
@@ -387,6 +391,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
       float de_run = 0.f;
       uint16_t hbuf[2][16], lbuf[2][16];
       load_h(0, hbuf[0], lbuf[0]);
+      const float* const rs_t = stage_rowscale(nu);
       ptx::mbar_wait(acc_full, (uint32_t)(nu & 1));
       ++nu;
       ptx::tc_fence_after();
@@ -406,7 +411,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
             const int rs = hh * 16 + k;  // row within a pair of chunks; UB divides 32
             float hv = __uint_as_float((uint32_t)h[k] << 16);
             if (Hlj) hv += __uint_as_float((uint32_t)hl[k] << 16);
-            const float z = __uint_as_float(r[k]) * fmaf(-hv, hv, 1.f);
+            const float z = (__uint_as_float(r[k]) * rs_t[ch * 16 + k]) * fmaf(-hv, hv, 1.f);
             dp_acc[rs % UB] += z;
             de_run += z;
             if (rs % UB == UB - 1) {  // last label of a frame: flush d e
@@ -539,7 +544,7 @@ int joint_dh_impl(const void* G, const void* G_lo, int ldg, const void* w, const
                   const void* H_lo, int ldh, const float* rowscale, int nb, int T, int U1, int V, int J,
                   const int32_t* logit_len, const int32_t* target_len, float* de, float* dp, int max_ctas,
                   b200_stream_t stream) {
-  B200_CHECK_ARG(!(rowscale && G_lo), "b200_joint_dh: rowscale is for single-pass operands only");
+
   B200_CHECK_ARG(G && w && H && de && dp, "b200_joint_dh: null pointer");
   B200_CHECK_ARG(nb > 0 && T > 0 && U1 > 0 && V > 0, "b200_joint_dh: bad shape nb=%d T=%d U1=%d V=%d", nb, T,
                  U1, V);
@@ -633,6 +638,17 @@ extern "C" int b200_joint_dh_split(const void* G_hi, const void* G_lo, int ldg, 
                                    float* de, float* dp, int max_ctas, b200_stream_t stream) {
   B200_CHECK_ARG(G_lo && w_lo && H_lo, "b200_joint_dh_split: null pointer");
   return joint_dh_impl(G_hi, G_lo, ldg, w_hi, w_lo, H_hi, H_lo, ldh, nullptr, nb, T, U1, V, J, logit_len,
+                       target_len, de, dp, max_ctas, stream);
+}
+
+// split operands with a per-cell factor (no-recompute backward in fp32 mode)
+extern "C" int b200_joint_dh_split_scaled(const void* G_hi, const void* G_lo, int ldg, const void* w_hi,
+                                          const void* w_lo, const void* H_hi, const void* H_lo, int ldh,
+                                          const float* rowscale, int nb, int T, int U1, int V, int J,
+                                          const int32_t* logit_len, const int32_t* target_len, float* de, float* dp,
+                                          int max_ctas, b200_stream_t stream) {
+  B200_CHECK_ARG(G_lo && w_lo && H_lo && rowscale, "b200_joint_dh_split_scaled: null pointer");
+  return joint_dh_impl(G_hi, G_lo, ldg, w_hi, w_lo, H_hi, H_lo, ldh, rowscale, nb, T, U1, V, J, logit_len,
                        target_len, de, dp, max_ctas, stream);
 }
 

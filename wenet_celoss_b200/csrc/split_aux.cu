@@ -8,7 +8,11 @@
 //   rnnt_fixup_kernel       G[cell, blank] -= scale exp(x_b + cb), G[cell, y] -= scale exp(x_y + ce) on the
 //                           split G written by split_gemm MODE_EXP (the sparse terms of the rnnt_loss gradient)
 //   ctc_fixup_kernel        G[b,t,c] -= scale_b * posterior(c at t) for the blank and every distinct label
-//   colsum_split_kernel     d bias[c] = sum_r (G_hi + G_lo)[r, c]
+//   colsum_split_kernel     d bias[c] = sum_r w[r] (G_hi + G_lo)[r, c]   (w optional)
+//   joint_patch_split_kernel / hs_split_kernel   the no-recompute backward in fp32 mode (cf. joint_nr.cu):
+//                           rowscale[c] = scale exp(c0), the blank / target entries of the split Pt = exp(logit)
+//                           replaced by exp(x) - exp(x + c_b - c_0) (exact fp32 logits from joint_pick_kernel),
+//                           Hs = rowscale * (H_hi + H_lo) split again
 // All of them are small next to the GEMMs (gathered dot products: 2 or L+1 classes per row out of V).
 #include "common.cuh"
 
@@ -206,6 +210,63 @@ rnnt_fixup_kernel(const float4* __restrict__ coef, const float2* __restrict__ xb
   if (y >= 0) split_put(Ghi, Glo, row + y, split_get(Ghi, Glo, row + y) - fe);
 }
 
+// one thread per lattice cell: rowscale and the two patched entries of the split Pt (see joint_nr.cu)
+__global__ void __launch_bounds__(256)
+joint_patch_split_kernel(const float4* __restrict__ coef, const float2* __restrict__ xbe,
+                         const int32_t* __restrict__ targets, int T, int U1, int blank, long long ncells,
+                         __nv_bfloat16* __restrict__ Phi, __nv_bfloat16* __restrict__ Plo, long long ldg,
+                         float* __restrict__ rowscale) {
+  const long long cell = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (cell >= ncells) return;
+  const float4 c = coef[cell];
+  const float rs = c.x == -INFINITY ? 0.f : c.w * expf(c.x);
+  rowscale[cell] = rs;
+  if (rs == 0.f) return;
+  const float2 x = xbe[cell];
+  const bool has_b = c.y != -INFINITY, has_e = c.z != -INFINITY;
+  int y = -1;
+  if (has_e) {
+    const long long bt = cell / U1;
+    const int u = (int)(cell - bt * U1);
+    y = targets[(bt / T) * (U1 - 1) + u];
+  }
+  const long long row = cell * ldg;
+  if (has_b) {
+    float v = expf(x.x) - expf(x.x + (c.y - c.x));
+    if (y == blank) v -= expf(x.x + (c.z - c.x));
+    split_put(Phi, Plo, row + blank, v);
+  }
+  if (has_e && !(y == blank && has_b)) split_put(Phi, Plo, row + y, expf(x.y) - expf(x.y + (c.z - c.x)));
+}
+
+// Hs = rowscale * (H_hi + H_lo), split again; 8 elements per thread
+__global__ void __launch_bounds__(256)
+hs_split_kernel(const float* __restrict__ rowscale, const __nv_bfloat16* __restrict__ Hhi,
+                const __nv_bfloat16* __restrict__ Hlo, int J, long long ncells, int ldh,
+                __nv_bfloat16* __restrict__ Shi, __nv_bfloat16* __restrict__ Slo) {
+  const int g8 = J >> 3;
+  const long long total = ncells * g8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long cell = i / g8;
+    const int k0 = (int)(i - cell * g8) << 3;
+    const float rs = __ldg(rowscale + cell);
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(Hhi + cell * ldh + k0));
+    const uint4 b = __ldg(reinterpret_cast<const uint4*>(Hlo + cell * ldh + k0));
+    const uint32_t* pa = &a.x;
+    const uint32_t* pb = &b.x;
+    __align__(16) __nv_bfloat16 h[8], l[8];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float v0 = (__uint_as_float(pa[k] << 16) + __uint_as_float(pb[k] << 16)) * rs;
+      const float v1 = (__uint_as_float(pa[k] & 0xffff0000u) + __uint_as_float(pb[k] & 0xffff0000u)) * rs;
+      split1(v0, h[2 * k], l[2 * k]);
+      split1(v1, h[2 * k + 1], l[2 * k + 1]);
+    }
+    *reinterpret_cast<uint4*>(Shi + cell * ldh + k0) = *reinterpret_cast<const uint4*>(h);
+    *reinterpret_cast<uint4*>(Slo + cell * ldh + k0) = *reinterpret_cast<const uint4*>(l);
+  }
+}
+
 // one warp per (b, t): posteriors of the extended states, merged per class through the leader table
 __global__ void __launch_bounds__(256)
 ctc_fixup_kernel(const float* __restrict__ lp_ext, const float* __restrict__ alpha, const float* __restrict__ beta,
@@ -255,7 +316,7 @@ ctc_fixup_kernel(const float* __restrict__ lp_ext, const float* __restrict__ alp
 // grid (column blocks of 256, row slabs); thread = one column pair over a slab of rows
 __global__ void __launch_bounds__(128)
 colsum_split_kernel(const __nv_bfloat16* __restrict__ Ghi, const __nv_bfloat16* __restrict__ Glo, long long rows, int N,
-                    long long ldg, long long rows_per_slab, float* __restrict__ out) {
+                    long long ldg, long long rows_per_slab, const float* __restrict__ w, float* __restrict__ out) {
   const int c = (blockIdx.x * 128 + threadIdx.x) * 2;
   if (c >= N) return;
   const long long r0 = blockIdx.y * rows_per_slab;
@@ -266,12 +327,13 @@ colsum_split_kernel(const __nv_bfloat16* __restrict__ Ghi, const __nv_bfloat16* 
     const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(Ghi + r * ldg + c);
     float2 v = __bfloat1622float2(h);
     if (Glo) {
-      const float2 w = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(Glo + r * ldg + c));
-      v.x += w.x;
-      v.y += w.y;
+      const float2 lo2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(Glo + r * ldg + c));
+      v.x += lo2.x;
+      v.y += lo2.y;
     }
-    s0 += v.x;
-    s1 += v.y;
+    const float wr = w ? __ldg(w + r) : 1.f;
+    s0 = fmaf(v.x, wr, s0);
+    s1 = fmaf(v.y, wr, s1);
   }
   atomicAdd(out + c, s0);
   if (pair_ok) atomicAdd(out + c + 1, s1);
@@ -373,8 +435,8 @@ extern "C" int b200_ctc_fixup(const float* lp_ext, const float* alpha, const flo
   return B200_OK;
 }
 
-extern "C" int b200_colsum_split(const void* G_hi, const void* G_lo, long long rows, int N, long long ldg, float* out,
-                                 b200_stream_t stream) {
+static int colsum_split_impl(const void* G_hi, const void* G_lo, long long rows, int N, long long ldg, const float* w,
+                             float* out, b200_stream_t stream) {
   B200_CHECK_ARG(G_hi && out && rows > 0 && N > 0 && ldg >= N && ldg % 2 == 0, "b200_colsum_split: bad arguments");
   const int cblocks = (N + 255) / 256;
   int slabs = (148 * 8 + cblocks - 1) / cblocks;
@@ -383,7 +445,44 @@ extern "C" int b200_colsum_split(const void* G_hi, const void* G_lo, long long r
   dim3 grid(cblocks, (unsigned)((rows + per - 1) / per));
   sa::colsum_split_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(reinterpret_cast<const __nv_bfloat16*>(G_hi),
                                                                   reinterpret_cast<const __nv_bfloat16*>(G_lo), rows, N,
-                                                                  ldg, per, out);
+                                                                  ldg, per, w, out);
   B200_CHECK_LAUNCH("colsum_split_kernel");
+  return B200_OK;
+}
+
+extern "C" int b200_colsum_split(const void* G_hi, const void* G_lo, long long rows, int N, long long ldg, float* out,
+                                 b200_stream_t stream) {
+  return colsum_split_impl(G_hi, G_lo, rows, N, ldg, nullptr, out, stream);
+}
+
+// out[c] += sum_r w[r] (G_hi + G_lo)[r, c]: d bias of the no-recompute backward (w = rowscale, G = Pt')
+extern "C" int b200_colsum_split_w(const void* G_hi, const void* G_lo, long long rows, int N, long long ldg,
+                                   const float* w, float* out, b200_stream_t stream) {
+  B200_CHECK_ARG(w, "b200_colsum_split_w: null weights");
+  return colsum_split_impl(G_hi, G_lo, rows, N, ldg, w, out, stream);
+}
+
+// fp32-mode twin of b200_joint_rowscale (joint_nr.cu): rowscale, the patched entries of the split Pt from the
+// exact logits xbe of b200_joint_pick, Hs = rowscale * H split again
+extern "C" int b200_joint_rowscale_split(const float* coef, const float* xbe, const int32_t* targets, int B, int T,
+                                         int U1, int V, int J, int blank, void* P_hi, void* P_lo, long long ldg,
+                                         const void* H_hi, const void* H_lo, int ldh, void* Hs_hi, void* Hs_lo,
+                                         float* rowscale, b200_stream_t stream) {
+  B200_CHECK_ARG(coef && xbe && P_hi && P_lo && H_hi && H_lo && Hs_hi && Hs_lo && rowscale && (U1 == 1 || targets),
+                 "b200_joint_rowscale_split: null pointer");
+  B200_CHECK_ARG(B > 0 && T > 0 && U1 > 0 && blank >= 0 && blank < V && ldg >= V && J % 8 == 0 && ldh >= J && ldh % 8 == 0,
+                 "b200_joint_rowscale_split: bad arguments");
+  B200_CHECK_ARG((((uintptr_t)coef | (uintptr_t)H_hi | (uintptr_t)H_lo | (uintptr_t)Hs_hi | (uintptr_t)Hs_lo) & 15) == 0 &&
+                     ((uintptr_t)xbe & 7) == 0,
+                 "b200_joint_rowscale_split: misaligned pointer");
+  const long long ncells = (long long)B * T * U1;
+  sa::joint_patch_split_kernel<<<(unsigned)((ncells + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const float4*>(coef), reinterpret_cast<const float2*>(xbe), targets, T, U1, blank, ncells,
+      reinterpret_cast<__nv_bfloat16*>(P_hi), reinterpret_cast<__nv_bfloat16*>(P_lo), ldg, rowscale);
+  B200_CHECK_LAUNCH("joint_patch_split_kernel");
+  sa::hs_split_kernel<<<grid_for(ncells * (J / 8), 256, 148 * 16), 256, 0, (cudaStream_t)stream>>>(
+      rowscale, reinterpret_cast<const __nv_bfloat16*>(H_hi), reinterpret_cast<const __nv_bfloat16*>(H_lo), J, ncells, ldh,
+      reinterpret_cast<__nv_bfloat16*>(Hs_hi), reinterpret_cast<__nv_bfloat16*>(Hs_lo));
+  B200_CHECK_LAUNCH("hs_split_kernel");
   return B200_OK;
 }

@@ -18,6 +18,11 @@
 //               split backward GEMMs), coef = {c0, -, -, scale} per row; the sparse "- posterior"
 //               terms of the RNN-T / CTC gradients are applied afterwards by a fix-up kernel
 //   MODE_LSM    out[r, c] = x[r, c] - lse[r] in fp32                   (CTC.log_softmax)
+//   MODE_EXPLSE the training forward of the NO-RECOMPUTE backward (wenet_celoss_b200/joint.py, fp32 mode):
+//               Pt[r, c] = exp(x[r, c]) written SPLIT and lse[r] from the same pass.  exp without a
+//               maximum needs bounded logits: the kernel reads the device scalar `logit_bound` and, when
+//               bound * log2(e) >= 60, degrades to MODE_LSE (nothing stored) - the host applies the
+//               same test to the same scalar when it picks the backward variant
 // Roofline: tensor pipe; algorithmic flops per launch = 2 * rows * K * N (x3 issued in split mode).
 #include <cuda.h>
 
@@ -44,7 +49,8 @@ constexpr int kXchgBytes = 128 * 8;
 constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + kBiasBytes + kXchgBytes + 256;
 static_assert(kSmemBytes <= 232448, "shared memory budget");
 
-enum { MODE_LSE = 0, MODE_EXP = 1, MODE_LSM = 2 };
+enum { MODE_LSE = 0, MODE_EXP = 1, MODE_LSM = 2, MODE_EXPLSE = 3 };
+constexpr float kNrMaxLog2Bound = 60.f;  // = jf::kNrMaxLog2Bound (joint_fused.cu)
 
 struct Params {
   long long rows;
@@ -52,6 +58,7 @@ struct Params {
   const float* bias;   // [ceil(N/256)*256] natural units
   float* lse;          // MODE_LSE out / MODE_LSM in, natural log
   const float4* coef;  // MODE_EXP: {c0, -, -, scale} per row
+  const float* logit_bound;  // MODE_EXPLSE: device scalar max_v(|W_v|_1 + |b_v|)
 };
 
 struct Bars {
@@ -197,10 +204,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
       return col < P.N ? __ldg(P.bias + col) * kLog2e : -INFINITY;
     };
     float bnext = bias_at(0, 0);
+    constexpr bool kStats = MODE == MODE_LSE || MODE == MODE_EXPLSE;
+    const bool nr_ok = MODE == MODE_EXPLSE && P.logit_bound != nullptr &&
+                       __ldg(P.logit_bound) * kLog2e < kNrMaxLog2Bound;
+    const bool stores = MODE == MODE_EXP || MODE == MODE_LSM || nr_ok;
     for (int mt = pair_id; mt < mtiles; mt += npairs) {
       const long long row = (long long)mt * 256 + rank * 128 + rrow;
       const bool in_range = row < P.rows;
-      float m2 = kNegBig, ssum = 0.f;         // MODE_LSE
+      float m2 = nr_ok ? 0.f : kNegBig, ssum = 0.f;  // MODE_LSE / MODE_EXPLSE
       float c0 = -INFINITY, scale = 0.f;      // MODE_EXP (log2 domain) / MODE_LSM (c0 = -lse2)
       if (MODE == MODE_EXP && in_range) {
         const float4 c = __ldg(P.coef + row);
@@ -230,7 +241,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
             }
             bnext = bias_at(nn, cc);
           }
-          if (MODE != MODE_LSE) {  // the previous chunk's store must have drained the staging tile
+          if (stores) {  // the previous chunk's store must have drained the staging tile
             if (lane == 0) ptx::bulk_wait_group_read0();
             __syncwarp();
           }
@@ -251,7 +262,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
             t[4 * i + 3] = fmaf(__uint_as_float(r[4 * i + 3]), kLog2e, bv.w);
           }
           const int col0 = n * kTileN + half * 128 + c * 32;
-          if (MODE == MODE_LSE) {
+          if (kStats && !nr_ok) {
             float cm[4] = {t[0], t[1], t[2], t[3]};
 #pragma unroll
             for (int i = 4; i < 32; ++i) cm[i & 3] = fmaxf(cm[i & 3], t[i]);
@@ -261,8 +272,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
             for (int i = 0; i < 32; ++i) a4[i & 3] += ex2_approx(t[i] - mn);
             ssum = ssum * ex2_approx(m2 - mn) + ((a4[0] + a4[1]) + (a4[2] + a4[3]));
             m2 = mn;
-          } else if (MODE == MODE_EXP) {
-            if (pos) {
+          } else if (MODE == MODE_EXP || MODE == MODE_EXPLSE) {
+            if (MODE == MODE_EXPLSE) {  // Pt = 2^t (bounded logits), summed for lse on the way
+              float a4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                t[i] = ex2_approx(t[i]);
+                a4[i & 3] += t[i];
+              }
+              ssum += (a4[0] + a4[1]) + (a4[2] + a4[3]);
+            } else if (pos) {
 #pragma unroll
               for (int i = 0; i < 32; ++i) t[i] = ex2_approx(t[i] + c0s);
             } else {
@@ -317,7 +336,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         acc ^= 1;
         if (acc == 0) acc_ph ^= 1;
       }
-      if (MODE == MODE_LSE) {
+      if (kStats) {
         // the two column halves of a row sit in two warps: half 1 hands (m2, ssum) to half 0
         // (named barriers 1 + q: data ready, 5 + q: slot free again; 64 threads each)
         if (half == 1) xchg[rrow] = make_float2(m2, ssum);
@@ -331,7 +350,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         asm volatile("bar.sync %0, 64;" ::"r"(5 + q) : "memory");
       }
     }
-    if (MODE != MODE_LSE && lane == 0) ptx::bulk_wait_group0();
+    if (stores && lane == 0) ptx::bulk_wait_group0();
   }
 
   ptx::tc_fence_before();
@@ -431,6 +450,17 @@ int sg_run(int mode, const void* a_hi, const void* a_lo, long long rows, int K, 
   P.lse = lse;
   P.coef = reinterpret_cast<const float4*>(coef);
   cudaStream_t st = (cudaStream_t)stream;
+  if (mode == sg::MODE_EXPLSE) {
+    // `coef` carries the logit-bound scalar in this mode
+    P.coef = nullptr;
+    P.logit_bound = coef;
+    B200_CHECK_ARG(lse && coef && o_hi && (!split || o_lo), "b200_split_gemm_explse: null pointer");
+    B200_CHECK_ARG(ldo >= N && ldo % 8 == 0 && (((uintptr_t)o_hi | (uintptr_t)o_lo) & 15) == 0,
+                   "b200_split_gemm_explse: Pt must be 16-byte aligned, ldo=%lld >= N and a multiple of 8", ldo);
+    if (int rc = sg_map(&m[4], o_hi, bf, 2, rows, N, ldo * 2, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B)) return rc;
+    if (int rc = sg_map(&m[5], split ? o_lo : o_hi, bf, 2, rows, N, ldo * 2, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B)) return rc;
+    return split ? sg_launch<sg::MODE_EXPLSE, 3>(m, P, max_ctas, st) : sg_launch<sg::MODE_EXPLSE, 1>(m, P, max_ctas, st);
+  }
   if (mode == sg::MODE_LSE) {
     B200_CHECK_ARG(lse, "b200_split_gemm_lse: null lse");
     return split ? sg_launch<sg::MODE_LSE, 3>(m, P, max_ctas, st) : sg_launch<sg::MODE_LSE, 1>(m, P, max_ctas, st);
@@ -467,6 +497,15 @@ extern "C" int b200_split_gemm_exp(const void* a_hi, const void* a_lo, long long
                                    b200_stream_t stream) {
   return sg_run(sg::MODE_EXP, a_hi, a_lo, rows, K, lda, b_hi, b_lo, N, ldb, bias_pad, nullptr, coef, g_hi, g_lo, ldg,
                 max_ctas, stream);
+}
+
+// lse AND Pt = exp(x) (split) from one pass: the training forward of the no-recompute backward, fp32 mode
+extern "C" int b200_split_gemm_explse(const void* a_hi, const void* a_lo, long long rows, int K, int lda,
+                                      const void* b_hi, const void* b_lo, int N, int ldb, const float* bias_pad,
+                                      const float* logit_bound, float* lse, void* p_hi, void* p_lo, long long ldp,
+                                      int max_ctas, b200_stream_t stream) {
+  return sg_run(sg::MODE_EXPLSE, a_hi, a_lo, rows, K, lda, b_hi, b_lo, N, ldb, bias_pad, lse, logit_bound, p_hi, p_lo,
+                ldp, max_ctas, stream);
 }
 
 extern "C" int b200_split_gemm_lsm(const void* a_hi, const void* a_lo, long long rows, int K, int lda,

@@ -311,7 +311,8 @@ class _FusedJointLossFp32Fn(torch.autograd.Function):
 
     @staticmethod
     @custom_fwd(device_type="cuda", cast_inputs=torch.float32)
-    def forward(ctx, e, p, w_out, b_out, targets, logit_lengths, target_lengths, blank, max_ctas=0):
+    def forward(ctx, e, p, w_out, b_out, targets, logit_lengths, target_lengths, blank, max_ctas=0,
+                no_recompute=None):
         dev = e.device
         with torch.cuda.device(dev):
             st = _lib.stream_handle(dev)
@@ -331,15 +332,43 @@ class _FusedJointLossFp32Fn(torch.autograd.Function):
                       ptr(H_lo), i32(J), st)
             lat = torch.zeros(3, B, T, U1, dtype=torch.float32, device=dev)
             lse, lpb, lpe = lat.unbind(0)
-            _lib.call("b200_split_gemm_lse", ptr(H_hi), ptr(H_lo), _i64(ncells), i32(J), i32(J), ptr(w_hi),
-                      ptr(w_lo), i32(V), i32(J), ptr(bias_pad), ptr(lse), i32(max_ctas), st)
+            # no-recompute backward (see _FusedJointLossFn): the forward GEMM also keeps exp(logit) as a
+            # split pair when the scratch fits and the logit bound is small (decided on the device)
+            ldg = (V + 15) // 16 * 16
+            nr = NO_RECOMPUTE if no_recompute is None else bool(no_recompute)
+            nr = (nr and any(ctx.needs_input_grad[:4]) and J in (256, 512)
+                  and 2 * ncells * ldg * 2 <= 2 * SCRATCH_BYTES)
+            P_hi = P_lo = nr_flag = nr_event = None
+            if nr:
+                bound = joint_logit_bound(w_hi, bias_pad, V)  # of the bf16 head: within 2^-8 of the fp32 bound
+                nr_flag = _flag_slot()
+                nr_flag[0][0].copy_(bound * _LOG2E < NR_MAX_LOG2_BOUND - 1.0, non_blocking=True)
+                nr_event = torch.cuda.Event()
+                nr_event.record(torch.cuda.current_stream(dev))
+                try:
+                    P_hi = torch.empty(ncells, ldg, dtype=torch.bfloat16, device=dev)
+                    P_lo = torch.empty_like(P_hi)
+                except torch.cuda.OutOfMemoryError:
+                    nr, P_hi, P_lo = False, None, None
+            if nr:
+                _lib.call("b200_split_gemm_explse", ptr(H_hi), ptr(H_lo), _i64(ncells), i32(J), i32(J), ptr(w_hi),
+                          ptr(w_lo), i32(V), i32(J), ptr(bias_pad), ptr(bound), ptr(lse), ptr(P_hi), ptr(P_lo),
+                          _i64(ldg), i32(max_ctas), st)
+            else:
+                _lib.call("b200_split_gemm_lse", ptr(H_hi), ptr(H_lo), _i64(ncells), i32(J), i32(J), ptr(w_hi),
+                          ptr(w_lo), i32(V), i32(J), ptr(bias_pad), ptr(lse), i32(max_ctas), st)
             xbe = torch.zeros(B, T, U1, 2, dtype=torch.float32, device=dev)
             _lib.call("b200_joint_pick", ptr(e32), ptr(p32), ptr(w32), ptr(b32), ptr(targets),
                       ptr(logit_lengths), ptr(target_lengths), i32(B), i32(T), i32(U1), i32(V), i32(J),
                       i32(blank), ptr(lse), ptr(lpb), ptr(lpe), ptr(xbe), st)
             alpha, beta, costs, diag_off = rnnt_lattice(lpb, lpe, logit_lengths, target_lengths)
-        ctx.save_for_backward(w32, w_hi, w_lo, bias_pad, targets, logit_lengths, target_lengths, lse, alpha,
-                              beta, diag_off, H_hi, H_lo, xbe)
+        if nr:
+            ctx.save_for_backward(w32, w_hi, w_lo, bias_pad, targets, logit_lengths, target_lengths, lse, alpha,
+                                  beta, diag_off, H_hi, H_lo, xbe, P_hi, P_lo)
+        else:
+            ctx.save_for_backward(w32, w_hi, w_lo, bias_pad, targets, logit_lengths, target_lengths, lse, alpha,
+                                  beta, diag_off, H_hi, H_lo, xbe)
+        ctx.nr, ctx.nr_flag, ctx.nr_event = nr, nr_flag, nr_event
         ctx.shape = (B, T, U1, V, J)
         ctx.blank = blank
         ctx.max_ctas = max_ctas
@@ -349,8 +378,22 @@ class _FusedJointLossFp32Fn(torch.autograd.Function):
     @staticmethod
     @custom_bwd(device_type="cuda")
     def backward(ctx, dy):
+        global LAST_BACKWARD_PATH
+        if ctx.nr:
+            ctx.nr_event.synchronize()
+            slot, gen = ctx.nr_flag
+            if slot[1] == gen:
+                take_nr = bool(slot[0][0])
+            else:
+                w_hi_, bias_pad_ = ctx.saved_tensors[1], ctx.saved_tensors[3]
+                take_nr = float(joint_logit_bound(w_hi_, bias_pad_, w_hi_.shape[0]).item()) * _LOG2E \
+                    < NR_MAX_LOG2_BOUND - 1.0
+            if take_nr:
+                LAST_BACKWARD_PATH = "no_recompute"
+                return _FusedJointLossFp32Fn._backward_nr(ctx, dy)
+        LAST_BACKWARD_PATH = "recompute"
         (w32, w_hi, w_lo, bias_pad, targets, logit_lengths, target_lengths, lse, alpha, beta, diag_off,
-         H_hi_all, H_lo_all, xbe) = ctx.saved_tensors
+         H_hi_all, H_lo_all, xbe) = ctx.saved_tensors[:14]
         B, T, U1, V, J = ctx.shape
         dev = w32.device
         blank = ctx.blank
@@ -401,7 +444,43 @@ class _FusedJointLossFp32Fn(torch.autograd.Function):
                     dp[b0:b1] = dz.sum(1)
                     del Gf, Hf, dz
         dt_e, dt_p, dt_w, dt_b = ctx.in_dtypes
-        return (de.to(dt_e), dp.to(dt_p), dW.to(dt_w), db.to(dt_b), None, None, None, None, None)
+        return (de.to(dt_e), dp.to(dt_p), dW.to(dt_w), db.to(dt_b), None, None, None, None, None, None)
+
+    @staticmethod
+    def _backward_nr(ctx, dy):
+        """G = rowscale * Pt' on split operands: no second logits GEMM (9 tensor-core products per step
+        instead of 12)."""
+        (w32, w_hi, w_lo, bias_pad, targets, logit_lengths, target_lengths, lse, alpha, beta, diag_off,
+         H_hi, H_lo, xbe, P_hi, P_lo) = ctx.saved_tensors
+        B, T, U1, V, J = ctx.shape
+        dev = w32.device
+        mc = ctx.max_ctas
+        ncells = B * T * U1
+        ldg = P_hi.stride(0)
+        with torch.cuda.device(dev):
+            st = _lib.stream_handle(dev)
+            dyf = dy.detach().to(torch.float32).contiguous()
+            coef = rnnt_grad_coef(lse, alpha, beta, diag_off, dyf, targets, logit_lengths,
+                                  target_lengths, ctx.blank)
+            rowscale = torch.empty(ncells, dtype=torch.float32, device=dev)
+            Hs_hi = torch.empty_like(H_hi)
+            Hs_lo = torch.empty_like(H_lo)
+            _lib.call("b200_joint_rowscale_split", ptr(coef), ptr(xbe), ptr(targets), i32(B), i32(T), i32(U1),
+                      i32(V), i32(J), i32(ctx.blank), ptr(P_hi), ptr(P_lo), _i64(ldg), ptr(H_hi), ptr(H_lo), i32(J),
+                      ptr(Hs_hi), ptr(Hs_lo), ptr(rowscale), st)
+            dW = torch.zeros(V, J, dtype=torch.float32, device=dev)
+            db = torch.zeros(V, dtype=torch.float32, device=dev)
+            de = torch.zeros(B, T, J, dtype=torch.float32, device=dev)
+            dp = torch.zeros(B, U1, J, dtype=torch.float32, device=dev)
+            _lib.call("b200_colsum_split_w", ptr(P_hi), ptr(P_lo), _i64(ncells), i32(V), _i64(ldg), ptr(rowscale),
+                      ptr(db), st)
+            _lib.call("b200_joint_dw_split", ptr(P_hi), ptr(P_lo), i32(ldg), ptr(Hs_hi), ptr(Hs_lo), i32(J),
+                      _i64(ncells), i32(V), i32(J), ptr(dW), i32(mc), st)
+            _lib.call("b200_joint_dh_split_scaled", ptr(P_hi), ptr(P_lo), i32(ldg), ptr(w_hi), ptr(w_lo), ptr(H_hi),
+                      ptr(H_lo), i32(J), ptr(rowscale), i32(B), i32(T), i32(U1), i32(V), i32(J),
+                      ptr(logit_lengths), ptr(target_lengths), ptr(de), ptr(dp), i32(mc), st)
+        dt_e, dt_p, dt_w, dt_b = ctx.in_dtypes
+        return (de.to(dt_e), dp.to(dt_p), dW.to(dt_w), db.to(dt_b), None, None, None, None, None, None)
 
 
 def _check_joint_module(joint) -> None:
@@ -458,7 +537,8 @@ def fused_joint_rnnt_loss(joint, enc_out: torch.Tensor, pred_out: torch.Tensor,
         precision = "bf16" if half or torch.is_autocast_enabled("cuda") else "fp32"
     if precision == "fp32":
         costs = _FusedJointLossFp32Fn.apply(e, p, joint.ffn_out.weight, joint.ffn_out.bias, targets,
-                                            logit_lengths, target_lengths, int(blank), int(_max_ctas))
+                                            logit_lengths, target_lengths, int(blank), int(_max_ctas),
+                                            _no_recompute)
     else:
         costs = _FusedJointLossFn.apply(e, p, joint.ffn_out.weight, joint.ffn_out.bias, targets,
                                         logit_lengths, target_lengths, int(blank), int(_max_ctas),
