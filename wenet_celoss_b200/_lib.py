@@ -114,3 +114,22 @@ def cached_host_read(tensors, compute):
         del _HOST_READS[0]
     _HOST_READS.append((tuple(weakref.ref(t) for t in tensors), tuple(t._version for t in tensors), result))
     return result
+
+
+_CONVERTED: list = []  # [(weak reference, version, device, dtype, converted tensor)]
+
+
+def cached_convert(t, device, dtype):
+    """``t.to(device, dtype).contiguous()`` - remembered per tensor object and version when it needs a copy
+    (length tensors given as int64 are converted to the kernels' int32 once per batch, not once per call)."""
+    import weakref
+    if t.device == device and t.dtype == dtype and t.is_contiguous():
+        return t
+    for ref, ver, dev, dt, out in reversed(_CONVERTED):
+        if ref() is t and t._version == ver and dev == device and dt == dtype:
+            return out
+    out = t.to(device=device, dtype=dtype).contiguous()
+    if len(_CONVERTED) >= 8:
+        del _CONVERTED[0]
+    _CONVERTED.append((weakref.ref(t), t._version, device, dtype, out))
+    return out

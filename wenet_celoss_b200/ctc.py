@@ -178,9 +178,9 @@ def ctc_loss(logits: torch.Tensor, ys_pad: torch.Tensor, hlens: torch.Tensor, ys
         raise RuntimeError("batch dimension mismatch between logits, ys_pad, hlens and ys_lens")
     dev = logits.device
     logits = logits.contiguous()
-    ys = ys_pad.to(device=dev, dtype=torch.int64).contiguous()
-    hl = hlens.to(device=dev, dtype=torch.int32).contiguous()
-    yl = ys_lens.to(device=dev, dtype=torch.int32).contiguous()
+    ys = _lib.cached_convert(ys_pad, dev, torch.int64)
+    hl = _lib.cached_convert(hlens, dev, torch.int32)
+    yl = _lib.cached_convert(ys_lens, dev, torch.int32)
     _check_lengths(hl, yl, logits.size(1), ys.size(1), key=(hlens, ys_lens))
     nll = _CtcLossFn.apply(logits, ys, hl, yl, int(blank))
     if reduction == "sum":
@@ -202,9 +202,9 @@ def _ctc_forward(self, hs_pad: torch.Tensor, hlens: torch.Tensor, ys_pad: torch.
         if ys_pad.dim() != 2 or ys_pad.size(0) != B or hlens.numel() != B or ys_lens.numel() != B:
             raise RuntimeError("batch dimension mismatch between hs_pad, ys_pad, hlens and ys_lens")
         dev = hs.device
-        ys = ys_pad.to(device=dev, dtype=torch.int64).contiguous()
-        hl = hlens.to(device=dev, dtype=torch.int32).contiguous()
-        yl = ys_lens.to(device=dev, dtype=torch.int32).contiguous()
+        ys = _lib.cached_convert(ys_pad, dev, torch.int64)
+        hl = _lib.cached_convert(hlens, dev, torch.int32)
+        yl = _lib.cached_convert(ys_lens, dev, torch.int32)
         _check_lengths(hl, yl, T, ys.size(1), key=(hlens, ys_lens))
         nll = _FusedCtcFn.apply(hs, self.ctc_lo.weight, self.ctc_lo.bias, ys, hl, yl, 0)
         return (nll.sum() if reduce else nll) / B
