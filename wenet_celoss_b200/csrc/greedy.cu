@@ -81,6 +81,7 @@ __global__ void init_kernel(State S, int blank, int L, int H) {
     S.counters[1] = 0;
     S.counters[2] = 0;
     S.counters[3] = 0;
+    S.counters[6] = 0;  // arrival counter of the persistent kernel's grid barrier
   }
   if (b >= S.B) return;
   S.t[b] = 0;
@@ -344,6 +345,7 @@ __global__ void __launch_bounds__(1024) update_kernel(Model M, State S, int roun
 #include "greedy_bias.inc"
 #include "greedy_gate_cluster.inc"
 #include "greedy_persistent.inc"
+#include "greedy_replicated.inc"
 
 }  // namespace gs
 }  // namespace b200
