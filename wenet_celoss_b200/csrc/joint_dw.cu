@@ -53,7 +53,6 @@ struct Params {
   float* dW;          // [V, J] fp32, accumulated
   const float* rowscale;  // optional [n]: weights of the column sums below
   float* db;          // optional [V] fp32, accumulated: sum over cells of rowscale[c] * G[c, v]
-  int dbg;            // experiment switches (B200_DW_MODE)
 };
 __device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr)
@@ -268,15 +267,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
           if (rank == 0) {
             ptx::mbar_wait(full_bar(s), ph);
             if (cw == 0 && lane == 0) mbar_arrive_cluster_relaxed(map_to_cta(lfull_bar(s), 1));
-          } else if (P.dbg & 8) {
-            ptx::mbar_wait(lfull_bar(s), ph);
           } else {
             mbar_wait_cluster_acq(lfull_bar(s), ph);
-          }
-          if (P.dbg & 4) {
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(csdone_bar(s));
-            continue;
           }
           const uint32_t a = smem_base + (uint32_t)s * sbytes + box * kBoxBytes + half * 32 * 128 + (lane & 3) * 4;
           const int ch = lane >> 2;
@@ -431,7 +423,6 @@ static int joint_dw_impl(const void* G, const void* G_lo, int ldg, const void* H
   P.dW = dW;
   P.rowscale = rowscale;
   P.db = db;
-  if (const char* m = getenv("B200_DW_MODE")) P.dbg = atoi(m);
   const int smem = dw::kStages * dw::stage_bytes(J) + 1024;
   // per device, and cheap: set on every call (a process may drive several GPUs)
   B200_CHECK_CUDA(cudaFuncSetAttribute(dw::joint_dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
