@@ -10,6 +10,12 @@ wl = bench.WORKLOADS[name](dict(bench.CFG3), 0)
 for _ in range(4):
     wl.step()
 torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+e0.record()
+for _ in range(10):
+    wl.step()
+e1.record(); e1.synchronize()
+print(f"step (10 back-to-back, no profiler): {e0.elapsed_time(e1) / 10:.3f} ms")
 n = 3
 with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     for _ in range(n):
