@@ -52,3 +52,30 @@ def test_product_does_not_import_oracle():
         src = f.read_text()
         assert "oracle" not in re.sub(r'""".*?"""', "", src, flags=re.S).replace("build_oracle", "") \
             or f.name == "build.py", f"{f} references the oracle"
+
+
+def test_round2_entry_points_validate_arguments_without_a_gpu():
+    """The entry points added in round 2 (no-recompute backward, rescoring, fp32 twin) reject null /
+    inconsistent arguments with status 1 and a message, before touching the device."""
+    from wenet_celoss_b200 import _lib
+    L = _lib.lib()
+    c = ctypes
+    cases = [
+        ("b200_joint_fwd_p", (None,) * 7 + (1, 1, 1, 8, 64, 0) + (None,) * 5 + (64, None, 16, 0, None), b"null pointer"),
+        ("b200_joint_rowscale", (None,) * 5 + (1, 1, 1, 8, 64, 0, None, 16, None, 64, None, None, None), b"null pointer"),
+        ("b200_joint_dw_db", (None, 16, None, 64, c.c_longlong(4), 8, 128, None, None, None, 0, None), b"null pointer"),
+        ("b200_joint_dh_scaled", (None, 16, None, None, 64, None, 1, 1, 1, 8, 256, None, None, None, None, 0, None),
+         b"null pointer"),
+        ("b200_attn_rescore", (None, None, None, None, 1, 1, 0, 8, 0, c.c_double(0), c.c_double(1), None,
+                               c.c_double(0), None, c.c_double(0), None, None, None, None), b"null pointer"),
+        ("b200_joint_h", (None, None, 1, 1, 1, 64, None, 64, None), b"null pointer"),
+        ("b200_joint_rowscale_split", (None,) * 3 + (1, 1, 1, 8, 64, 0, None, None, c.c_longlong(16), None, None, 64,
+                                                      None, None, None, None), b"null pointer"),
+        ("b200_colsum_split_w", (None, None, c.c_longlong(1), 8, c.c_longlong(8), None, None, None), b"null"),
+    ]
+    for name, args, needle in cases:
+        fn = getattr(L, name)
+        fn.restype = ctypes.c_int
+        rc = fn(*args)
+        assert rc == 1, (name, rc)
+        assert needle in L.b200_last_error(), (name, L.b200_last_error())
