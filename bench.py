@@ -58,8 +58,41 @@ class ClockSampler:
         self.index = index
         self.rows = []
         self.proc = None
+        self.nvml = None  # (module, handle): NVML polled every 5 ms from a thread - the timed region is a
+        self.stop_flag = False  # few hundred ms, nvidia-smi -lms 100 gave 1-4 samples (often one idle sample)
+        self.samples = []
+
+    def _nvml_open(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            try:
+                uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+                h = nv.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:  # noqa: BLE001
+                h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            return nv, h
+        except Exception:  # noqa: BLE001
+            return None
+
+    def _poll(self):
+        nv, h = self.nvml
+        reasons_fn = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+            getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons")
+        while not self.stop_flag:
+            try:
+                self.samples.append((nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM),
+                                     nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM), int(reasons_fn(h))))
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(0.005)
 
     def start(self):
+        self.nvml = self._nvml_open()
+        if self.nvml is not None:
+            self.thr = threading.Thread(target=self._poll, daemon=True)
+            self.thr.start()
+            return
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
@@ -74,6 +107,15 @@ class ClockSampler:
             self.rows.append(line.strip())
 
     def stop(self):
+        if self.nvml is not None:
+            self.stop_flag = True
+            self.thr.join(timeout=1.0)
+            bits = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+            reasons = sorted({n for _, _, r in self.samples for bit, n in bits.items() if r & bit})
+            sm = [c for c, _, _ in self.samples]
+            return {"sm_mhz": statistics.median(sm) if sm else None,
+                    "sm_max_mhz": max((m for _, m, _ in self.samples), default=None), "samples": len(sm),
+                    "reasons": reasons, "source": "nvml, 5 ms period"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
