@@ -27,3 +27,20 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     for _ in range(5): step()
     torch.cuda.synchronize()
 print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=14, max_name_column_width=60))
+
+if len(sys.argv) > 1 and sys.argv[1] == "module":
+    # the fused module (ctc_lo + log_softmax + loss): per-kernel device times of CTC.forward + backward
+    E = 256
+    m = pkg.CTC(V, E).to(dev)
+    hs = torch.randn(B5, T5, E, generator=g).to(dev).requires_grad_(True)
+    def mstep():
+        hs.grad = None
+        m.zero_grad(set_to_none=True)
+        loss = m(hs, hl, ys, yl)
+        loss.backward()
+    for _ in range(3): mstep()
+    torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+        for _ in range(5): mstep()
+        torch.cuda.synchronize()
+    print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=24, max_name_column_width=70))

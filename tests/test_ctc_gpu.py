@@ -95,6 +95,32 @@ def test_fp32_vs_aten_and_c_oracle(shape):
     assert np.abs(grad.sum(-1)).max() < 1e-4  # sum_c grad = scale*(1 - sum_s posterior)
 
 
+@pytest.mark.parametrize("shape,dtype", [((3, 50, 7, 4233), torch.float32), ((2, 301, 140, 1030), torch.float32),
+                                         ((5, 17, 3, 7), torch.float32), ((3, 43, 9, 1001), torch.bfloat16),
+                                         ((2, 33, 6, 250), torch.float16)])
+def test_grad_kernel_shapes(shape, dtype):
+    """ctc_grad_kernel writes the label entries inside the row stream (bitmap over the classes + rank into
+    the class-ordered entries of the row).  Shapes: frames not a multiple of the 8-row group, rows not
+    16-byte aligned (odd V: the per-element bitmap path), more than 256 extended states (the loops past
+    the register-resident states), 8 elements per 16-byte segment; every label entry and every plain entry
+    against the fp64 oracle."""
+    B, T, L, V = shape
+    logits, ys, hl, yl = _case(B, T, L, V, seed=T + V)
+    lq = logits.to(dtype)
+    scale = torch.linspace(0.5, 1.5, B)
+    grad = _mine(lq, ys, hl, yl, scale)[1]
+    g64 = np.zeros_like(grad)
+    for b in range(B):
+        g64[b] = ctc_loss_c(lq[b:b + 1].float(), ys[b:b + 1], hl[b:b + 1], yl[b:b + 1], blank=0,
+                            scale=float(scale[b]))[1][0]
+    if dtype == torch.float32:
+        np.testing.assert_allclose(grad, g64, rtol=1e-4, atol=1e-6)
+    else:
+        np.testing.assert_allclose(grad, g64, rtol=1e-2, atol=6e-3 if dtype == torch.bfloat16 else 8e-4)
+    for b in range(B):
+        assert np.all(grad[b, hl[b]:] == 0)
+
+
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 def test_half_precisions(dtype):
     logits, ys, hl, yl = _case(3, 40, 8, 1000, seed=3)

@@ -335,11 +335,172 @@ __global__ void ctc_lattice_kernel(const float* __restrict__ lp_ext,
 }
 
 // ---------------------------------------------------------------------------
-// pass 3: gradient w.r.t. logits, one warp per (b,t) row
+// pass 3: gradient w.r.t. logits
 //   grad[c] = scale_b * ( exp(x[c]-lse) - occ[c] ),  0 for t >= T_b
+// Persistent CTAs of kRowWarps STREAMING warps + one PATCH warp.  A work unit ("group") is
+// kRowWarps consecutive frames of one utterance; CTA i takes groups i, i + grid, ...
+//   * streaming warp w streams row w of the group: scale * softmax, 16-byte loads and stores - the
+//     2*B*T*V*s bytes that bound the pass - and needs nothing from memory to start: lse, scale and the
+//     live flag of its row were left in shared memory by the patch warp;
+//   * the patch warp works ONE GROUP AHEAD (two shared-memory buffers, named barriers full / empty
+//     per buffer): it forms the state posteriors of the group's rows,
+//       occ[leader(s)] += exp(alpha_t(s) + beta_t(s) - lp_t(s) + off),
+//     and leaves, per row, the final entries scale * (exp(lp) - occ) of the utterance's distinct label
+//     classes (and blank) IN CLASS ORDER, next to a bitmap over the classes and its running popcount:
+//     the entry of class c sits at rank(c) = number of label classes below c.  lp_ext[s] IS x[l'_s] - lse
+//     (pass 1 stored exactly that difference), so nothing is gathered from the logits row;
+//   * the streaming warp substitutes these entries INSIDE its stream (one bitmap word per 16-byte
+//     segment; the rare hit costs a popcount): every byte of the gradient is written once, by a full
+//     512-byte warp store.
+// Why: the previous kernels wrote the <= S patched entries AFTER the row's stream.  6.4 M scattered
+// 4-byte writes into lines that had already left L2 are 6.4 M read-modify-writes of a DRAM burst each:
+// 156 us of a 597 us kernel (measured by switching the scatter off), i.e. as much as 1 GB of streaming.
+// A round trip to memory takes 2-4 us while 32 warps per SM stream (queueing), so nothing latency-bound
+// may sit in front of a row's stream: the patch warp makes one round trip per group (alpha / beta /
+// lp_ext of the group's rows are one contiguous piece of each array: cp.async, no registers; per-row
+// scalars by lanes 0..7 next to them; leader / label tables per utterance).
+// Shared memory is kept small on purpose (28 KB per CTA at cfg5): the loads in flight live in the L1
+// part of the same 256 KB, and a 52 KB variant (class -> state table of 2 V bytes per buffer) that left
+// 18 KB of L1 per SM streamed at 569 us where 36 KB per CTA gave 530.
+// History at cfg5 (2.56 GB): 537 us = 0.73 of the HBM peak (one warp per row did occupancies, stream,
+// scatter); 597 us with a patch warp but the scatter kept; 441 us without the scatter.
 // ---------------------------------------------------------------------------
+constexpr int kPatchWarps = 4;                          // each takes kRowWarps / kPatchWarps rows of a group
+constexpr int kPatchRows = kRowWarps / kPatchWarps;
+constexpr int kGradThreads = (kRowWarps + kPatchWarps) * 32;
+constexpr int kGradInfo = 32;  // floats of per-group row info per buffer: c0l2[8] | scale[8]
+
+__device__ __forceinline__ void cp_async_f(float* dst, const float* src, bool vec) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+  if (vec)
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src) : "memory");
+  else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(src) : "memory");
+}
+// n floats global -> shared by one warp; dst and src have the same position within their 16-byte line
+// (the caller offsets dst by the phase of src), so all but the ragged ends go as 16-byte copies
+__device__ __forceinline__ void cp_async_span(float* dst, const float* src, int n, int lane) {
+  int head = (int)((16 - ((uintptr_t)src & 15)) & 15) >> 2;
+  if (head > n) head = n;
+  const int nvec = (n - head) >> 2;
+  if (lane < head) cp_async_f(dst + lane, src + lane, false);
+  for (int i = lane; i < nvec; i += 32) cp_async_f(dst + head + 4 * i, src + head + 4 * i, true);
+  const int done = head + 4 * nvec;
+  if (lane < n - done) cp_async_f(dst + done + lane, src + done + lane, false);
+}
+__device__ __forceinline__ void named_bar_sync(int id, int n) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+__device__ __forceinline__ void named_bar_arrive(int id, int n) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+
+// shared-memory layout (32-bit words): per patch warp its staging alpha | beta | lp_ext (the alpha part
+// doubles as the occupancy accumulator), then per buffer: values [kRowWarps][Lmax + 1],
+// row info, class bitmap [nbm], running popcount [nbm] (uint16)
+struct GradLayout {
+  int nst, nval, nbm, nbuf;
+  size_t bytes;
+};
+__host__ __device__ inline GradLayout ctc_grad_layout(int Lmax, int V) {
+  GradLayout L;
+  L.nst = (kPatchRows * (2 * Lmax + 1) + 4 + 3) & ~3;  // per patch warp and array, + the 16-byte phase of the source
+  L.nval = (kRowWarps * (Lmax + 1) + 3) & ~3;
+  L.nbm = ((V + 31) / 32 + 3) & ~3;
+  L.nbuf = L.nval + kGradInfo + L.nbm + L.nbm / 2;
+  L.bytes = ((size_t)3 * kPatchWarps * L.nst + 2 * (size_t)L.nbuf) * sizeof(float);
+  return L;
+}
+
+// shared-memory reads by 32-bit shared-space address (the pointers below are selected per buffer; as
+// generic pointers every read re-derived the shared window: a dozen instructions per patched entry)
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t a) {
+  uint16_t v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float lds_f32(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+
+// the patched entry of class e, if e is a label class of the utterance: rank = set bits below e
+// (bm: class bitmap, pre: running popcount per word (uint16), val: entries in class order)
+__device__ __forceinline__ void ctc_patch_elem(float& f, int e, uint32_t bm, uint32_t pre, uint32_t val) {
+  const uint32_t word = lds_u32(bm + 4u * (e >> 5));
+  const uint32_t sh = e & 31;
+  if ((word >> sh) & 1u) f = lds_f32(val + 4u * (lds_u16(pre + 2u * (e >> 5)) + __popc(word & ((1u << sh) - 1u))));
+}
+
+// One row of the gradient by one warp: out[e] = scale * exp(x[e] - lse), entries of label classes
+// replaced from val while they pass through registers.
 template <typename T>
-__global__ void __launch_bounds__(kRowWarps * 32)
+__device__ __forceinline__ void ctc_grad_row(const T* __restrict__ row, T* __restrict__ out, int V, int lane,
+                                             float c0l2, float scale, uint32_t bm, uint32_t pre, uint32_t val) {
+  constexpr int K = Elem<T>::kPerVec;
+  RowSegs<T> rs(row, V);
+  uint4* oseg0 = reinterpret_cast<uint4*>(reinterpret_cast<uintptr_t>(out) & ~uintptr_t(15));
+  uint4 v[kUnroll], nv[kUnroll];
+  warp_row_stream_begin<T>(rs, lane, nv);
+  const bool aligned = rs.head == 0;  // a segment's K classes are K adjacent bits of ONE bitmap word
+  for (int base = 0; base < rs.nseg; base += 32 * kUnroll) {
+#pragma unroll
+    for (int j = 0; j < kUnroll; ++j) v[j] = nv[j];
+#pragma unroll
+    for (int j = 0; j < kUnroll; ++j) {  // software pipeline: next block's loads in flight
+      int idx = base + 32 * kUnroll + j * 32 + lane;
+      if (idx < rs.nseg) nv[j] = ldg_stream16(rs.seg0 + idx);
+    }
+#pragma unroll
+    for (int j = 0; j < kUnroll; ++j) {
+      int idx = base + j * 32 + lane;
+      if (idx >= rs.nseg) continue;
+      float f[K];
+      Elem<T>::unpack(v[j], f);
+#pragma unroll
+      for (int k = 0; k < K; ++k) f[k] = scale * ex2_approx(fmaf(f[k], kLog2e, c0l2));
+      const int e0 = idx * K - rs.head;
+      if (e0 >= 0 && e0 + K <= V) {
+        if (aligned) {
+          const uint32_t word = lds_u32(bm + 4u * (e0 >> 5));
+          const uint32_t sh = e0 & 31;
+          const uint32_t bits = (word >> sh) & ((1u << K) - 1u);
+          if (bits) {  // ~L of V/K segments (but some lane of the warp nearly every time)
+            uint32_t a = val + 4u * (lds_u16(pre + 2u * (e0 >> 5)) + __popc(word & ((1u << sh) - 1u)));
+#pragma unroll
+            for (int k = 0; k < K; ++k)
+              if ((bits >> k) & 1u) {
+                f[k] = lds_f32(a);
+                a += 4u;
+              }
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < K; ++k) ctc_patch_elem(f[k], e0 + k, bm, pre, val);
+        }
+        stg_stream16(oseg0 + idx, Elem<T>::pack(f));
+      } else {  // edge segments shared with the neighbouring rows: element stores
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          int e = e0 + k;
+          if (e >= 0 && e < V) {
+            ctc_patch_elem(f[k], e, bm, pre, val);
+            out[e] = Elem<T>::from_float(f[k]);
+          }
+        }
+      }
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kGradThreads, 3)
 ctc_grad_kernel(const T* __restrict__ logits, const float* __restrict__ lse,
                 const float* __restrict__ lp_ext, const float* __restrict__ alpha,
                 const float* __restrict__ beta, const double* __restrict__ frame_off,
@@ -347,102 +508,237 @@ ctc_grad_kernel(const T* __restrict__ logits, const float* __restrict__ lse,
                 const int32_t* __restrict__ hlens, const int32_t* __restrict__ ys_lens,
                 const int32_t* __restrict__ leader, int B, int Tm, int V, int Lmax, int blank,
                 T* __restrict__ grad) {
-  extern __shared__ float occ_all[];  // [kRowWarps][Smax]
-  const long long rows = (long long)B * Tm;
-  const long long rowi = (long long)blockIdx.x * kRowWarps + (threadIdx.x >> 5);
+  extern __shared__ __align__(16) float smem_f[];
+  const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  if (rowi >= rows) return;
   const int Smax = 2 * Lmax + 1;
-  float* occ = occ_all + (threadIdx.x >> 5) * Smax;
-  const int b = int(rowi / Tm), t = int(rowi - (long long)b * Tm);
-  const T* row = logits + rowi * V;
-  T* grow = grad + rowi * V;
-  const float sc = scale[b];
-  const bool dead = (t >= hlens[b]) || (sc == 0.f);
-  if (dead) {
-    warp_row_softmax_store<T>(row, grow, V, lane, true, 0.f, 0.f, -1.f);
+  const GradLayout L = ctc_grad_layout(Lmax, V);
+  const int gpu = (Tm + kRowWarps - 1) / kRowWarps;  // groups per utterance
+  const int ngroups = B * gpu;
+  float* bufs = smem_f + 3 * kPatchWarps * L.nst;
+  // named barriers: full[buf] = 1 + buf (patch warps arrive, streaming warps wait),
+  //                 empty[buf] = 3 + buf (streaming warps arrive, patch warps wait),
+  //                 5: among the patch warps (class bitmap of the group built by the first of them)
+
+  if (warp >= kRowWarps) {  // ---- patch warps: one group ahead of the streaming warps ----
+    const int pw = warp - kRowWarps;  // takes rows pw * kPatchRows .. of every group
+    float* st_al = smem_f + 3 * pw * L.nst;
+    float* st_be = st_al + L.nst;
+    float* st_lp = st_be + L.nst;
+    constexpr int kOcc = 8;  // states s = lane + 32 i, i < kOcc, keep leader / class / rank in registers
+    int pd[kOcc], pc[kOcc], pr[kOcc];
+    int cur_b = -1;
+    bool dups = false;  // the utterance repeats a label (among its first 32 kOcc states)
+    int k = 0;
+    for (int g = blockIdx.x; g < ngroups; g += gridDim.x, ++k) {
+      const int buf = k & 1;
+      float* val_all = bufs + (size_t)buf * L.nbuf;
+      float* info = val_all + L.nval;
+      uint32_t* bm = reinterpret_cast<uint32_t*>(info + kGradInfo);
+      uint16_t* pre = reinterpret_cast<uint16_t*>(bm + L.nbm);
+      const int b = g / gpu;
+      const int t0 = (g - b * gpu) * kRowWarps;
+      const int nrows = Tm - t0 < kRowWarps ? Tm - t0 : kRowWarps;
+      const long long row0 = (long long)b * Tm + t0;
+      // (1) alpha / beta / lp_ext of this warp's rows: one contiguous piece of each array
+      const int w0 = pw * kPatchRows;
+      const int myrows = nrows - w0 < kPatchRows ? (nrows - w0 > 0 ? nrows - w0 : 0) : kPatchRows;
+      const float* g_al = alpha + (row0 + w0) * Smax;
+      const float* g_be = beta + (row0 + w0) * Smax;
+      const float* g_lp = lp_ext + (row0 + w0) * Smax;
+      const int ph_al = (int)((uintptr_t)g_al & 15) >> 2, ph_be = (int)((uintptr_t)g_be & 15) >> 2,
+                ph_lp = (int)((uintptr_t)g_lp & 15) >> 2;
+      cp_async_span(st_al + ph_al, g_al, myrows * Smax, lane);
+      cp_async_span(st_be + ph_be, g_be, myrows * Smax, lane);
+      cp_async_span(st_lp + ph_lp, g_lp, myrows * Smax, lane);
+      // (2) per-row scalars (lane i: this warp's row i) and the utterance's leader / class per state
+      const float sc = scale[b];
+      const int hl = hlens[b];
+      const int S = 2 * ys_lens[b] + 1;
+      float my_nl = 0.f, my_c0 = 0.f;
+      if (lane < myrows) {
+        const int t = t0 + w0 + lane;
+        // alpha_hat + beta_hat + (off_a[t] + off_b[t] - ll): the bracket is O(1) because
+        // sum_s alpha_t(s) beta_t(s) / y_t(l'_s) = exp(ll) for every t
+        const double* oa = frame_off + (long long)b * 2 * (Tm + 1);
+        my_nl = (float)(oa[t] + oa[Tm + 1 + t] - oa[Tm]);
+        my_c0 = -lse[row0 + w0 + lane] * kLog2e;
+      }
+      const int32_t* ld = leader + (long long)b * Smax;
+      const long long* ys = ys_pad + (long long)b * Lmax;
+      if (b != cur_b) {
+        cur_b = b;
+#pragma unroll
+        for (int i = 0; i < kOcc; ++i) {
+          const int s = lane + 32 * i;
+          pd[i] = 0;
+          pc[i] = -1;
+          if (s < S) {
+            pd[i] = ld[s];
+            if (s & 1) pc[i] = (int)ys[s >> 1];
+          }
+        }
+#pragma unroll
+        bool d = false;
+#pragma unroll
+        for (int i = 0; i < kOcc; ++i) {  // only the first state of each distinct label patches
+          const int s = lane + 32 * i;
+          d |= s < S && (s & 1) && pd[i] != s;
+          if (pd[i] != s || pc[i] >= V || pc[i] == blank) pc[i] = -1;
+        }
+        dups = __any_sync(0xffffffffu, d);
+      }
+      // (3) this buffer's previous group (k - 2) has been streamed
+      if (k >= 2) named_bar_sync(3 + buf, kGradThreads);
+      // class bitmap of utterance b and its running popcount (first patch warp), the rank of every
+      // patching state (all of them)
+      if (pw == 0) {
+        for (int i = lane; i < L.nbm; i += 32) bm[i] = 0u;
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < kOcc; ++i)
+          if (pc[i] >= 0) atomicOr(&bm[pc[i] >> 5], 1u << (pc[i] & 31));
+        for (int s = lane + 32 * kOcc; s < S; s += 32) {  // longer label sequences
+          if (!(s & 1) || ld[s] != s) continue;
+          const int c = (int)ys[s >> 1];
+          if (c >= 0 && c < V && c != blank) atomicOr(&bm[c >> 5], 1u << (c & 31));
+        }
+        if (lane == 0) atomicOr(&bm[blank >> 5], 1u << (blank & 31));
+        __syncwarp();
+        {
+          const int chunk = (L.nbm + 31) / 32;
+          int cnt = 0;
+          for (int j = 0; j < chunk; ++j) {
+            const int w = lane * chunk + j;
+            if (w < L.nbm) cnt += __popc(bm[w]);
+          }
+          int incl = cnt;
+#pragma unroll
+          for (int d = 1; d < 32; d <<= 1) {
+            const int n = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += n;
+          }
+          int run = incl - cnt;
+          for (int j = 0; j < chunk; ++j) {
+            const int w = lane * chunk + j;
+            if (w < L.nbm) {
+              pre[w] = (uint16_t)run;
+              run += __popc(bm[w]);
+            }
+          }
+        }
+        __syncwarp();
+      }
+      named_bar_sync(5, kPatchWarps * 32);
+      auto rank_of = [&](int c) { return (int)pre[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u)); };
+#pragma unroll
+      for (int i = 0; i < kOcc; ++i) pr[i] = pc[i] >= 0 ? rank_of(pc[i]) : -1;
+      const int rank_blank = rank_of(blank);
+      asm volatile("cp.async.wait_all;" ::: "memory");
+      __syncwarp();
+      // (4) this warp's rows of the group
+      for (int r = 0; r < myrows; ++r) {
+        const int w = w0 + r;
+        const bool live = t0 + w < hl && sc != 0.f;
+        const float nl = __shfl_sync(0xffffffffu, my_nl, r);
+        const float c0 = __shfl_sync(0xffffffffu, my_c0, r);
+        if (lane == 0) {
+          info[w] = c0;
+          info[kRowWarps + w] = live ? sc : 0.f;  // 0: the streaming warp writes a row of zeros
+        }
+        if (!live) continue;
+        float* al = st_al + ph_al + r * Smax;  // becomes the occupancy accumulator (repeated labels / long sequences)
+        float* be = st_be + ph_be + r * Smax;  // becomes the state posterior (long sequences)
+        const float* lp = st_lp + ph_lp + r * Smax;
+        float* val = val_all + (size_t)w * (Lmax + 1);
+        // alpha*beta counts the emission at t twice: take lp out once.  The first state of a label
+        // (leader) owns its occupancy slot and stores into it; the other states of a repeated label add
+        // to it afterwards - none in most utterances (dups, a vote per utterance), so that the common row
+        // is: three shared-memory reads, one exp per state, registers from there on.
+        float post[kOcc], pl[kOcc];
+        float occ_blank = 0.f;
+#pragma unroll
+        for (int i = 0; i < kOcc; ++i) {
+          const int s = lane + 32 * i;
+          post[i] = pl[i] = 0.f;
+          if (s < S) {
+            pl[i] = lp[s];
+            post[i] = expf(al[s] + be[s] + nl - pl[i]);
+            if (!(s & 1)) occ_blank += post[i];
+          }
+        }
+        for (int s = lane + 32 * kOcc; s < S; s += 32) {  // longer label sequences: through shared memory
+          const float p = expf(al[s] + be[s] + nl - lp[s]);
+          be[s] = p;
+          if (!(s & 1)) occ_blank += p;
+        }
+        if (dups || S > 32 * kOcc) {
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < kOcc; ++i) {
+            const int s = lane + 32 * i;
+            if (s < S && (s & 1) && pd[i] == s) al[s] = post[i];
+          }
+          for (int s = lane + 32 * kOcc; s < S; s += 32)
+            if ((s & 1) && ld[s] == s) al[s] = be[s];
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < kOcc; ++i) {
+            const int s = lane + 32 * i;
+            if (s < S && (s & 1) && pd[i] != s) atomicAdd(&al[pd[i]], post[i]);
+          }
+          for (int s = lane + 32 * kOcc; s < S; s += 32)
+            if ((s & 1) && ld[s] != s) atomicAdd(&al[ld[s]], be[s]);
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < kOcc; ++i) {
+            const int s = lane + 32 * i;
+            if (s < S && (s & 1) && pd[i] == s) post[i] = al[s];
+          }
+        }
+        occ_blank = warp_sum(occ_blank);
+        // occupancy -> gradient entry at the rank of its class
+#pragma unroll
+        for (int i = 0; i < kOcc; ++i)
+          if (pr[i] >= 0) val[pr[i]] = sc * (expf(pl[i]) - post[i]);
+        for (int s = lane + 32 * kOcc; s < S; s += 32) {
+          if (!(s & 1) || ld[s] != s) continue;
+          const int c = (int)ys[s >> 1];
+          if (c >= 0 && c < V && c != blank) val[rank_of(c)] = sc * (expf(lp[s]) - al[s]);
+        }
+        if (lane == 0) val[rank_blank] = sc * (expf(lp[0]) - occ_blank);
+      }
+      __syncwarp();
+      __threadfence_block();
+      named_bar_arrive(1 + buf, kGradThreads);
+    }
     return;
   }
-  const int S = 2 * ys_lens[b] + 1;
-  const float l = lse[rowi];
-  // alpha_hat + beta_hat + (off_a[t] + off_b[t] - ll): the bracket is O(1) because
-  // sum_s alpha_t(s) beta_t(s) / y_t(l'_s) = exp(ll) for every t
-  const double* oa = frame_off + (long long)b * 2 * (Tm + 1);
-  const float nl = (float)(oa[t] + oa[Tm + 1 + t] - oa[Tm]);
-  const float* al = alpha + rowi * Smax;
-  const float* be = beta + rowi * Smax;
-  const float* lp = lp_ext + rowi * Smax;
-  const int32_t* ld = leader + (long long)b * Smax;
-  // logits at the label classes, gathered BEFORE the row is streamed (see ctc_logprobs_kernel)
-  const long long* ys = ys_pad + (long long)b * Lmax;
-  constexpr int kPre = 8;
-  float xg[kPre];
-#pragma unroll
-  for (int i = 0; i < kPre; ++i) {
-    const int s = 1 + 2 * (lane + 32 * i);
-    xg[i] = 0.f;
-    if (s < S && ld[s] == s) {
-      const int c = (int)ys[s >> 1];
-      if (c >= 0 && c < V) xg[i] = Elem<T>::to_float(row[c]);
+
+  // ---- streaming warps ----
+  int k = 0;
+  for (int g = blockIdx.x; g < ngroups; g += gridDim.x, ++k) {
+    const int buf = k & 1;
+    const float* val_all = bufs + (size_t)buf * L.nbuf;
+    const float* info = val_all + L.nval;
+    const uint32_t* bm = reinterpret_cast<const uint32_t*>(info + kGradInfo);
+    const uint16_t* pre = reinterpret_cast<const uint16_t*>(bm + L.nbm);
+    named_bar_sync(1 + buf, kGradThreads);
+    const int b = g / gpu;
+    const int t = (g - b * gpu) * kRowWarps + warp;
+    if (t < Tm) {
+      const long long rowi = (long long)b * Tm + t;
+      const T* row = logits + rowi * V;
+      T* grow = grad + rowi * V;
+      const float sc = info[kRowWarps + warp];
+      if (sc == 0.f)
+        warp_row_softmax_store<T>(row, grow, V, lane, true, 0.f, 0.f, -1.f);
+      else
+        ctc_grad_row<T>(row, grow, V, lane, info[warp], sc, (uint32_t)__cvta_generic_to_shared(bm),
+                        (uint32_t)__cvta_generic_to_shared(pre),
+                        (uint32_t)__cvta_generic_to_shared(val_all + (size_t)warp * (Lmax + 1)));
     }
-  }
-  const float xblank = Elem<T>::to_float(row[blank]);
-  // the first kOcc * 32 states: all four loads of every state issued before the first use (a
-  // rolled loop with the shared-memory atomic in its body paid one memory round trip per 32 states)
-  constexpr int kOcc = 8;
-  float pa[kOcc], pb[kOcc], pl[kOcc];
-  int pd[kOcc];
-#pragma unroll
-  for (int i = 0; i < kOcc; ++i) {
-    const int s = lane + 32 * i;
-    pa[i] = pb[i] = pl[i] = 0.f;
-    pd[i] = 0;
-    if (s < S) {
-      pa[i] = al[s];
-      pb[i] = be[s];
-      pl[i] = lp[s];
-      pd[i] = ld[s];
-    }
-  }
-  for (int s = lane; s < S; s += 32) occ[s] = 0.f;
-  __syncwarp();
-  float occ_blank = 0.f;
-#pragma unroll
-  for (int i = 0; i < kOcc; ++i) {
-    const int s = lane + 32 * i;
-    if (s >= S) continue;
-    // alpha*beta counts the emission at t twice: take lp out once
-    const float post = expf(pa[i] + pb[i] + nl - pl[i]);
-    if (s & 1)
-      atomicAdd(&occ[pd[i]], post);
-    else
-      occ_blank += post;
-  }
-  for (int s = lane + 32 * kOcc; s < S; s += 32) {  // longer label sequences
-    float post = expf(al[s] + be[s] + nl - lp[s]);
-    if (s & 1)
-      atomicAdd(&occ[ld[s]], post);
-    else
-      occ_blank += post;
-  }
-  occ_blank = warp_sum(occ_blank);
-  warp_row_softmax_store<T>(row, grow, V, lane, false, -l * kLog2e, sc, -1.f);
-  __syncwarp();  // streaming stores and occ[] atomics are ordered before the fix-ups
-  if (lane == 0) grow[blank] = Elem<T>::from_float(sc * (expf(xblank - l) - occ_blank));
-#pragma unroll
-  for (int i = 0; i < kPre; ++i) {
-    const int s = 1 + 2 * (lane + 32 * i);
-    if (s >= S || ld[s] != s) continue;  // only the first state of each distinct label writes
-    const int c = (int)ys[s >> 1];
-    if (c < 0 || c >= V || c == blank) continue;
-    grow[c] = Elem<T>::from_float(sc * (expf(xg[i] - l) - occ[s]));
-  }
-  for (int s = 1 + 2 * (lane + 32 * kPre); s < S; s += 64) {  // longer label sequences
-    if (ld[s] != s) continue;
-    const int c = (int)ys[s >> 1];
-    if (c < 0 || c >= V || c == blank) continue;
-    const float x = Elem<T>::to_float(row[c]);
-    grow[c] = Elem<T>::from_float(sc * (expf(x - l) - occ[s]));
+    if ((long long)g + 2ll * gridDim.x < ngroups) named_bar_arrive(3 + buf, kGradThreads);
   }
 }
 
@@ -522,31 +818,43 @@ extern "C" int b200_ctc_grad(const void* logits, int dtype, const float* lse, co
                  "b200_ctc_grad: null pointer");
   B200_CHECK_ARG(((reinterpret_cast<uintptr_t>(logits) ^ reinterpret_cast<uintptr_t>(grad)) & 15) == 0,
                  "b200_ctc_grad: logits and grad must share 16-byte alignment phase");
-  const long long rows = (long long)B * T;
-  const unsigned grid = (unsigned)((rows + kRowWarps - 1) / kRowWarps);
-  const int Smax = 2 * Lmax + 1;
-  const size_t smem = (size_t)kRowWarps * Smax * sizeof(float);
   cudaStream_t st = (cudaStream_t)stream;
   const long long* ys = reinterpret_cast<const long long*>(ys_pad);
+  int dev = 0, sms = 0, smem_max = 0;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  B200_CHECK_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  const GradLayout L = ctc_grad_layout(Lmax, V);  // 28 KB at cfg5; 1 CTA per SM from about 2 Lmax + 1 = 700 states
+  B200_CHECK_ARG(L.bytes <= (size_t)smem_max, "b200_ctc_grad: %zu bytes of shared memory needed, %d available",
+                 L.bytes, smem_max);
+  const long long ngroups = (long long)B * ((T + kRowWarps - 1) / kRowWarps);
+  B200_CHECK_ARG(ngroups < (1ll << 31), "b200_ctc_grad: B*T too large");
+#define B200_CTC_GRAD_LAUNCH(TYPE)                                                                           \
+  do {                                                                                                       \
+    auto* fn = ctc_grad_kernel<TYPE>;                                                                        \
+    B200_CHECK_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.bytes));    \
+    int per_sm = 0;                                                                                          \
+    B200_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kGradThreads, L.bytes));      \
+    if (per_sm < 1) per_sm = 1;                                                                              \
+    const long long grid = ngroups < (long long)sms * per_sm ? ngroups : (long long)sms * per_sm;            \
+    fn<<<(unsigned)grid, kGradThreads, L.bytes, st>>>((const TYPE*)logits, lse, lp_ext, alpha, beta,         \
+                                                      frame_off, scale, ys, hlens, ys_lens, leader, B, T, V, \
+                                                      Lmax, blank, (TYPE*)grad);                             \
+  } while (0)
   switch (dtype) {
     case B200_F32:
-      ctc_grad_kernel<float><<<grid, kRowWarps * 32, smem, st>>>(
-          (const float*)logits, lse, lp_ext, alpha, beta, frame_off, scale, ys, hlens, ys_lens, leader, B,
-          T, V, Lmax, blank, (float*)grad);
+      B200_CTC_GRAD_LAUNCH(float);
       break;
     case B200_F16:
-      ctc_grad_kernel<__half><<<grid, kRowWarps * 32, smem, st>>>(
-          (const __half*)logits, lse, lp_ext, alpha, beta, frame_off, scale, ys, hlens, ys_lens, leader, B,
-          T, V, Lmax, blank, (__half*)grad);
+      B200_CTC_GRAD_LAUNCH(__half);
       break;
     case B200_BF16:
-      ctc_grad_kernel<__nv_bfloat16><<<grid, kRowWarps * 32, smem, st>>>(
-          (const __nv_bfloat16*)logits, lse, lp_ext, alpha, beta, frame_off, scale, ys, hlens, ys_lens,
-          leader, B, T, V, Lmax, blank, (__nv_bfloat16*)grad);
+      B200_CTC_GRAD_LAUNCH(__nv_bfloat16);
       break;
     default:
       B200_CHECK_ARG(false, "b200_ctc_grad: unsupported dtype %d", dtype);
   }
+#undef B200_CTC_GRAD_LAUNCH
   B200_CHECK_LAUNCH("ctc_grad_kernel");
   return B200_OK;
 }

@@ -66,25 +66,30 @@ __device__ __forceinline__ float warp_row_lse(const T* __restrict__ row, int V, 
   return M + logf(S);
 }
 
+// First block of 16-byte loads of a row stream.  Split from the body so that a caller can put
+// independent work (whose own loads are already issued) between the two: the stream's first
+// round trip to HBM then overlaps that work instead of following it.
+template <typename T>
+__device__ __forceinline__ void warp_row_stream_begin(const RowSegs<T>& rs, int lane, uint4 (&nv)[kUnroll]) {
+#pragma unroll
+  for (int j = 0; j < kUnroll; ++j) {
+    int idx = j * 32 + lane;
+    if (idx < rs.nseg) nv[j] = ldg_stream16(rs.seg0 + idx);
+  }
+}
+
 // Stream one row: out[e] = clamp(scale * exp(x[e] + c0)) (or zeros when dead), with
 // 16-byte stores for whole segments and element stores on the two edge segments that
-// may be shared with neighbouring rows.  c0l2 = c0 * log2(e).
+// may be shared with neighbouring rows.  c0l2 = c0 * log2(e).  nv: the loads of
+// warp_row_stream_begin (unused when dead).
 template <typename T>
-__device__ __forceinline__ void warp_row_softmax_store(const T* __restrict__ row,
-                                                       T* __restrict__ out, int V, int lane,
-                                                       bool dead, float c0l2, float scale,
-                                                       float clamp) {
+__device__ __forceinline__ void warp_row_softmax_store_from(const RowSegs<T>& rs, uint4 (&nv)[kUnroll],
+                                                            T* __restrict__ out, int V, int lane,
+                                                            bool dead, float c0l2, float scale,
+                                                            float clamp) {
   constexpr int K = Elem<T>::kPerVec;
-  RowSegs<T> rs(row, V);
   uint4* oseg0 = reinterpret_cast<uint4*>(reinterpret_cast<uintptr_t>(out) & ~uintptr_t(15));
-  uint4 v[kUnroll], nv[kUnroll];
-  if (!dead) {
-#pragma unroll
-    for (int j = 0; j < kUnroll; ++j) {
-      int idx = j * 32 + lane;
-      if (idx < rs.nseg) nv[j] = ldg_stream16(rs.seg0 + idx);
-    }
-  }
+  uint4 v[kUnroll];
   for (int base = 0; base < rs.nseg; base += 32 * kUnroll) {
     if (!dead) {  // software pipeline: next block's loads in flight while this one is written
 #pragma unroll
@@ -123,6 +128,17 @@ __device__ __forceinline__ void warp_row_softmax_store(const T* __restrict__ row
       }
     }
   }
+}
+
+template <typename T>
+__device__ __forceinline__ void warp_row_softmax_store(const T* __restrict__ row,
+                                                       T* __restrict__ out, int V, int lane,
+                                                       bool dead, float c0l2, float scale,
+                                                       float clamp) {
+  RowSegs<T> rs(row, V);
+  uint4 nv[kUnroll];
+  if (!dead) warp_row_stream_begin<T>(rs, lane, nv);
+  warp_row_softmax_store_from<T>(rs, nv, out, V, lane, dead, c0l2, scale, clamp);
 }
 
 }  // namespace b200
