@@ -199,7 +199,8 @@ def _ctc_case(B, T, E, V, Lmax, seed, repeats=False):
     return hs, hl, ys, yl
 
 
-@pytest.mark.parametrize("shape", [(4, 120, 256, 5000, 20), (3, 60, 512, 1000, 12), (2, 50, 256, 37, 9)])
+@pytest.mark.parametrize("shape", [(4, 120, 256, 5000, 20), (3, 60, 512, 1000, 12), (2, 50, 256, 37, 9),
+                                   (2, 600, 256, 700, 127), (2, 900, 256, 900, 200)])  # label blocks of 127: edge, two
 @pytest.mark.parametrize("reduce", [True, False])
 def test_ctc_module_fused_fp32(shape, reduce):
     """CTC.forward through split_gemm (no [B,T,V] logits) against the reference module's arithmetic
