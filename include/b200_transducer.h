@@ -357,6 +357,12 @@ int b200_joint_dh_split_scaled(const void* G_hi, const void* G_lo, int ldg, cons
 int b200_joint_dw_split(const void* G_hi, const void* G_lo, int ldg, const void* H_hi,
                         const void* H_lo, int ldh, long long n, int V, int J, float* dW,
                         int max_ctas, b200_stream_t stream);
+/* b200_joint_dw_split with the bias gradient (autograd of ffn_out.bias, joint.py:69, and of ctc_lo.bias,
+ * ctc.py:57): db [V] += sum_r w[r] (G_hi + G_lo)[r, v], w = rowscale [n] or NULL for plain column sums;
+ * taken from the operand tiles in shared memory (no second pass over G).  db is accumulated: zero it first. */
+int b200_joint_dw_split_db(const void* G_hi, const void* G_lo, int ldg, const void* H_hi,
+                           const void* H_lo, int ldh, long long n, int V, int J, float* dW,
+                           const float* rowscale, float* db, int max_ctas, b200_stream_t stream);
 int b200_joint_dh_split(const void* G_hi, const void* G_lo, int ldg, const void* w_hi,
                         const void* w_lo, const void* H_hi, const void* H_lo, int ldh, int nb,
                         int T, int U1, int V, int J, const int32_t* logit_len,

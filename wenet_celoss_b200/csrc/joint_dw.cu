@@ -248,43 +248,50 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         constexpr int kRsAhead = 6;
         auto load_rs = [&](int kb) {  // rows beyond n are zero-filled by TMA
           const long long c = (long long)kb * kBlockK + half * 32 + lane;
+          if (P.rowscale == nullptr) return 1.f;  // plain column sums (rows beyond n are zeros)
           return (kb < kb1 && c < P.n) ? __ldg(P.rowscale + c) : 0.f;
         };
         float rq[kRsAhead];
+        // split operands: the stage's A boxes hold G_hi in pass 0, G_lo in pass 1 (both summed: G = G_hi +
+        // G_lo) and G_hi again in pass 2 (only the hand-shake with the producer is kept up)
+        for (int pass = 0; pass < P.npass; ++pass) {
+          const bool sum_pass = pass < 2;
 #pragma unroll
-        for (int i = 0; i < kRsAhead; ++i) rq[i] = load_rs(kb0 + i);
-        for (int kb = kb0; kb < kb1; ++kb, ++it) {
-          const int s = (int)(it % kStages);
-          const uint32_t ph = (uint32_t)((it / kStages) & 1);
-          const float rs = rq[0];
+          for (int i = 0; i < kRsAhead; ++i) rq[i] = load_rs(kb0 + i);
+          for (int kb = kb0; kb < kb1; ++kb, ++it) {
+            const int s = (int)(it % kStages);
+            const uint32_t ph = (uint32_t)((it / kStages) & 1);
+            const float rs = rq[0];
 #pragma unroll
-          for (int i = 0; i + 1 < kRsAhead; ++i) rq[i] = rq[i + 1];
-          rq[kRsAhead - 1] = load_rs(kb + kRsAhead);
-          // "stage full": the TMA completion signals the LEADER's barrier only.  Rank 0 waits on it and one
-          // of its lanes relays it to a barrier in rank 1.  The relay is a RELAXED arrive: a release at
-          // cluster scope costs ~2 us per stage (measured: 6.9 -> 16 ms per launch), and the bytes it would
-          // order were written by rank 1's own TMA before the completion it follows
-          if (rank == 0) {
-            ptx::mbar_wait(full_bar(s), ph);
-            if (cw == 0 && lane == 0) mbar_arrive_cluster_relaxed(map_to_cta(lfull_bar(s), 1));
-          } else {
-            mbar_wait_cluster_acq(lfull_bar(s), ph);
+            for (int i = 0; i + 1 < kRsAhead; ++i) rq[i] = rq[i + 1];
+            rq[kRsAhead - 1] = load_rs(kb + kRsAhead);
+            // "stage full": the TMA completion signals the LEADER's barrier only.  Rank 0 waits on it and one
+            // of its lanes relays it to a barrier in rank 1.  The relay is a RELAXED arrive: a release at
+            // cluster scope costs ~2 us per stage (measured: 6.9 -> 16 ms per launch), and the bytes it would
+            // order were written by rank 1's own TMA before the completion it follows
+            if (rank == 0) {
+              ptx::mbar_wait(full_bar(s), ph);
+              if (cw == 0 && lane == 0) mbar_arrive_cluster_relaxed(map_to_cta(lfull_bar(s), 1));
+            } else {
+              mbar_wait_cluster_acq(lfull_bar(s), ph);
+            }
+            const uint32_t a = smem_base + (uint32_t)s * sbytes + box * kBoxBytes + half * 32 * 128 + (lane & 3) * 4;
+            const int ch = lane >> 2;
+            if (sum_pass)
+#pragma unroll
+            for (int r = 0; r < 32; r += 2) {
+              const uint32_t x0 = lds_u32(a + r * 128 + ((ch ^ (r & 7)) << 4));
+              const uint32_t x1 = lds_u32(a + (r + 1) * 128 + ((ch ^ ((r + 1) & 7)) << 4));
+              const float w0 = __shfl_sync(0xffffffffu, rs, r);
+              const float w1 = __shfl_sync(0xffffffffu, rs, r + 1);
+              a0 = fmaf(__uint_as_float(x0 << 16), w0, a0);
+              a1 = fmaf(__uint_as_float(x0 & 0xffff0000u), w0, a1);
+              a2 = fmaf(__uint_as_float(x1 << 16), w1, a2);
+              a3 = fmaf(__uint_as_float(x1 & 0xffff0000u), w1, a3);
+            }
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(csdone_bar(s));
           }
-          const uint32_t a = smem_base + (uint32_t)s * sbytes + box * kBoxBytes + half * 32 * 128 + (lane & 3) * 4;
-          const int ch = lane >> 2;
-#pragma unroll
-          for (int r = 0; r < 32; r += 2) {
-            const uint32_t x0 = lds_u32(a + r * 128 + ((ch ^ (r & 7)) << 4));
-            const uint32_t x1 = lds_u32(a + (r + 1) * 128 + ((ch ^ ((r + 1) & 7)) << 4));
-            const float w0 = __shfl_sync(0xffffffffu, rs, r);
-            const float w1 = __shfl_sync(0xffffffffu, rs, r + 1);
-            a0 = fmaf(__uint_as_float(x0 << 16), w0, a0);
-            a1 = fmaf(__uint_as_float(x0 & 0xffff0000u), w0, a1);
-            a2 = fmaf(__uint_as_float(x1 << 16), w1, a2);
-            a3 = fmaf(__uint_as_float(x1 & 0xffff0000u), w1, a3);
-          }
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(csdone_bar(s));
         }
         const int v = vt * kTileV + (int)rank * 128 + box * 64 + (lane >> 2) * 8 + (lane & 3) * 2;
         if (v < P.V) atomicAdd(P.db + v, a0 + a2);
@@ -370,8 +377,7 @@ int make_dw_map(CUtensorMap* map, const void* ptr, long long rows, int cols, lon
 static int joint_dw_impl(const void* G, const void* G_lo, int ldg, const void* H, const void* H_lo, int ldh,
                         long long n, int V, int J, float* dW, const float* rowscale, float* db, int max_ctas,
                         b200_stream_t stream) {
-  B200_CHECK_ARG((rowscale == nullptr) == (db == nullptr) && !(db && G_lo),
-                 "b200_joint_dw: rowscale and db go together (single-pass operands only)");
+  B200_CHECK_ARG(rowscale == nullptr || db != nullptr, "b200_joint_dw: rowscale without db");
   B200_CHECK_ARG(G && H && dW, "b200_joint_dw: null pointer");
   B200_CHECK_ARG((G_lo == nullptr) == (H_lo == nullptr), "b200_joint_dw: G_lo and H_lo go together");
   B200_CHECK_ARG(n > 0 && V > 0, "b200_joint_dw: bad shape n=%lld V=%d", n, V);
@@ -453,4 +459,14 @@ extern "C" int b200_joint_dw_split(const void* G_hi, const void* G_lo, int ldg, 
                                    b200_stream_t stream) {
   B200_CHECK_ARG(G_lo && H_lo, "b200_joint_dw_split: null pointer");
   return joint_dw_impl(G_hi, G_lo, ldg, H_hi, H_lo, ldh, n, V, J, dW, nullptr, nullptr, max_ctas, stream);
+}
+
+// the same with the bias gradient: db [V] += sum over rows of w[r] * (G_hi + G_lo)[r, v] (w = rowscale, or
+// nullptr for plain column sums), taken from the operand boxes of passes 0 and 1 while they sit in shared
+// memory - replaces a separate pass over both halves of G (b200_colsum_split: 2 * n * V * 2 bytes)
+extern "C" int b200_joint_dw_split_db(const void* G_hi, const void* G_lo, int ldg, const void* H_hi,
+                                      const void* H_lo, int ldh, long long n, int V, int J, float* dW,
+                                      const float* rowscale, float* db, int max_ctas, b200_stream_t stream) {
+  B200_CHECK_ARG(G_lo && H_lo && db, "b200_joint_dw_split_db: null pointer");
+  return joint_dw_impl(G_hi, G_lo, ldg, H_hi, H_lo, ldh, n, V, J, dW, rowscale, db, max_ctas, stream);
 }

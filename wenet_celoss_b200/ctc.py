@@ -134,11 +134,11 @@ class _FusedCtcFn(torch.autograd.Function):
             dW = torch.zeros(V, E, dtype=torch.float32, device=dev)
             db = torch.zeros(V, dtype=torch.float32, device=dev)
             dhs = torch.empty(B, T, E, dtype=torch.float32, device=dev)
-            _lib.call("b200_joint_dw_split", ptr(G_hi), ptr(G_lo), i32(ldg), ptr(hs_hi), ptr(hs_lo), i32(E),
-                      _i64(rows), i32(V), i32(E), ptr(dW), i32(0), st)
+            # d ctc_lo.weight and, from the same operand tiles, d ctc_lo.bias (column sums of G)
+            _lib.call("b200_joint_dw_split_db", ptr(G_hi), ptr(G_lo), i32(ldg), ptr(hs_hi), ptr(hs_lo), i32(E),
+                      _i64(rows), i32(V), i32(E), ptr(dW), None, ptr(db), i32(0), st)
             _lib.call("b200_split_gemm_nn", ptr(G_hi), ptr(G_lo), i32(ldg), ptr(w_hi), ptr(w_lo), _i64(rows),
                       i32(V), i32(E), ptr(dhs), i32(0), st)
-            _lib.call("b200_colsum_split", ptr(G_hi), ptr(G_lo), _i64(rows), i32(V), _i64(ldg), ptr(db), st)
         dt_h, dt_w, dt_b = ctx.in_dtypes
         return dhs.to(dt_h), dW.to(dt_w), db.to(dt_b), None, None, None, None
 

@@ -427,10 +427,9 @@ class _FusedJointLossFp32Fn(torch.autograd.Function):
                           i32(mc), st)
                 _lib.call("b200_rnnt_fixup", ptr(cf), ptr(xbe[b0:b1]), ptr(tg[b0:b1]), i32(b1 - b0), i32(T),
                           i32(U1), i32(V), i32(blank), ptr(G_hi), ptr(G_lo), _i64(ldg), st)
-                _lib.call("b200_colsum_split", ptr(G_hi), ptr(G_lo), _i64(n), i32(V), _i64(ldg), ptr(db), st)
-                if own:
-                    _lib.call("b200_joint_dw_split", ptr(G_hi), ptr(G_lo), i32(ldg), ptr(H_hi), ptr(H_lo),
-                              i32(J), _i64(n), i32(V), i32(J), ptr(dW), i32(mc), st)
+                if own:  # d b: column sums of G taken inside the dW kernel
+                    _lib.call("b200_joint_dw_split_db", ptr(G_hi), ptr(G_lo), i32(ldg), ptr(H_hi), ptr(H_lo),
+                              i32(J), _i64(n), i32(V), i32(J), ptr(dW), None, ptr(db), i32(mc), st)
                     _lib.call("b200_joint_dh_split", ptr(G_hi), ptr(G_lo), i32(ldg), ptr(w_hi), ptr(w_lo),
                               ptr(H_hi), ptr(H_lo), i32(J), i32(b1 - b0), i32(T), i32(U1), i32(V), i32(J),
                               ptr(logit_lengths[b0:b1]), ptr(target_lengths[b0:b1]), ptr(de[b0:b1]),
@@ -439,6 +438,7 @@ class _FusedJointLossFp32Fn(torch.autograd.Function):
                     Gf = G_hi[:n, :V].float() + G_lo[:n, :V].float()
                     Hf = H_hi.float() + H_lo.float()
                     dW += Gf.t() @ Hf
+                    db += Gf.sum(0)
                     dz = ((Gf @ w32) * (1 - Hf * Hf)).view(b1 - b0, T, U1, J)
                     de[b0:b1] = dz.sum(2)
                     dp[b0:b1] = dz.sum(1)
@@ -472,10 +472,8 @@ class _FusedJointLossFp32Fn(torch.autograd.Function):
             db = torch.zeros(V, dtype=torch.float32, device=dev)
             de = torch.zeros(B, T, J, dtype=torch.float32, device=dev)
             dp = torch.zeros(B, U1, J, dtype=torch.float32, device=dev)
-            _lib.call("b200_colsum_split_w", ptr(P_hi), ptr(P_lo), _i64(ncells), i32(V), _i64(ldg), ptr(rowscale),
-                      ptr(db), st)
-            _lib.call("b200_joint_dw_split", ptr(P_hi), ptr(P_lo), i32(ldg), ptr(Hs_hi), ptr(Hs_lo), i32(J),
-                      _i64(ncells), i32(V), i32(J), ptr(dW), i32(mc), st)
+            _lib.call("b200_joint_dw_split_db", ptr(P_hi), ptr(P_lo), i32(ldg), ptr(Hs_hi), ptr(Hs_lo), i32(J),
+                      _i64(ncells), i32(V), i32(J), ptr(dW), ptr(rowscale), ptr(db), i32(mc), st)
             _lib.call("b200_joint_dh_split_scaled", ptr(P_hi), ptr(P_lo), i32(ldg), ptr(w_hi), ptr(w_lo), ptr(H_hi),
                       ptr(H_lo), i32(J), ptr(rowscale), i32(B), i32(T), i32(U1), i32(V), i32(J),
                       ptr(logit_lengths), ptr(target_lengths), ptr(de), ptr(dp), i32(mc), st)
