@@ -35,9 +35,14 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t addr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
   return r;
 }
+// Arrive on an mbarrier of another CTA of the cluster ("accumulator drained": epilogue -> the leader's MMA
+// warp).  Default qualifiers = release at CTA scope: the hand-over is ordered by tcgen05.fence::before /
+// after_thread_sync around it, no memory written by this thread is read by the waiter.  With
+// .release.cluster the arrive first waits until every earlier store / reduction / TMA-staged write of the
+// thread is visible cluster-wide: ncu on split_gemm<EXP> showed 26 % of all warp samples on that membar
+// (ERRBAR + SYNCS.ARRIVE: ~2 us per arrive behind outstanding stores).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr)
-               : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load of one box into THIS CTA's shared memory; completion bytes go to the mbarrier at
 // cluster address `bar` (the leader CTA's) - the pair's MMA consumes both CTAs' stages
