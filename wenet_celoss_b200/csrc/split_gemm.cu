@@ -199,9 +199,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     const uint32_t tmem_empty0 = map_to_cta(ptx::smem_u32(&bars->tmem_empty[0]), 0);
     const uint64_t o_policy = ptx::l2_policy_evict_first();
     int acc = 0, acc_ph = 0;
-    auto bias_at = [&](int n, int c) {  // log2 domain; classes >= N are -inf
+    // raw value: the conversion to the log2 domain happens at the use, one chunk later (a multiply right
+    // behind the load waited for it on the spot - a quarter of the epilogue's stall samples in ncu);
+    // classes >= N are -inf
+    auto bias_at = [&](int n, int c) {
       const int col = n * kTileN + half * 128 + c * 32 + lane;
-      return col < P.N ? __ldg(P.bias + col) * kLog2e : -INFINITY;
+      return col < P.N ? __ldg(P.bias + col) : -INFINITY;
     };
     float bnext = bias_at(0, 0);
     constexpr bool kStats = MODE == MODE_LSE || MODE == MODE_EXPLSE;
@@ -231,7 +234,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
           ptx::tmem_ld32(lane_addr + (uint32_t)acc * kTileN + c * 32, r);
           // this chunk's bias into the warp's slot (loaded one chunk ahead), the next one into a register
           __syncwarp();
-          bias_w[lane] = bnext;
+          bias_w[lane] = bnext * kLog2e;
           __syncwarp();
           {
             int nn = n, cc = c + 1;
