@@ -490,6 +490,19 @@ int b200_ctc_forced_align(const float* logp, const int64_t* ys_pad, const int32_
                           int32_t* alignment, void* workspace, size_t ws_bytes,
                           b200_stream_t stream);
 
+/* b200_ctc_forced_align without a caller workspace and without any allocation.  No counterpart in the
+ * reference: added for callers that cannot call cudaMalloc (CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  The back-pointers live in a static
+ * device array of b200_ctc_forced_align_static_max_bytes() = 32 MiB that every GPU loading the library
+ * holds until exit; B*T*(2*Lmax+1)*2 bytes beyond that are rejected (B200_ERR_ARG).  All calls on a
+ * device share the array: calls that overlap on the GPU race - serialise them or use the workspace form.
+ * Nothing in the array has to start at zero (every back-pointer read was written by the same launch).
+ * Same inputs, outputs and results as b200_ctc_forced_align. */
+size_t b200_ctc_forced_align_static_max_bytes(void);
+int b200_ctc_forced_align_static(const float* logp, const int64_t* ys_pad, const int32_t* hlens,
+                                 const int32_t* ys_lens, int B, int T, int V, int Lmax, int blank,
+                                 int32_t* alignment, b200_stream_t stream);
+
 /* ---- Hot-word cross-entropy loss ------------------------------------------------
  * replaces self.hw_criterion = nn.CrossEntropyLoss() (wenet/transducer/transducer.py:66) as
  * applied at :170-200: logits [B, C, U] fp32 (class dimension 1), labels [B, U] int64, mean over

@@ -125,3 +125,73 @@ extern "C" int b200_ctc_forced_align(const float* logp, const int64_t* ys_pad, c
   B200_CHECK_LAUNCH("ctc_forced_align_kernel");
   return B200_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops,
+// harnesses that forbid it).  The back-pointer scratch [B,T,2*Lmax+1] int16 lives in a file-scope
+// device array of fixed size; every GPU that loads the library holds these bytes until exit.
+//   * limit: B * T * (2*Lmax+1) * 2 bytes <= B200_CTC_FORCED_ALIGN_STATIC_MAX_BYTES (32 MiB;
+//     the cfg5 shape B=64, T=1000, Lmax=100 needs 25.7 MB); larger problems are rejected;
+//   * every call on a device shares the one array: calls that overlap on the GPU (two streams,
+//     two host threads) race on it - serialise them, or use b200_ctc_forced_align with an own
+//     workspace.  The array keeps the previous call's contents; nothing has to start at zero:
+//     the backtrack reads only back-pointers path[t, s], 1 <= t < T_b, s < S_b, and the forward
+//     sweep of the same launch has written every one of them;
+//   * in host code the array's NAME is a host-side stand-in, not a device address: the address is
+//     taken with cudaGetSymbolAddress, once per device, with that device current.
+// ---------------------------------------------------------------------------------------------
+namespace b200 {
+namespace al {
+constexpr size_t kStaticScratchBytes = (size_t)32 << 20;
+static __device__ __align__(256) unsigned char g_align_scratch[kStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+static void* g_scratch_ptr[kMaxDevices];  // device address of g_align_scratch per device, nullptr = not yet asked
+}  // namespace al
+}  // namespace b200
+
+extern "C" size_t b200_ctc_forced_align_static_max_bytes(void) { return al::kStaticScratchBytes; }
+
+extern "C" int b200_ctc_forced_align_static(const float* logp, const int64_t* ys_pad, const int32_t* hlens,
+                                            const int32_t* ys_lens, int B, int T, int V, int Lmax, int blank,
+                                            int32_t* alignment, b200_stream_t stream) {
+  B200_CHECK_ARG(logp && ys_pad && hlens && ys_lens && alignment, "b200_ctc_forced_align_static: null pointer");
+  B200_CHECK_ARG(B > 0 && T > 0 && V > 0 && Lmax > 0,
+                 "b200_ctc_forced_align_static: bad shape B=%d T=%d V=%d Lmax=%d", B, T, V, Lmax);
+  B200_CHECK_ARG(blank >= 0 && blank < V, "b200_ctc_forced_align_static: blank %d out of range", blank);
+  const int Smax = 2 * Lmax + 1;
+  B200_CHECK_ARG(Smax <= 1024, "b200_ctc_forced_align_static: 2*Lmax+1 = %d > 1024 states not supported", Smax);
+  const size_t need = b200_ctc_forced_align_workspace_bytes(B, T, Lmax);
+  B200_CHECK_ARG(need <= al::kStaticScratchBytes,
+                 "b200_ctc_forced_align_static: B*T*(2*Lmax+1)*2 = %zu bytes of back-pointers exceed the static "
+                 "scratch of %zu bytes (use b200_ctc_forced_align with a caller workspace)",
+                 need, al::kStaticScratchBytes);
+  int dev = 0;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_CHECK_ARG(dev >= 0 && dev < al::kMaxDevices, "b200_ctc_forced_align_static: device %d not supported", dev);
+  // set-up, once per device, with that device current (a benign race: every thread would store the same value)
+  void* scratch = __atomic_load_n(&al::g_scratch_ptr[dev], __ATOMIC_ACQUIRE);
+  if (scratch == nullptr) {
+    B200_CHECK_CUDA(cudaGetSymbolAddress(&scratch, al::g_align_scratch));
+    B200_CHECK_ARG(scratch != nullptr, "b200_ctc_forced_align_static: no device address for the scratch array");
+    __atomic_store_n(&al::g_scratch_ptr[dev], scratch, __ATOMIC_RELEASE);
+  }
+  al::Params P{};
+  P.logp = logp;
+  P.ys = reinterpret_cast<const long long*>(ys_pad);
+  P.hlens = hlens;
+  P.ys_lens = ys_lens;
+  P.B = B;
+  P.T = T;
+  P.V = V;
+  P.Lmax = Lmax;
+  P.blank = blank;
+  P.path = reinterpret_cast<int16_t*>(scratch);
+  P.out = alignment;
+  const int threads = (Smax + 31) / 32 * 32;
+  const size_t smem = (size_t)3 * Smax * sizeof(float);
+  al::ctc_forced_align_kernel<<<B, threads, smem, (cudaStream_t)stream>>>(P);
+  B200_CHECK_LAUNCH("ctc_forced_align_kernel");
+  return B200_OK;
+}
