@@ -282,6 +282,24 @@ int b200_split_gemm_exp(const void* a_hi, const void* a_lo, long long rows, int 
                         const void* b_hi, const void* b_lo, int N, int ldb, const float* bias_pad,
                         const float* coef, void* g_hi, void* g_lo, long long ldg, int max_ctas,
                         b200_stream_t stream);
+/* b200_split_gemm_exp with a sparse term subtracted inside the epilogue: G = scale exp(x + c0) - sub, the
+ * whole CTC gradient w.r.t. the ctc_lo logits (autograd of log_softmax + CTCLoss, ctc.py:60-61) in one pass
+ * instead of b200_split_gemm_exp + b200_ctc_fixup (a read-modify-write of the label entries of G).
+ * b200_ctc_post writes the term: rows come in groups of group_rows = T (utterances);
+ *   words [B, ceil(V/32), 2] uint32: {bitmap over the classes: blank + the utterance's distinct valid labels,
+ *                                     number of set bits in the words before this one}
+ *   val   [B, Lmax + 1, T] fp32: val[b, rank(c), t] = scale_b * posterior(class c at frame t), rank(c) = set bits
+ *                                below c (entries of ranks the utterance does not use are never read).
+ * alpha / beta / frame_off / leader as b200_ctc_lattice wrote them; rows must be B * T. */
+int b200_ctc_post(const float* lp_ext, const float* alpha, const float* beta, const double* frame_off,
+                  const float* scale, const int64_t* ys_pad, const int32_t* hlens,
+                  const int32_t* ys_lens, const int32_t* leader, int B, int T, int V, int Lmax,
+                  int blank, uint32_t* words, float* val, b200_stream_t stream);
+int b200_split_gemm_exp_sub(const void* a_hi, const void* a_lo, long long rows, int K, int lda,
+                            const void* b_hi, const void* b_lo, int N, int ldb, const float* bias_pad,
+                            const float* coef, const uint32_t* sub_words, const float* sub_val,
+                            int group_rows, int nranks, void* g_hi, void* g_lo, long long ldg,
+                            int max_ctas, b200_stream_t stream);
 int b200_split_gemm_lsm(const void* a_hi, const void* a_lo, long long rows, int K, int lda,
                         const void* b_hi, const void* b_lo, int N, int ldb, const float* bias_pad,
                         const float* lse, float* out, long long ldo, int max_ctas,

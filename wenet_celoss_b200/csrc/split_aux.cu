@@ -377,6 +377,112 @@ ctc_fixup_kernel(const float* __restrict__ lp_ext, const float* __restrict__ alp
   }
 }
 
+// The sparse part of the CTC gradient, in the form the EXP-mode GEMM epilogue subtracts on the fly
+// (split_gemm.cu MODE_EXPSUB) instead of a read-modify-write pass over G (ctc_fixup_kernel above):
+//   words [B][nwords] {bitmap over the classes: blank + the utterance's distinct valid labels,
+//                      number of set bits in the words before this one}
+//   val   [B][Lmax + 1][T]: val[b][rank(c)][t] = scale_b * posterior(class c at frame t), rank(c) = set bits below c
+// (frame-minor, so that the 32 rows = frames of an epilogue warp read 128 contiguous bytes).
+// One CTA = 32 frames of one utterance: warps form the state posteriors of four rows each (occupancies merged
+// per class through the leader table in shared memory), then each (patching state, 32 frames) goes out as one
+// 128-byte line.  Rows beyond hlens / with scale 0 get zeros.
+constexpr int kPostFrames = 32;
+__global__ void __launch_bounds__(256)
+ctc_post_kernel(const float* __restrict__ lp_ext, const float* __restrict__ alpha, const float* __restrict__ beta,
+                const double* __restrict__ frame_off, const float* __restrict__ scale,
+                const long long* __restrict__ ys_pad, const int32_t* __restrict__ hlens,
+                const int32_t* __restrict__ ys_lens, const int32_t* __restrict__ leader, int Tm, int V, int Lmax,
+                int blank, int nwords, uint2* __restrict__ words, float* __restrict__ val) {
+  extern __shared__ float post_sm[];  // occ [32][Smax] | bitmap [nwords] | prefix [nwords]
+  const int Smax = 2 * Lmax + 1;
+  float* occ_all = post_sm;
+  uint32_t* bm = reinterpret_cast<uint32_t*>(post_sm + kPostFrames * Smax);
+  uint32_t* pre = bm + nwords;
+  const int b = blockIdx.y;
+  const int t0 = blockIdx.x * kPostFrames;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const float sc = scale[b];
+  const int hl = hlens[b];
+  const int S = 2 * ys_lens[b] + 1;
+  const int32_t* ld = leader + (long long)b * Smax;
+  const long long* ys = ys_pad + (long long)b * Lmax;
+  auto patch_class = [&](int s) -> int {  // class whose entry state s carries, -1: none
+    if (s == 0) return blank;
+    if (!(s & 1) || ld[s] != s) return -1;
+    const long long c = ys[s >> 1];
+    return (c >= 0 && c < V && c != blank) ? (int)c : -1;
+  };
+  // class bitmap and its running popcount
+  for (int i = tid; i < nwords; i += 256) bm[i] = 0u;
+  __syncthreads();
+  for (int s = tid; s < S; s += 256) {
+    const int c = patch_class(s);
+    if (c >= 0) atomicOr(&bm[c >> 5], 1u << (c & 31));
+  }
+  __syncthreads();
+  if (warp == 0) {
+    const int chunk = (nwords + 31) / 32;
+    int cnt = 0;
+    for (int j = 0; j < chunk; ++j) {
+      const int w = lane * chunk + j;
+      if (w < nwords) cnt += __popc(bm[w]);
+    }
+    int incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += n;
+    }
+    int run = incl - cnt;
+    for (int j = 0; j < chunk; ++j) {
+      const int w = lane * chunk + j;
+      if (w < nwords) {
+        pre[w] = (uint32_t)run;
+        run += __popc(bm[w]);
+      }
+    }
+  }
+  // state posteriors of this warp's rows
+  const double* oa = frame_off + (long long)b * 2 * (Tm + 1);
+  for (int r = warp * 4; r < warp * 4 + 4; ++r) {
+    const int t = t0 + r;
+    float* occ = occ_all + r * Smax;
+    for (int s = lane; s < S; s += 32) occ[s] = 0.f;
+    if (t >= Tm || t >= hl || sc == 0.f) continue;
+    __syncwarp();
+    const float nl = (float)(oa[t] + oa[Tm + 1 + t] - oa[Tm]);
+    const long long rowi = (long long)b * Tm + t;
+    const float* al = alpha + rowi * Smax;
+    const float* be = beta + rowi * Smax;
+    const float* lp = lp_ext + rowi * Smax;
+    float occ_blank = 0.f;
+    for (int s = lane; s < S; s += 32) {
+      const float post = expf(al[s] + be[s] + nl - lp[s]);  // alpha*beta counts the emission at t twice
+      if (s & 1)
+        atomicAdd(&occ[ld[s]], post);
+      else
+        occ_blank += post;
+    }
+    occ_blank = warp_sum(occ_blank);
+    __syncwarp();
+    if (lane == 0) occ[0] = occ_blank;
+  }
+  __syncthreads();
+  if (blockIdx.x == 0)
+    for (int i = tid; i < nwords; i += 256) words[(long long)b * nwords + i] = make_uint2(bm[i], pre[i]);
+  // lane = frame, warps walk the patching states
+  const int t = t0 + lane;
+  if (t < Tm) {
+    float* vb = val + (long long)b * (Lmax + 1) * Tm + t;
+    for (int s = warp; s < S; s += 8) {
+      const int c = patch_class(s);
+      if (c < 0) continue;
+      const int rank = (int)pre[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+      vb[(long long)rank * Tm] = sc * occ_all[lane * Smax + s];
+    }
+  }
+}
+
 // grid (column blocks of 256, row slabs); thread = one column pair over a slab of rows
 __global__ void __launch_bounds__(128)
 colsum_split_kernel(const __nv_bfloat16* __restrict__ Ghi, const __nv_bfloat16* __restrict__ Glo, long long rows, int N,
@@ -497,6 +603,29 @@ extern "C" int b200_ctc_fixup(const float* lp_ext, const float* alpha, const flo
       lp_ext, alpha, beta, frame_off, scale, reinterpret_cast<const long long*>(ys_pad), hlens, ys_lens, leader, B, T, V,
       Lmax, blank, reinterpret_cast<__nv_bfloat16*>(G_hi), reinterpret_cast<__nv_bfloat16*>(G_lo), ldg);
   B200_CHECK_LAUNCH("ctc_fixup_kernel");
+  return B200_OK;
+}
+
+extern "C" int b200_ctc_post(const float* lp_ext, const float* alpha, const float* beta, const double* frame_off,
+                             const float* scale, const int64_t* ys_pad, const int32_t* hlens,
+                             const int32_t* ys_lens, const int32_t* leader, int B, int T, int V, int Lmax, int blank,
+                             uint32_t* words, float* val, b200_stream_t stream) {
+  B200_CHECK_ARG(lp_ext && alpha && beta && frame_off && scale && hlens && ys_lens && leader && words && val &&
+                     (Lmax == 0 || ys_pad),
+                 "b200_ctc_post: null pointer");
+  B200_CHECK_ARG(B > 0 && T > 0 && V > 0 && Lmax >= 0 && blank >= 0 && blank < V && 2 * Lmax + 1 <= 1024,
+                 "b200_ctc_post: bad shape B=%d T=%d V=%d Lmax=%d blank=%d", B, T, V, Lmax, blank);
+  B200_CHECK_ARG(((uintptr_t)words & 7) == 0, "b200_ctc_post: words must be 8-byte aligned");
+  const int Smax = 2 * Lmax + 1;
+  const int nwords = (V + 31) / 32;
+  const size_t smem = ((size_t)sa::kPostFrames * Smax + 2 * (size_t)nwords) * sizeof(float);
+  B200_CHECK_ARG(smem <= 200 * 1024, "b200_ctc_post: %zu bytes of shared memory needed (V=%d, Lmax=%d)", smem, V, Lmax);
+  B200_CHECK_CUDA(cudaFuncSetAttribute(sa::ctc_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  dim3 grid((T + sa::kPostFrames - 1) / sa::kPostFrames, B);
+  sa::ctc_post_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(
+      lp_ext, alpha, beta, frame_off, scale, reinterpret_cast<const long long*>(ys_pad), hlens, ys_lens, leader, T, V,
+      Lmax, blank, nwords, reinterpret_cast<uint2*>(words), val);
+  B200_CHECK_LAUNCH("ctc_post_kernel");
   return B200_OK;
 }
 

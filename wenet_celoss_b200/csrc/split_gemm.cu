@@ -49,7 +49,7 @@ constexpr int kXchgBytes = 128 * 8;
 constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + kBiasBytes + kXchgBytes + 256;
 static_assert(kSmemBytes <= 232448, "shared memory budget");
 
-enum { MODE_LSE = 0, MODE_EXP = 1, MODE_LSM = 2, MODE_EXPLSE = 3 };
+enum { MODE_LSE = 0, MODE_EXP = 1, MODE_LSM = 2, MODE_EXPLSE = 3, MODE_EXPSUB = 4 };
 constexpr float kNrMaxLog2Bound = 60.f;  // = jf::kNrMaxLog2Bound (joint_fused.cu)
 
 struct Params {
@@ -59,6 +59,12 @@ struct Params {
   float* lse;          // MODE_LSE out / MODE_LSM in, natural log
   const float4* coef;  // MODE_EXP: {c0, -, -, scale} per row
   const float* logit_bound;  // MODE_EXPLSE: device scalar max_v(|W_v|_1 + |b_v|)
+  // MODE_EXPSUB: G = scale exp(x + c0) - sub, a sparse term per (row, class) in the layout of b200_ctc_post:
+  // rows come in groups of group_rows (utterances); per group a bitmap over the classes with running popcounts,
+  // and the values [group][rank][row in group]
+  const uint2* sub_words;    // [groups][nwords] {bitmap word, set bits before it}
+  const float* sub_val;      // [groups][nranks][group_rows]
+  int group_rows, nranks, nwords;
 };
 
 struct Bars {
@@ -210,20 +216,37 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     constexpr bool kStats = MODE == MODE_LSE || MODE == MODE_EXPLSE;
     const bool nr_ok = MODE == MODE_EXPLSE && P.logit_bound != nullptr &&
                        __ldg(P.logit_bound) * kLog2e < kNrMaxLog2Bound;
-    const bool stores = MODE == MODE_EXP || MODE == MODE_LSM || nr_ok;
+    constexpr bool kExp = MODE == MODE_EXP || MODE == MODE_EXPSUB;
+    const bool stores = kExp || MODE == MODE_LSM || nr_ok;
     for (int mt = pair_id; mt < mtiles; mt += npairs) {
       const long long row = (long long)mt * 256 + rank * 128 + rrow;
       const bool in_range = row < P.rows;
       float m2 = nr_ok ? 0.f : kNegBig, ssum = 0.f;  // MODE_LSE / MODE_EXPLSE
       float c0 = -INFINITY, scale = 0.f;      // MODE_EXP (log2 domain) / MODE_LSM (c0 = -lse2)
-      if (MODE == MODE_EXP && in_range) {
+      if (kExp && in_range) {
         const float4 c = __ldg(P.coef + row);
         scale = c.w;
         c0 = c.x * kLog2e;
       }
       if (MODE == MODE_LSM && in_range) c0 = -__ldg(P.lse + row) * kLog2e;
+      // MODE_EXPSUB: this row's group (utterance): bitmap words and values; rows with scale 0 subtract nothing.
+      // The bitmap word of a chunk is loaded one chunk ahead (like the bias), the first value it selects at the
+      // top of its chunk, under the tcgen05.ld / store-drain waits.
+      const uint2* sub_w = nullptr;
+      const float* sub_v = nullptr;
+      uint2 wnext = make_uint2(0u, 0u);
+      auto word_at = [&](int n, int c) {
+        const int wi = n * (kTileN / 32) + half * 4 + c;
+        return (sub_w != nullptr && wi < P.nwords) ? __ldg(sub_w + wi) : make_uint2(0u, 0u);
+      };
+      if (MODE == MODE_EXPSUB && in_range && scale != 0.f) {
+        const long long grp = row / P.group_rows;
+        sub_w = P.sub_words + grp * P.nwords;
+        sub_v = P.sub_val + grp * P.nranks * P.group_rows + (row - grp * P.group_rows);
+        wnext = word_at(0, 0);
+      }
       // scale >= 0 on every row of the warp: move it into the exponent (log2(0) = -inf: exact zeros)
-      const bool pos = MODE == MODE_EXP && __all_sync(0xffffffffu, scale >= 0.f);
+      const bool pos = kExp && __all_sync(0xffffffffu, scale >= 0.f);
       const float c0s = pos ? c0 + log2f(scale) : c0;
       for (int n = 0; n < NT; ++n) {
         ptx::mbar_wait(ptx::smem_u32(&bars->tmem_full[acc]), (uint32_t)acc_ph);
@@ -243,6 +266,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
               nn = (n + 1 == NT) ? 0 : n + 1;
             }
             bnext = bias_at(nn, cc);
+          }
+          uint2 wp = make_uint2(0u, 0u);
+          float d0 = 0.f;
+          if (MODE == MODE_EXPSUB) {
+            wp = wnext;
+            if (c + 1 < 4 || n + 1 < NT) wnext = word_at(c + 1 < 4 ? n : n + 1, c + 1 < 4 ? c + 1 : 0);
+            if (wp.x) d0 = __ldg(sub_v + (long long)wp.y * P.group_rows);
           }
           if (stores) {  // the previous chunk's store must have drained the staging tile
             if (lane == 0) ptx::bulk_wait_group_read0();
@@ -275,7 +305,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
             for (int i = 0; i < 32; ++i) a4[i & 3] += ex2_approx(t[i] - mn);
             ssum = ssum * ex2_approx(m2 - mn) + ((a4[0] + a4[1]) + (a4[2] + a4[3]));
             m2 = mn;
-          } else if (MODE == MODE_EXP || MODE == MODE_EXPLSE) {
+          } else if (kExp || MODE == MODE_EXPLSE) {
             if (MODE == MODE_EXPLSE) {  // Pt = 2^t (bounded logits), summed for lse on the way
               float a4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -290,6 +320,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
             } else {
 #pragma unroll
               for (int i = 0; i < 32; ++i) t[i] = scale * ex2_approx(t[i] + c0s);
+            }
+            if (MODE == MODE_EXPSUB && __any_sync(0xffffffffu, wp.x != 0u)) {
+              // the selected classes of this chunk: bit k of the word = column col0 + k, values in rank order.
+              // The register index is compile-time only, hence a compare-select sweep per set bit (1.4 bits on
+              // average in a word that has any; the lanes of a warp share the word unless they straddle groups)
+              uint32_t w = wp.x;
+              int kk = w ? __ffs(w) - 1 : -1;
+#pragma unroll
+              for (int i = 0; i < 32; ++i) t[i] -= (i == kk) ? d0 : 0.f;
+              w &= w - 1u;
+              long long rk = (long long)wp.y + 1;
+              while (__any_sync(0xffffffffu, w != 0u)) {
+                kk = w ? __ffs(w) - 1 : -1;
+                const float d = w ? __ldg(sub_v + rk * P.group_rows) : 0.f;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) t[i] -= (i == kk) ? d : 0.f;
+                w &= w - 1u;
+                ++rk;
+              }
             }
             // split: hi = bf16(v), lo = bf16(v - hi); two 32 x 64-byte tiles (SWIZZLE_64B: 16-byte
             // piece j of row r at j ^ ((r >> 1) & 3)), written by two TMA stores
@@ -427,7 +476,7 @@ int sg_launch(const CUtensorMap* m, const sg::Params& P, int max_ctas, cudaStrea
 
 int sg_run(int mode, const void* a_hi, const void* a_lo, long long rows, int K, int lda, const void* b_hi,
            const void* b_lo, int N, int ldb, const float* bias_pad, float* lse, const float* coef, void* o_hi,
-           void* o_lo, long long ldo, int max_ctas, b200_stream_t stream) {
+           void* o_lo, long long ldo, int max_ctas, b200_stream_t stream, const sg::Params* sub = nullptr) {
   B200_CHECK_ARG(a_hi && b_hi && bias_pad, "b200_split_gemm: null pointer");
   B200_CHECK_ARG((a_lo == nullptr) == (b_lo == nullptr), "b200_split_gemm: a_lo and b_lo go together");
   B200_CHECK_ARG(rows > 0 && N > 0 && K > 0 && K % 8 == 0, "b200_split_gemm: bad shape rows=%lld N=%d K=%d (K %% 8)",
@@ -468,13 +517,25 @@ int sg_run(int mode, const void* a_hi, const void* a_lo, long long rows, int K, 
     B200_CHECK_ARG(lse, "b200_split_gemm_lse: null lse");
     return split ? sg_launch<sg::MODE_LSE, 3>(m, P, max_ctas, st) : sg_launch<sg::MODE_LSE, 1>(m, P, max_ctas, st);
   }
-  if (mode == sg::MODE_EXP) {
+  if (mode == sg::MODE_EXP || mode == sg::MODE_EXPSUB) {
     B200_CHECK_ARG(coef && o_hi && (!split || o_lo), "b200_split_gemm_exp: null pointer");
     B200_CHECK_ARG(((uintptr_t)coef & 15) == 0 && ldo >= N && ldo % 8 == 0 &&
                        (((uintptr_t)o_hi | (uintptr_t)o_lo) & 15) == 0,
                    "b200_split_gemm_exp: coef / G must be 16-byte aligned, ldg=%lld >= N and a multiple of 8", ldo);
     if (int rc = sg_map(&m[4], o_hi, bf, 2, rows, N, ldo * 2, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B)) return rc;
     if (int rc = sg_map(&m[5], split ? o_lo : o_hi, bf, 2, rows, N, ldo * 2, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B)) return rc;
+    if (mode == sg::MODE_EXPSUB) {
+      B200_CHECK_ARG(sub && sub->sub_words && sub->sub_val && sub->group_rows > 0 && sub->nranks > 0 &&
+                         sub->nwords == (N + 31) / 32 && rows % sub->group_rows == 0,
+                     "b200_split_gemm_exp_sub: bad sparse term (rows must be whole groups, nwords = ceil(N / 32))");
+      P.sub_words = sub->sub_words;
+      P.sub_val = sub->sub_val;
+      P.group_rows = sub->group_rows;
+      P.nranks = sub->nranks;
+      P.nwords = sub->nwords;
+      return split ? sg_launch<sg::MODE_EXPSUB, 3>(m, P, max_ctas, st)
+                   : sg_launch<sg::MODE_EXPSUB, 1>(m, P, max_ctas, st);
+    }
     return split ? sg_launch<sg::MODE_EXP, 3>(m, P, max_ctas, st) : sg_launch<sg::MODE_EXP, 1>(m, P, max_ctas, st);
   }
   B200_CHECK_ARG(lse && o_hi, "b200_split_gemm_lsm: null pointer");
@@ -500,6 +561,24 @@ extern "C" int b200_split_gemm_exp(const void* a_hi, const void* a_lo, long long
                                    b200_stream_t stream) {
   return sg_run(sg::MODE_EXP, a_hi, a_lo, rows, K, lda, b_hi, b_lo, N, ldb, bias_pad, nullptr, coef, g_hi, g_lo, ldg,
                 max_ctas, stream);
+}
+
+// G = scale exp(x + c0) - sub: the CTC gradient w.r.t. the ctc_lo logits in one pass (softmax part from the GEMM,
+// state posteriors of the label classes from b200_ctc_post), no read-modify-write of G afterwards
+extern "C" int b200_split_gemm_exp_sub(const void* a_hi, const void* a_lo, long long rows, int K, int lda,
+                                       const void* b_hi, const void* b_lo, int N, int ldb, const float* bias_pad,
+                                       const float* coef, const uint32_t* sub_words, const float* sub_val,
+                                       int group_rows, int nranks, void* g_hi, void* g_lo, long long ldg,
+                                       int max_ctas, b200_stream_t stream) {
+  B200_CHECK_ARG(((uintptr_t)sub_words & 7) == 0, "b200_split_gemm_exp_sub: sub_words must be 8-byte aligned");
+  sg::Params sub{};
+  sub.sub_words = reinterpret_cast<const uint2*>(sub_words);
+  sub.sub_val = sub_val;
+  sub.group_rows = group_rows;
+  sub.nranks = nranks;
+  sub.nwords = (N + 31) / 32;
+  return sg_run(sg::MODE_EXPSUB, a_hi, a_lo, rows, K, lda, b_hi, b_lo, N, ldb, bias_pad, nullptr, coef, g_hi, g_lo,
+                ldg, max_ctas, stream, &sub);
 }
 
 // lse AND Pt = exp(x) (split) from one pass: the training forward of the no-recompute backward, fp32 mode

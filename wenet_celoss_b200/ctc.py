@@ -117,7 +117,7 @@ class _FusedCtcFn(torch.autograd.Function):
         with torch.cuda.device(dev):
             st = _lib.stream_handle(dev)
             scale = dy.detach().to(torch.float32).contiguous()
-            # G = scale_b * softmax for t < hlens[b] (zero rows beyond), then minus the state posteriors
+            # G = scale_b * softmax for t < hlens[b] (zero rows beyond) minus the state posteriors
             live = torch.arange(T, device=dev)[None, :] < hlens[:, None]
             coef = torch.zeros(B, T, 4, dtype=torch.float32, device=dev)
             coef[..., 0] = -lse
@@ -125,12 +125,16 @@ class _FusedCtcFn(torch.autograd.Function):
             ldg = (V + 15) // 16 * 16
             G_hi = torch.empty(rows, ldg, dtype=torch.bfloat16, device=dev)
             G_lo = torch.empty_like(G_hi)
-            _lib.call("b200_split_gemm_exp", ptr(hs_hi), ptr(hs_lo), _i64(rows), i32(E), i32(E), ptr(w_hi),
-                      ptr(w_lo), i32(V), i32(E), ptr(bias_pad), ptr(coef), ptr(G_hi), ptr(G_lo), _i64(ldg),
-                      i32(0), st)
-            _lib.call("b200_ctc_fixup", ptr(lp_ext), ptr(alpha), ptr(beta), ptr(frame_off), ptr(scale),
-                      ptr(ys_pad), ptr(hlens), ptr(ys_lens), ptr(leader), i32(B), i32(T), i32(V), i32(Lmax),
-                      i32(ctx.blank), ptr(G_hi), ptr(G_lo), _i64(ldg), st)
+            # the sparse part (state posteriors of blank and the labels) goes into the EXP epilogue: one pass over G
+            nwords = (V + 31) // 32
+            words = torch.empty(B, nwords, 2, dtype=torch.int32, device=dev)
+            val = torch.empty(B, Lmax + 1, T, dtype=torch.float32, device=dev)
+            _lib.call("b200_ctc_post", ptr(lp_ext), ptr(alpha), ptr(beta), ptr(frame_off), ptr(scale), ptr(ys_pad),
+                      ptr(hlens), ptr(ys_lens), ptr(leader), i32(B), i32(T), i32(V), i32(Lmax), i32(ctx.blank),
+                      ptr(words), ptr(val), st)
+            _lib.call("b200_split_gemm_exp_sub", ptr(hs_hi), ptr(hs_lo), _i64(rows), i32(E), i32(E), ptr(w_hi),
+                      ptr(w_lo), i32(V), i32(E), ptr(bias_pad), ptr(coef), ptr(words), ptr(val), i32(T),
+                      i32(Lmax + 1), ptr(G_hi), ptr(G_lo), _i64(ldg), i32(0), st)
             dW = torch.zeros(V, E, dtype=torch.float32, device=dev)
             db = torch.zeros(V, dtype=torch.float32, device=dev)
             dhs = torch.empty(B, T, E, dtype=torch.float32, device=dev)
