@@ -66,12 +66,26 @@ def stream_handle(device=None) -> c_void_p:
     return c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
+# Measurement hook (bench.py, scripts/): while TRACE is a list, every entry-point call is bracketed by
+# two CUDA events on the current stream - the stream the wrappers hand to the kernels - and
+# (name, start, end) is appended, so a caller can read per-kernel times INSIDE a real step.
+TRACE = None
+
+
 def call(fn_name: str, *args) -> None:
     """Invoke an int-returning entry point and raise on a non-zero status."""
     L = lib()
     fn = getattr(L, fn_name)
     fn.restype = c_int
+    trace = TRACE
+    if trace is not None:
+        ev0 = torch.cuda.Event(enable_timing=True)
+        ev0.record()
     rc = fn(*args)
+    if trace is not None:
+        ev1 = torch.cuda.Event(enable_timing=True)
+        ev1.record()
+        trace.append((fn_name, ev0, ev1))
     if rc != 0:
         msg = L.b200_last_error().decode("utf-8", "replace")
         raise B200Error(f"{fn_name} failed (status {rc}): {msg}")

@@ -4,9 +4,13 @@
 //   (wenet/transducer/search/prefix_beam_search.py:42-148; one utterance, Python lists,
 //    N*N .item() syncs per frame) for a whole batch.  Per frame i and utterance b with
 //    N live hypotheses ("rows", row = b*beam + j):
-//   lstm / pred_z   predictor.forward_step on every row from the row's cached state
-//                   (prefix_beam_search.py:31-40, predictor.py:180-200) and the joint's
-//                   hidden z = tanh(enc_ffn(enc)[i] + pred_ffn(pred))       (joint.py:55-68)
+//   lstm / pred     predictor.forward_step from the row's cached state (prefix_beam_search.py:31-40,
+//                   predictor.py:180-200) and pred_ffn of its output (joint.py:57) - only for the rows
+//                   whose hypothesis was EXTENDED by the previous frame ("dirty" rows).  The reference
+//                   repeats the step for every hypothesis on every frame, but a hypothesis kept through
+//                   a blank has the same last token and the same cache, i.e. the same step: its result
+//                   (new state, projected output) is carried with the row instead (bit-identical).
+//   z               z = tanh(enc_ffn(enc)[i] + pred_ffn(pred)) for every live row      (joint.py:55-68)
 //   logits          ffn_out(z) for all rows x V                                 (joint.py:69)
 //   topk            log_softmax, shallow fusion log(tw*exp(lp) + cw*exp(ctc_lp[i])) in fp32
 //                   (:99-101) and a warp-level top-k (k = beam, sorted descending, :104)
@@ -54,14 +58,16 @@ struct State {
   int32_t* n_beam;     // [2][B]
   float* cache_h;      // [2][L][B*beam][H]  state BEFORE consuming the row's last token
   float* cache_c;
-  float* new_h;        // [L][B*beam][H]     state AFTER consuming it (this frame)
+  float* new_h;        // [2][L][B*beam][H]  state AFTER consuming it (computed once, then carried)
   float* new_c;
+  float* pproj;        // [2][B*beam][J]     pred_ffn(new_h of the last layer) + bias, carried likewise
   float* z;            // [B*beam][J]
   float* logits;       // [B*beam][V]
   float* topv;         // [B*beam][beam]
   int32_t* topi;       // [B*beam][beam]
-  int32_t* row_list;   // [2][B*beam]
-  int32_t* n_rows;     // [2]
+  int32_t* row_list;   // [2][B*beam]  live rows
+  int32_t* dirty_list; // [2][B*beam]  live rows whose predictor step has not been computed yet
+  int32_t* n_rows;     // [4]: live rows of set 0 / 1, dirty rows of set 0 / 1
 };
 
 __device__ __forceinline__ unsigned long long hash_push(unsigned long long h, int tok) {
@@ -75,6 +81,8 @@ __global__ void init_kernel(State S, int blank) {
   if (b == 0) {
     S.n_rows[0] = 0;
     S.n_rows[1] = 0;
+    S.n_rows[2] = 0;
+    S.n_rows[3] = 0;
   }
   if (b >= S.B) return;
   const int row = b * S.beam;
@@ -89,7 +97,10 @@ __global__ void init_kernel(State S, int blank) {
 __global__ void init_rows_kernel(State S) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= S.B) return;
-  if (S.lens[b] > 0) S.row_list[atomicAdd(&S.n_rows[0], 1)] = b * S.beam;
+  if (S.lens[b] > 0) {
+    S.row_list[atomicAdd(&S.n_rows[0], 1)] = b * S.beam;
+    S.dirty_list[atomicAdd(&S.n_rows[2], 1)] = b * S.beam;  // the seed hypothesis has no predictor step yet
+  }
 }
 
 #include "beam_gemm.inc"

@@ -165,10 +165,14 @@ class _FusedJointLossFn(torch.autograd.Function):
             if nr:
                 lat = torch.empty(3, B, T, U1, dtype=torch.float32, device=dev)
                 lse, lpb, lpe = lat.unbind(0)
-                _lib.call("b200_joint_fwd_p", ptr(e32), ptr(p32), ptr(w_bf16), ptr(bias_pad), ptr(targets),
+                # H = tanh(e + p), then the tensor-core kernel on the ready H (what b200_joint_fwd_p does in
+                # one call; two calls so that a trace of the entry points sees the two kernels separately)
+                st = _lib.stream_handle(dev)
+                _lib.call("b200_joint_h", ptr(e32), ptr(p32), i32(B), i32(T), i32(U1), i32(J), ptr(H), i32(J), st)
+                _lib.call("b200_joint_fwd_p_h", ptr(e32), ptr(p32), ptr(w_bf16), ptr(bias_pad), ptr(targets),
                           ptr(logit_lengths), ptr(target_lengths), i32(B), i32(T), i32(U1), i32(V), i32(J),
                           i32(blank), ptr(lse), ptr(lpb), ptr(lpe), ptr(bound), ptr(H), i32(J), ptr(Pt),
-                          i32(ldg), i32(max_ctas), _lib.stream_handle(dev))
+                          i32(ldg), i32(max_ctas), st)
             else:
                 lse, lpb, lpe = joint_logprobs(e32, p32, w_bf16, bias_pad, targets, logit_lengths,
                                                target_lengths, V, blank, max_ctas=max_ctas,
