@@ -285,3 +285,32 @@ def test_beam10_cfg4_shape_vs_oracle():
             continue
         np.testing.assert_allclose([s.score for s in beams[b]], [s.score for s in want], rtol=1e-5)
         assert len(want[0].hyp) > 3
+
+
+@pytest.mark.parametrize("flat,weights", [(False, (0.3, 0.7)), (True, (0.3, 0.7)), (False, (0.0, 1.0)),
+                                          (False, (1.0, 0.0))])
+def test_beam_bounded_topk_equals_full_evaluation(flat, weights, monkeypatch):
+    """The beam's top-k evaluates the fused score only where a cheap upper bound reaches the K-th best
+    sampled score (csrc/beam_select.inc); B200_BEAM_TOPK_FULL=1 evaluates every vocabulary entry.  Both
+    must give the same n-best lists and bit-identical scores: on the bench's peaked model, on a flat one
+    (every entry survives the bound: more than the survivor cap, i.e. the fallback inside the default
+    path), and with one of the two weights zero (log 0 in the bound)."""
+    from wenet_celoss_b200 import prefix_beam_search_batch
+    cfg, m, _ = _bench_search_model()
+    if flat:
+        with torch.no_grad():
+            m.joint.ffn_out.weight.mul_(1e-3)
+            m.joint.ffn_out.bias.zero_()
+    g = torch.Generator().manual_seed(7)
+    B, T = 3, 60
+    enc = (torch.randn(B, T, cfg["E"], generator=g) * 2.0).to(DEV)
+    lens = torch.tensor([60, 47, 60], dtype=torch.int32, device=DEV)
+    m = m.to(DEV)
+    cw, tw = weights
+    out = {}
+    for full in ("0", "1"):
+        monkeypatch.setenv("B200_BEAM_TOPK_FULL", full)
+        beams = prefix_beam_search_batch(m, enc, lens, beam_size=10, ctc_weight=cw, transducer_weight=tw)
+        out[full] = [[(tuple(s.hyp), s.score) for s in bb] for bb in beams]
+    assert out["0"] == out["1"]
+    assert all(len(bb) > 0 for bb in out["0"])
