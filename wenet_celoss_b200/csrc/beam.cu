@@ -76,6 +76,18 @@ __device__ __forceinline__ unsigned long long hash_push(unsigned long long h, in
 }
 __device__ __forceinline__ float sigm(float x) { return 1.f / (1.f + expf(-x)); }
 
+// Programmatic dependent launch (beam_host.inc launches the frame kernels with
+// cudaLaunchAttributeProgrammaticStreamSerialization): FIRST statement of every frame kernel.  The next kernel
+// of the stream is set up while this one runs and starts as soon as this grid's CTAs have exited (no explicit
+// trigger: with griddepcontrol.launch_dependents at the top the waiting CTAs of up to six later kernels sat on
+// the SMs' shared memory and registers and the decode got SLOWER, 656 vs 694 utt/s); the wait blocks until
+// the grid launched before this one has completed and its writes are visible, so nothing of a kernel's global
+// memory traffic moves ahead of its predecessor.  Measured: 694 -> 755 utt/s at cfg4 (launch gaps 18 -> 3 us
+// per frame).  B200_BEAM_NO_PDL=1 launches without the attribute.
+__device__ __forceinline__ void pdl_enter() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 __global__ void init_kernel(State S, int blank) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b == 0) {
