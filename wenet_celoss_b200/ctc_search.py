@@ -48,8 +48,10 @@ def ctc_prefix_beam_search_batch(ctc_probs: torch.Tensor, lens: torch.Tensor, be
         lens_h = out_len.cpu().tolist()
         scores = out_score.cpu().tolist()
         width = max(max(max(r) for r in lens_h), 1) if B else 1
-        toks = out_tok[:, :, :width].cpu().tolist()
-    return [[(tuple(toks[b][k][:lens_h[b][k]]), scores[b][k]) for k in range(n[b])] for b in range(B)]
+        toks = out_tok[:, :, :width].cpu().numpy()
+    # one flat .tolist() per hypothesis (a nested .tolist() of the padded [B, beam, width] block was 2/3 of
+    # the call at long prefixes)
+    return [[(tuple(toks[b, k, :lens_h[b][k]].tolist()), scores[b][k]) for k in range(n[b])] for b in range(B)]
 
 
 def _ctc_prefix_beam_search(self, speech: torch.Tensor, speech_lengths: torch.Tensor, beam_size: int,
