@@ -221,3 +221,57 @@ def test_hotword_greedy_full_dims_vs_oracle(mode):
                                     return_decisions=True)
     same = sum(hyps[b] == want[b][0] and (mode == "off" or dec[b] == want[b][1]) for b in range(B))
     assert same == B, (same, [(hyps[b][:8], want[b][0][:8]) for b in range(B)])
+
+
+@pytest.mark.parametrize("switch", ["B200_GREEDY_ROUND_KERNELS", "B200_GREEDY_NO_REPL", "B200_GATE_SINGLE_CTA"])
+@pytest.mark.parametrize("mode", [None, "on"])
+def test_greedy_alternative_paths_agree(switch, mode, monkeypatch):
+    """The library keeps alternative device paths behind environment switches: the
+    per-round kernels (also what shapes without a cooperative launch take), the persistent kernel without
+    the replicated decode state, the one-CTA gate chain.  Each must decode exactly what the default path
+    decodes: plain greedy and the gated hot-word greedy (hypotheses and gate decisions)."""
+    import bench
+    from wenet_celoss_b200 import greedy_search_batch
+    if mode is None and switch == "B200_GATE_SINGLE_CTA":
+        pytest.skip("the gate chain only runs in the gated decode")
+    m = _search_model(1000, seed=31)
+    kw = {}
+    if mode == "on":
+        torch.manual_seed(32)
+        m.context_bias = bench._ContextBias(256, 100).eval()
+        m.loss_mode = "pred"
+        with torch.no_grad():
+            m.joint.ffn_out.bias[0] -= 4.5
+        kw = dict(context_list=torch.zeros(100, 4, dtype=torch.int32, device=DEV),
+                  context_lengths=torch.full((100,), 4, dtype=torch.int32, device=DEV),
+                  context_filter_state="on", return_decisions=True)
+    g = torch.Generator().manual_seed(33)
+    B, T = 5, 40
+    enc = (torch.randn(B, T, 256, generator=g) * 2.0).to(DEV)
+    lens = torch.tensor([40, 31, 40, 12, 25], device=DEV)
+    md = copy.deepcopy(m).to(DEV)
+    out = {}
+    for val in ("0", "1"):
+        monkeypatch.setenv(switch, val)
+        out[val] = greedy_search_batch(md, enc, lens, n_steps=5, **kw)
+    assert out["0"] == out["1"]
+    hyps = out["0"][0] if mode == "on" else out["0"]
+    assert any(len(h) > 0 for h in hyps)
+
+
+@pytest.mark.parametrize("switch", ["B200_BEAM_NO_PDL", "B200_BEAM_TM4"])
+def test_beam_alternative_paths_agree(switch, monkeypatch):
+    """Beam search launched without programmatic stream serialization, and with the 4-row register tiles of
+    the logits GEMM (same k order per accumulator): same n-best lists, bit-identical scores."""
+    from wenet_celoss_b200 import prefix_beam_search_batch
+    m = _search_model(1000, seed=41).to(DEV)
+    g = torch.Generator().manual_seed(43)
+    B, T = 4, 30
+    enc = (torch.randn(B, T, 256, generator=g) * 2.0).to(DEV)
+    lens = torch.tensor([30, 22, 30, 7], dtype=torch.int32, device=DEV)
+    out = {}
+    for val in ("0", "1"):
+        monkeypatch.setenv(switch, val)
+        beams = prefix_beam_search_batch(m, enc, lens, beam_size=10)
+        out[val] = [[(tuple(s.hyp), s.score) for s in bb] for bb in beams]
+    assert out["0"] == out["1"]
