@@ -43,15 +43,21 @@ __device__ __forceinline__ void argmax_pair(float& bv, int& bi, float ov, int oi
   }
 }
 // log_add over up to three terms in the reference's order (common.py:268-276)
-__device__ __forceinline__ double log_add3(double a, double b, double c) {
-  const double mx = fmax(a, fmax(b, c));
-  if (mx == -INFINITY) return -INFINITY;
-  return mx + log(exp(a - mx) + exp(b - mx) + exp(c - mx));
-}
+// A term of -inf contributes exp(-inf) = +0.0 to the sum, and x + log(1.0 + 0.0) == x: the shortcuts below
+// return bit-for-bit what the full expression returns (most entries of a frame have such a term, and the
+// fp64 exp / log chain of the entry phase is what a frame waits for).
 __device__ __forceinline__ double log_add2(double a, double b) {
+  if (a == -INFINITY) return b;
+  if (b == -INFINITY) return a;
   const double mx = fmax(a, b);
-  if (mx == -INFINITY) return -INFINITY;
   return mx + log(exp(a - mx) + exp(b - mx));
+}
+__device__ __forceinline__ double log_add3(double a, double b, double c) {
+  if (a == -INFINITY) return log_add2(b, c);
+  if (b == -INFINITY) return log_add2(a, c);
+  if (c == -INFINITY) return log_add2(a, b);
+  const double mx = fmax(a, fmax(b, c));
+  return mx + log(exp(a - mx) + exp(b - mx) + exp(c - mx));
 }
 
 struct Params {
